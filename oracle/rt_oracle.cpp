@@ -1,0 +1,295 @@
+// oracle/rt_oracle.cpp -- TEST INFRASTRUCTURE (oracle-2).
+//
+// Plain C++ CPU restatement of the reference's time-dependent multigroup S_N slab solve
+// (reference src/solver.cpp, src/correction.cpp, src/Planck.cpp, src/GLQuad.cpp,
+// include/Constants.h).  It exists so that parity tests can (a) snapshot the state after any
+// number of stage sweeps -- the reference has no per-step hook -- and (b) run at sizes where the
+// reference's per-cell `half_ends = ends` copy (O(N^2)) is intractable.
+//
+// Parity status: PINNED.  Checked bit-for-bit against the unmodified reference compiled in place
+// (oracle/_ref/ref_dump) by tests/golden/make_golden.py and tests/test_oracle_vs_golden.py.
+//
+// Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+// use this library; the product path (librt_cuda.so) never routes through it.
+#include "rt_oracle.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstddef>
+#include <cstring>
+#include <limits>
+#include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#include "planck_port.inc"
+#include "correction_port.inc"
+#include "sweep_port.inc"
+
+struct rto_solver
+{
+   rto_params p;
+   std::vector<double> mu, wt;
+   rto::GaussRule gauss;
+   rto::GroupTerms gt;
+   rto::Sweep sw;
+   int stages_done;
+   rto_solver() : gauss(rto::PLANCK_ACCURACY), stages_done(0) {}
+};
+
+extern "C" {
+
+// GLQuad::build, GLQuad.cpp:4-44 (Newton on the Legendre recurrence, tolerance 1e-12, truncated PI)
+void rto_glquad(int M, double norm, double *mu, double *wt)
+{
+   const double x1 = -1.0, x2 = 1.0;
+   const double xm = 0.5 * (x2 + x1), xl = 0.5 * (x2 - x1);
+   const double dnp = static_cast<double>(M);
+   const int m = (M + 1) / 2;
+   for (int i = 1; i <= m; ++i)
+   {
+      double di = static_cast<double>(i);
+      double z1, pp, z = std::cos(rto::PI_TRUNC * (di - 0.25) / (dnp + 0.5));
+      do
+      {
+         double p1 = 1.0, p2 = 0.0;
+         for (int j = 1; j <= M; ++j)
+         {
+            double dj = static_cast<double>(j);
+            double p3 = p2;
+            p2 = p1;
+            p1 = ((2.0 * dj - 1.0) * z * p2 - (dj - 1.0) * p3) / dj;
+         }
+         pp = dnp * (z * p1 - p2) / (z * z - 1.0);
+         z1 = z;
+         z = z1 - p1 / pp;
+      } while (std::fabs(z - z1) > 1.0e-12);
+      mu[i - 1] = xm - xl * z;
+      mu[M - i] = xm + xl * z;
+      wt[i - 1] = norm * xl / ((1.0 - z * z) * pp * pp);
+      wt[M - i] = wt[i - 1];
+   }
+}
+
+// Solver::generate_group_edges, solver.cpp:6-19.  For G == 1 the reference's
+// `assert(logfac = 1.)` is an assignment; logfac is unused then anyway.
+void rto_group_edges(int G, double efirst, double elast, double *e_edge)
+{
+   double logfac = (std::log(elast) - std::log(efirst)) / (G - 1.0);
+   logfac = std::exp(logfac);
+   e_edge[0] = 0.0;
+   e_edge[1] = efirst;
+   for (int g = 1; g < G; g++) e_edge[g + 1] = e_edge[g] * logfac;
+}
+
+void rto_planck(double T, int G, const double *e_edge, double *B, double *dBdT)
+{
+   rto::GaussRule q(rto::PLANCK_ACCURACY);
+   std::fill(B, B + G, 0.0);
+   std::fill(dBdT, dBdT + G, 0.0);
+   rto::planck_groups(q, T, G, e_edge, B, dBdT);
+}
+
+rto_solver *rto_create(const rto_params *p)
+{
+   rto_solver *s = new rto_solver();
+   s->p = *p;
+   const int M = p->M, N = p->N, G = p->G;
+   s->mu.assign(p->mu, p->mu + M);
+   s->wt.assign(p->wt, p->wt + M);
+   s->p.mu = s->mu.data();
+   s->p.wt = s->wt.data();
+   s->gt.setup(G, p->e_edge, p->kappa, p->rho);
+   s->p.e_edge = s->gt.e_edge.data();
+   s->p.kappa = s->gt.kappa.data();
+   rto::Sweep &sw = s->sw;
+   sw.M = M; sw.N = N; sw.G = G; sw.dx = p->dx; sw.dt = p->dt;
+   const size_t n3 = (size_t)M * G * N;
+   sw.ends.assign(2 * n3, 0.0);
+   sw.prev.assign(2 * n3, 0.0);
+   sw.half.assign(2 * n3, 0.0);
+   sw.psi.assign(n3, 0.0);
+   sw.psi_source.assign((size_t)M * G, 0.0);
+   if (p->psi_source) std::copy(p->psi_source, p->psi_source + (size_t)M * G, sw.psi_source.begin());
+   s->p.psi_source = sw.psi_source.data();
+   // Correction ctor computes the Planck integrals once (correction.cpp:318-319); the solver then
+   // initialises psi = ends(L) = ends(R) = B_g (solver.cpp:166-181).
+   rto::planck_groups(s->gauss, p->T, G, s->gt.e_edge.data(), s->gt.B.data(), s->gt.dBdT.data());
+   for (int c = 0; c < N; c++)
+      for (int g = 0; g < G; g++)
+         for (int i = 0; i < M; i++)
+         {
+            double v = s->gt.B[g];
+            sw.psi[sw.ip(i, g, c)] = v;
+            sw.ends[sw.ie(i, g, c, 0)] = v;
+            sw.ends[sw.ie(i, g, c, 1)] = v;
+         }
+   return s;
+}
+
+void rto_destroy(rto_solver *s) { delete s; }
+
+int rto_total_stages(const rto_solver *s) { return s->p.max_timesteps * (s->p.ts_method == 3 ? 4 : 1); }
+int rto_stages_done(const rto_solver *s) { return s->stages_done; }
+
+void rto_run_stages(rto_solver *s, int n)
+{
+   const rto_params &p = s->p;
+   rto::Sweep &sw = s->sw;
+   rto::GroupTerms &gt = s->gt;
+   const int M = p.M, G = p.G;
+   const double beta = p.V / rto::C_LIGHT;
+   for (int k = 0; k < n; k++)
+   {
+      const int it = s->stages_done;
+      if (it == 0 && p.use_mg_equilib)
+      {
+         // Solver::computeEquilibriumSources, solver.cpp:287-315
+         gt.per_stage(s->gauss, p.T);
+         for (int i = 0; i < M; i++)
+            for (int g = 0; g < G; g++)
+            {
+               double val = 4 * gt.B[g] - gt.dEB[g];
+               double mult = s->mu[i] * p.V / rto::C_LIGHT;
+               val *= mult;
+               val += gt.B[g];
+               sw.psi_source[i + (size_t)M * g] = val;
+            }
+      }
+      gt.per_stage(s->gauss, p.T);               // solver.cpp:608
+      int kind;
+      double tau;
+      bool snapshot = false;
+      if (p.ts_method != 3 || it % 4 == 0) sw.prev = sw.ends; // solver.cpp:620-625
+      if (p.ts_method == 1) { kind = 0; tau = p.dt; }
+      else if (p.ts_method == 2) { kind = 1; tau = p.dt; }
+      else
+      {
+         const int ind = it % 4;                 // solver.cpp:723-750
+         kind = (ind == 0 || ind == 2) ? 0 : (ind == 1 ? 1 : 2);
+         tau = p.dt / 2.;
+         snapshot = (ind == 1);
+      }
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static) num_threads(p.num_threads > 0 ? p.num_threads : 1)
+#endif
+      for (int g = 0; g < G; g++)
+         sw.sweep_group(g, kind, tau, snapshot, s->mu.data(), p.bc_left, p.bc_right, gt.rho[g], gt.kappa[g], gt.B[g],
+                        p.use_correction != 0, gt.cor1[g], gt.cor2[g], gt.cor3[g], beta);
+      s->stages_done++;
+   }
+}
+
+void rto_get_psi(const rto_solver *s, double *psi) { std::copy(s->sw.psi.begin(), s->sw.psi.end(), psi); }
+
+void rto_get_ends(const rto_solver *s, int which, double *out)
+{
+   const std::vector<double> &v = which == 0 ? s->sw.ends : (which == 1 ? s->sw.prev : s->sw.half);
+   std::copy(v.begin(), v.end(), out);
+}
+
+// solver.cpp:191-237 (ascending-m accumulation)
+void rto_moments(const rto_solver *s, double *phi, double *phi_plus, double *F)
+{
+   const rto::Sweep &sw = s->sw;
+   const int M = sw.M, N = sw.N, G = sw.G;
+   for (int g = 0; g < G; g++)
+      for (int c = 0; c < N; c++)
+      {
+         double a = 0., b = 0., f = 0.;
+         for (int m = 0; m < M; m++) a += s->wt[m] * sw.psi[sw.ip(m, g, c)];
+         for (int m = M / 2; m < M; m++) b += s->wt[m] * sw.psi[sw.ip(m, g, c)];
+         for (int m = 0; m < M; m++) f += s->mu[m] * s->wt[m] * sw.psi[sw.ip(m, g, c)];
+         if (phi) phi[g + (size_t)G * c] = a;
+         if (phi_plus) phi_plus[g + (size_t)G * c] = b;
+         if (F) F[g + (size_t)G * c] = f;
+      }
+}
+
+// solver.cpp:240-284
+void rto_balance(const rto_solver *s, double *balance)
+{
+   const rto::Sweep &sw = s->sw;
+   const int M = sw.M, N = sw.N, G = sw.G;
+   const double ac = rto::RAD_A * rto::C_LIGHT;
+   std::vector<double> phi((size_t)G * N);
+   rto_moments(s, phi.data(), nullptr, nullptr);
+   for (int g = 0; g < G; g++)
+   {
+      double j_half_minus = 0., j_half_plus = 0., jN_half_minus = 0., jN_half_plus = 0., a = 0., src = 0.;
+      for (int m = 0; m < M; m++)
+      {
+         double mu = s->mu[m];
+         if (mu < 0.)
+         {
+            j_half_minus -= sw.ends[sw.ie(m, g, 0, 0)] * mu * s->wt[m];
+            jN_half_minus -= sw.ends[sw.ie(m, g, N - 1, 0)] * mu * s->wt[m];
+         }
+         else
+         {
+            j_half_plus += sw.ends[sw.ie(m, g, 0, 1)] * mu * s->wt[m];
+            jN_half_plus += sw.ends[sw.ie(m, g, N - 1, 1)] * mu * s->wt[m];
+         }
+      }
+      for (int c = 0; c < N; c++)
+      {
+         a += s->gt.rho[g] * s->gt.kappa[g] * phi[g + (size_t)G * c] * sw.dx;
+         src += s->gt.rho[g] * s->gt.kappa[g] * ac * std::pow(s->p.T, 4) * sw.dx;
+      }
+      double sources = j_half_plus + jN_half_minus + src;
+      double sinks = jN_half_plus + j_half_minus + a;
+      balance[g] = std::fabs(sinks - sources) / sources;
+   }
+}
+
+// solver.cpp:826-850
+void rto_group_ends(const rto_solver *s, double *left, double *right)
+{
+   const rto::Sweep &sw = s->sw;
+   for (int g = 0; g < sw.G; g++)
+   {
+      double l = 0., r = 0.;
+      for (int m = 0; m < sw.M; m++)
+      {
+         if (s->mu[m] < 0.) l += sw.ends[sw.ie(m, g, 0, 0)];
+         else r += sw.ends[sw.ie(m, g, sw.N - 1, 1)];
+      }
+      left[g] = l / (s->gt.de_ave[g] * rto::C_LIGHT);
+      right[g] = r / (s->gt.de_ave[g] * rto::C_LIGHT);
+   }
+}
+
+void rto_get_group_terms(const rto_solver *s, double *B, double *dBdT, double *dEB, double *dsigEdE, double *dkapEB,
+                         double *kappa_edge)
+{
+   const rto::GroupTerms &gt = s->gt;
+   if (B) std::copy(gt.B.begin(), gt.B.end(), B);
+   if (dBdT) std::copy(gt.dBdT.begin(), gt.dBdT.end(), dBdT);
+   if (dEB) std::copy(gt.dEB.begin(), gt.dEB.end(), dEB);
+   if (dsigEdE) std::copy(gt.dsigEdE.begin(), gt.dsigEdE.end(), dsigEdE);
+   if (dkapEB) std::copy(gt.dkapEB.begin(), gt.dkapEB.end(), dkapEB);
+   if (kappa_edge) std::copy(gt.kappa_edge.begin(), gt.kappa_edge.end(), kappa_edge);
+}
+
+void rto_get_psi_source(const rto_solver *s, double *out)
+{
+   std::copy(s->sw.psi_source.begin(), s->sw.psi_source.end(), out);
+}
+
+// correction.cpp:39-63 and 100-122
+int rto_validate(const rto_solver *s, double *out3)
+{
+   const rto::GroupTerms &gt = s->gt;
+   const double ac = rto::RAD_A * rto::C_LIGHT, T = s->p.T;
+   double bsum = 0., dbsum = 0., emis = 0.;
+   for (int g = 0; g < gt.G; g++) { bsum += gt.B[g]; dbsum += gt.dBdT[g]; }
+   for (int g = 0; g < gt.G; g++) emis += gt.kappa[g] * gt.B[g];
+   if (out3) { out3[0] = bsum; out3[1] = dbsum; out3[2] = emis; }
+   double acT4 = ac * std::pow(T, 4), dacT4 = 4.0 * ac * std::pow(T, 3);
+   bool ok = !(std::fabs(acT4 - bsum) > rto::VALIDATION_TOL || std::fabs(dacT4 - dbsum) > rto::VALIDATION_TOL);
+   ok = ok && !(std::fabs(emis - s->p.kappa_grey * acT4) > rto::VALIDATION_TOL);
+   return ok ? 1 : 0;
+}
+
+} // extern "C"
