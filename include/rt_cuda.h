@@ -1,0 +1,134 @@
+/* include/rt_cuda.h -- C ABI of librt_cuda.so: the B200 (sm_100a) implementation of the
+ * radiative-transfer miniapp's hot path (time-dependent multigroup S_N slab solve).
+ *
+ * The reference has no FFI/plugin boundary; its hot layer is the C++ class rt::Solver
+ * (reference include/solver.h:76-98).  This ABI sits directly UNDER that class surface: the
+ * drop-in rt::Solver shipped in radiative-transfer_b200/host/ (and the Python mirror in
+ * radiative-transfer_b200/solver.py) forwards each public method to one entry point below.
+ * Plain C types only; all arrays are fp64; every pointer argument is a HOST pointer owned by
+ * the caller; results are written in the REFERENCE's own index order (Eigen column-major):
+ *
+ *     psi(i,g,c)      at i + M*(g + Gl*c)
+ *     ends(i,g,c,s)   at i + M*(g + Gl*(c + N*s))    s=0 left node, s=1 right node
+ *     phi/F(g,c)      at g + Gl*c
+ *     psi_source(i,g) at i + M*g                     (g global, 0..G-1)
+ *
+ * where Gl = group_count is the number of groups THIS handle owns (energy groups are the
+ * sharding unit across GPUs and the batching unit inside one GPU; they never couple).
+ *
+ * Every function returns 0 on success, non-zero on failure; rt_last_error() gives the message.
+ * There is no CPU fallback: rt_create fails if no CUDA device is usable.
+ * Thread-safety: a handle must be used from one host thread at a time (like rt::Solver).
+ */
+#ifndef RT_CUDA_H
+#define RT_CUDA_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_ABI_VERSION 1
+
+typedef struct rt_params
+{
+   /* sizes: replaces ParameterHandler::get_M/get_N/get_G (reference solver.cpp:57-59) */
+   int M;                /* directions, even                                             */
+   int N;                /* cells                                                        */
+   int G;                /* energy groups of the whole problem                           */
+   int group_begin;      /* first group owned by this handle (0 for a single-GPU solve)  */
+   int group_count;      /* number of groups owned (G for a single-GPU solve)            */
+   /* ParameterHandler getters used in the hot loop (solver.cpp:338,620,641,667,706) */
+   int ts_method;        /* 1 BE, 2 CN, 3 BDF2                                           */
+   int max_timesteps;
+   int bc_left;          /* 0 vacuum (falls through to source), 1 source, 2 reflective */
+   int bc_right;         /* 0 vacuum, 1 source, 2 reflective (=0 inflow, solver.cpp:647-652)      */
+   int use_correction;
+   int use_mg_equilib;
+   int validate;         /* include_validation: rt_solve fails if the sums are off (solver.cpp:609-612) */
+   int device;           /* CUDA device ordinal                                          */
+   int groups_per_batch; /* 0 = automatic: all owned groups if they fit in HBM, else the largest batch that fits */
+   double dx, dt, rho, T, V, kappa_grey;
+   const double *mu;         /* M    GLQuad nodes, ascending (solver.cpp:76-78)           */
+   const double *wt;         /* M    GLQuad weights                                       */
+   const double *e_edge;     /* G+1  group edges (solver.cpp:96-100)                      */
+   const double *kappa;      /* G    group opacities (solver.cpp:145-152)                 */
+   const double *psi_source; /* M*G  boundary sources or NULL (=0) (solver.cpp:67-73)     */
+} rt_params;
+
+typedef struct rt_solver rt_solver;
+
+typedef struct rt_timing
+{
+   double sweep_ms[3];        /* device time spent in BE / CN / BDF stage-sweep launches (CUDA events) */
+   long long sweep_launches[3];
+   double moments_ms;
+   long long stages;          /* stage sweeps executed (per batch, summed)                */
+   long long unknown_stages;  /* M * groups * N summed over executed stage sweeps         */
+   long long kernel_launches; /* all kernels launched by the library since rt_create      */
+   long long h2d_bytes, d2h_bytes;
+} rt_timing;
+
+typedef struct rt_plan
+{
+   int groups_per_batch, n_batches, resident; /* resident = 1 when one batch holds every owned group */
+   int tile_cells, tiles_per_row, sweep_grid, sweep_block;
+   size_t bytes_per_group, state_bytes, free_bytes, total_bytes;
+} rt_plan;
+
+const char *rt_last_error(void);
+int rt_abi_version(void);
+
+/* rt::Solver::Solver (solver.cpp:46-188): uploads the tables, evaluates the Planck integrals and
+ * per-group correction terms on the device, initialises psi = ends = B_g. */
+int rt_create(const rt_params *p, rt_solver **out);
+int rt_destroy(rt_solver *s);
+int rt_get_plan(const rt_solver *s, rt_plan *plan);
+
+/* rt::Solver::solve (solver.cpp:590-823): all max_timesteps*(ts_method==3?4:1) stage sweeps.
+ * Works in resident and in batched mode. */
+int rt_solve(rt_solver *s);
+/* n further stage sweeps (resident mode only) -- the per-step hook the parity tests use. */
+int rt_run_stages(rt_solver *s, int n);
+int rt_stages_done(const rt_solver *s, int *n);
+int rt_total_stages(const rt_solver *s, int *n);
+/* re-initialise psi = ends = B_g and the stage counter (new run on the same tables) */
+int rt_reset(rt_solver *s);
+
+/* caller-owned result buffers (solver.h:30-33; main.cc:88-98) */
+int rt_get_psi(rt_solver *s, double *psi);                 /* M*Gl*N ; resident mode               */
+int rt_get_ends(rt_solver *s, int which, double *ends);    /* which: 0 ends, 1 prev_ends, 2 half_ends ; M*Gl*N*2 ; resident mode */
+/* compute_angle_integrated_intensity / compute_positive_... / compute_radiative_flux
+ * (solver.cpp:191-237); each Gl*N, any pointer may be NULL */
+int rt_moments(rt_solver *s, double *phi, double *phi_plus, double *F);
+/* same three moments in the device-native group-major order g*N + c (no layout conversion) */
+int rt_moments_group_major(rt_solver *s, double *phi, double *phi_plus, double *F);
+int rt_balance(rt_solver *s, double *balance);             /* Gl ; compute_balance, solver.cpp:240-284 */
+int rt_group_ends(rt_solver *s, double *left, double *right); /* Gl each ; compute_group_ends, solver.cpp:826-850 */
+/* per-group terms of the Correction class for ALL G groups (correction.cpp:25-36,125-249,328-340):
+ * B, dBdT, dEB, dsigEdE, dkapEB (G each), kappa_edge (G+1); any pointer may be NULL */
+int rt_get_group_terms(rt_solver *s, double *B, double *dBdT, double *dEB, double *dsigEdE, double *dkapEB,
+                       double *kappa_edge);
+int rt_get_psi_source(rt_solver *s, double *psi_source);   /* M*G */
+/* Correction::validate_correction (correction.cpp:39-63,100-122): sums3 = {sum B, sum dBdT, sum kappa*B};
+ * *ok = 1 when all three identities hold to 1e-6 */
+int rt_validate(rt_solver *s, double *sums3, int *ok);
+
+/* After every completed time step (BDF2: 4 stage sweeps) copy phi (Gl*N, group-major g*N + c when
+ * group_major != 0, reference order otherwise) into `phi_host`; NULL switches it off.  Used by the
+ * end-to-end measurement: the device->host read of each step's result is inside rt_solve. */
+int rt_set_step_output(rt_solver *s, double *phi_host, int group_major);
+
+int rt_get_timing(const rt_solver *s, rt_timing *t);
+int rt_reset_timing(rt_solver *s);
+
+/* Standalone device evaluation of the Planck group integrals (Planck.cpp:50-77 + the unit change of
+ * correction.cpp:25-36) for `ncell` temperatures: B,dBdT are [ncell][G] (g fastest). */
+int rt_planck_groups(int device, int G, const double *e_edge, int ncell, const double *T, double *B, double *dBdT,
+                     double *kernel_ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_CUDA_H */

@@ -1,0 +1,288 @@
+// group_terms.cu -- G-length device kernels: Planck group integrals and the per-group pieces of the
+// reference's Correction class.  fp64 throughout; sm_100a.
+//
+// Reference being reproduced (results, not code):
+//   Planck::get_Planck / integrate_B / integrate_dBdT        src/Planck.cpp:50-229, include/Planck.h:86-125
+//   Correction::generate_planck_integrals                    src/correction.cpp:25-36
+//   Correction::compute_group_edge_opacities                 src/correction.cpp:125-139
+//   Correction::compute_components_of_correction_source, pf  src/correction.cpp:11-22,162-249
+//   Correction::compute_correction_terms                     src/correction.cpp:328-340
+//   Correction::validate_planck_integrals / validate_emission src/correction.cpp:39-63,100-122
+//   Solver::computeEquilibriumSources                        src/solver.cpp:287-315
+#include "rt_common.cuh"
+#include "group_terms.cuh"
+
+namespace rtk
+{
+__constant__ double c_gauss_pt[12];
+__constant__ double c_gauss_w[12];
+
+__device__ __forceinline__ double rad_a_long()
+{
+   // RADIATION_CONSTANT_A_LONG = 8 pi^5 k^4 / (15 h^3 c^3) with k = 1 (Constants.h:21-22)
+   const double pi2 = PI_TRUNC * PI_TRUNC;
+   return (8.0 * (pi2 * pi2 * PI_TRUNC)) / (15.0 * (H_KEV_SH * H_KEV_SH * H_KEV_SH) * (C_LIGHT * C_LIGHT * C_LIGHT));
+}
+
+__device__ __forceinline__ double inv_h3c2() { return 1.0 / ((H_KEV_SH * H_KEV_SH * H_KEV_SH) * (C_LIGHT * C_LIGHT)); }
+
+// Planck function and its temperature derivative at one energy (Planck.h:86-125), k = 1.
+__device__ __forceinline__ double planck_B(double T, double E)
+{
+   return 2.0 * (E * E * E) * inv_h3c2() / expm1(E / T);
+}
+__device__ __forceinline__ double planck_dBdT(double T, double E)
+{
+   const double ex = exp(E / T), em = expm1(E / T);
+   const double E2 = E * E;
+   return 2.0 * inv_h3c2() * (E2 * E2) / (T * T) * ex / (em * em);
+}
+
+// S(z1) - S(z2), S(z) = sum_{n=N..1} e^{-nz}/n^4 * P(nz), summed in DESCENDING n like the reference
+// (Planck.cpp:94-120, 170-194).  DERIV selects P: cubic (B) or quartic (dB/dT).  N starts at 32 and
+// grows while the tail estimate exceeds 2.2e-16 relative to the first term.
+template <bool DERIV>
+__device__ double planck_series(double z1, double z2)
+{
+   auto poly = [](double x) {
+      return DERIV ? ((((x + 4.0) * x + 12.0) * x + 24.0) * x + 24.0) : (((x + 3.0) * x + 6.0) * x + 6.0);
+   };
+   const double eps = 2.220446049250313e-16;
+   int N = 32;
+   double first = exp(-z1) * poly(z1);
+   first = fmax(first, eps);
+   const double geo = 1.0 / (1.0 - exp(-z1));
+   while (true)
+   {
+      const double n1 = N + 1.0;
+      const double n2 = n1 * n1;
+      const double val = exp(-n1 * z1) * geo / (n2 * n2) * poly(n1 * z1) / first;
+      if (val > eps && N < (1 << 20)) ++N; else break;
+   }
+   double s1 = 0.0, s2 = 0.0;
+   for (int n = N; n > 0; --n)
+   {
+      const double dn = (double)n, n2 = dn * dn, in4 = 1.0 / (n2 * n2);
+      s1 += exp(-dn * z1) * in4 * poly(dn * z1);
+      s2 += exp(-dn * z2) * in4 * poly(dn * z2);
+   }
+   return s1 - s2;
+}
+
+template <bool DERIV>
+__device__ double gauss12(double T, double lo, double hi)
+{
+   const double mid = 0.5 * (hi + lo), map = 0.5 * (hi - lo);
+   double acc = 0.0;
+#pragma unroll
+   for (int i = 0; i < 12; ++i)
+   {
+      const double E = mid + map * c_gauss_pt[i];
+      acc += map * c_gauss_w[i] * (DERIV ? planck_dBdT(T, E) : planck_B(T, E));
+   }
+   return acc;
+}
+
+// One group integral in keV units, times 4*pi (Planck.cpp:85-154 / 161-229): 12-point Gauss for
+// z2 <= 0.7, series for z1 >= 0.5, split at z = 0.6 otherwise.
+template <bool DERIV>
+__device__ double planck_group_integral(double T, double E_min, double E_max)
+{
+   if (T == 0.0 || E_min == E_max) return 0.0;
+   const double z1 = E_min / T, z2 = E_max / T;
+   const double T2 = T * T;
+   const double pref = 2.0 * (DERIV ? T2 * T : T2 * T2) * inv_h3c2();
+   double v;
+   if (z2 <= 0.7) v = gauss12<DERIV>(T, E_min, E_max);
+   else if (z1 >= 0.5) v = pref * planck_series<DERIV>(z1, z2);
+   else v = gauss12<DERIV>(T, E_min, 0.6 * T) + pref * planck_series<DERIV>(0.6, z2);
+   return v * 4.0 * PI_TRUNC;
+}
+
+// raw[cell][g] for g < G-1 ; one thread per (cell, group) x {B, dBdT}
+__global__ void planck_integrals_kernel(int G, int ncell, const double *__restrict__ e_edge, const double *__restrict__ T,
+                                        double *__restrict__ B, double *__restrict__ dBdT)
+{
+   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+   const long long total = (long long)ncell * (G - 1);
+   if (idx >= total) return;
+   const int c = (int)(idx / (G - 1)), g = (int)(idx % (G - 1));
+   const double t = T[c], lo = e_edge[g], hi = e_edge[g + 1];
+   if (blockIdx.y == 0) B[(size_t)c * G + g] = planck_group_integral<false>(t, lo, hi);
+   else dBdT[(size_t)c * G + g] = planck_group_integral<true>(t, lo, hi);
+}
+
+// Remainder of the grey totals into the last group (sequential ascending subtraction,
+// Planck.cpp:58-76: kept only if positive) and the keV -> jk unit change (correction.cpp:31-35).
+// One thread per cell.  keep_last: value the last group keeps when the remainder is not positive.
+__global__ void planck_finalize_kernel(int G, int ncell, const double *__restrict__ T, double *__restrict__ B,
+                                       double *__restrict__ dBdT)
+{
+   const int c = blockIdx.x * blockDim.x + threadIdx.x;
+   if (c >= ncell) return;
+   const double t = T[c];
+   double bsum = rad_a_long() * C_LIGHT * (t * t) * (t * t);
+   double dsum = 4.0 * rad_a_long() * C_LIGHT * (t * t) * t;
+   double *b = B + (size_t)c * G, *d = dBdT + (size_t)c * G;
+   for (int g = 0; g < G - 1; ++g)
+   {
+      bsum -= b[g];
+      dsum -= d[g];
+      b[g] *= K_JPK;
+      d[g] *= K_JPK;
+   }
+   // last group: the remainder when positive, otherwise the stale previous value re-scaled (reference quirk)
+   b[G - 1] = K_JPK * (bsum > 0.0 ? bsum : b[G - 1]);
+   d[G - 1] = K_JPK * (dsum > 0.0 ? dsum : d[G - 1]);
+}
+
+__device__ __forceinline__ double pf(double E, double T) // correction.cpp:11-22
+{
+   return K_JPK * (E * E * E) * inv_h3c2() / expm1(E / T);
+}
+
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+   return v;
+}
+
+// Everything G-length that follows the Planck integrals.  One block; threads stride over groups.
+__global__ void group_terms_kernel(GroupTermsArgs a)
+{
+   const int G = a.G, tid = threadIdx.x, nt = blockDim.x;
+   const double T = a.T;
+   // group averages / widths (solver.cpp:22-32) and edge opacities (correction.cpp:125-139)
+   for (int g = tid; g <= G; g += nt)
+   {
+      double ke;
+      if (g == 0) ke = a.kappa[0];
+      else if (g == G) ke = a.kappa[G - 1];
+      else
+      {
+         const double ea = 0.5 * (a.e_edge[g] + a.e_edge[g + 1]), eam = 0.5 * (a.e_edge[g - 1] + a.e_edge[g]);
+         const double wl = (ea - a.e_edge[g]) / (ea - eam), wr = (a.e_edge[g] - eam) / (ea - eam);
+         ke = a.kappa[g - 1] * wl + a.kappa[g] * wr;
+      }
+      a.kappa_edge[g] = ke;
+      a.epf[g] = (g == 0) ? 0.0 : a.e_edge[g] * pf(a.e_edge[g], T); // E*pf(E) at each edge (edge 0 is never used)
+   }
+   __syncthreads();
+   for (int g = tid; g < G; g += nt)
+   {
+      const double de = a.e_edge[g + 1] - a.e_edge[g];
+      double dEB, dsig, dkap;
+      // 2-point edge stencils (correction.cpp:165-174, 206-211, 241-249); note the last group's
+      // dkapEB uses edge G-1 for kappa as well, and for G == 1 the "last" formulas win for dsigEdE only.
+      if (g == 0)
+      {
+         dEB = a.epf[1];
+         dsig = a.kappa_edge[1] * a.e_edge[1] / de;
+         dkap = a.kappa_edge[1] * a.epf[1];
+      }
+      else if (g < G - 1)
+      {
+         dEB = a.epf[g + 1] - a.epf[g];
+         dsig = (a.kappa_edge[g + 1] * a.e_edge[g + 1] - a.kappa_edge[g] * a.e_edge[g]) / de;
+         dkap = a.kappa_edge[g + 1] * a.epf[g + 1] - a.kappa_edge[g] * a.epf[g];
+      }
+      else
+      {
+         dEB = -a.epf[G - 1];
+         dsig = 0.0; // set below
+         dkap = -a.kappa_edge[G - 1] * a.epf[G - 1];
+      }
+      if (g == G - 1) dsig = -a.kappa_edge[G] * a.e_edge[G] / de;
+      a.dEB[g] = dEB;
+      a.dsigEdE[g] = dsig;
+      a.dkapEB[g] = dkap;
+      const double sig = a.rho * a.kappa[g], Bg = a.B[g];
+      a.sigma[g] = sig;
+      a.srcB[g] = sig * Bg;
+      a.cor1[g] = dsig;
+      a.cor2[g] = 3.0 * sig * Bg - dkap;
+      a.cor3[g] = dsig * (4.0 * Bg - dEB);
+      a.de_ave[g] = de;
+   }
+   // validation sums (correction.cpp:39-63,100-122) -- warp-shuffle reduction
+   double sb = 0.0, sd = 0.0, se = 0.0;
+   for (int g = tid; g < G; g += nt)
+   {
+      sb += a.B[g];
+      sd += a.dBdT[g];
+      se += a.kappa[g] * a.B[g];
+   }
+   __shared__ double red[3][32];
+   sb = warp_sum(sb); sd = warp_sum(sd); se = warp_sum(se);
+   if ((tid & 31) == 0) { red[0][tid >> 5] = sb; red[1][tid >> 5] = sd; red[2][tid >> 5] = se; }
+   __syncthreads();
+   if (tid < 32)
+   {
+      const int nw = (nt + 31) >> 5;
+      sb = tid < nw ? red[0][tid] : 0.0; sd = tid < nw ? red[1][tid] : 0.0; se = tid < nw ? red[2][tid] : 0.0;
+      sb = warp_sum(sb); sd = warp_sum(sd); se = warp_sum(se);
+      if (tid == 0) { a.sums[0] = sb; a.sums[1] = sd; a.sums[2] = se; }
+   }
+}
+
+// Boundary inflow table bdry(i,g) (solver.cpp:635-692) from psi_source, optionally overwritten by the
+// equilibrium sources psi_source(i,g) = B_g + mu_i*(V/c)*(4 B_g - dEB_g) (solver.cpp:297-314).
+__global__ void boundary_table_kernel(int M, int G, int bc_left, int bc_right, int use_mg_equilib, double V,
+                                      const double *__restrict__ mu, const double *__restrict__ B,
+                                      const double *__restrict__ dEB, double *__restrict__ psi_source,
+                                      double *__restrict__ bdry)
+{
+   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+   if (idx >= M * G) return;
+   const int i = idx % M, g = idx / M;
+   double src = psi_source[idx];
+   if (use_mg_equilib)
+   {
+      double val = 4.0 * B[g] - dEB[g];
+      val *= mu[i] * V / C_LIGHT;
+      val += B[g];
+      src = val;
+      psi_source[idx] = val;
+   }
+   double b;
+   if (mu[i] < 0.0) b = (bc_right == 1) ? src : 0.0;          // vacuum and reflective right: no inflow
+   else b = (bc_left == 0 || bc_left == 1) ? src : 0.0;        // vacuum falls through to source; reflective is resolved in the sweep
+   bdry[idx] = b;
+}
+
+// ------------------------------------------------------------------------------------------ host side
+void upload_gauss_rule(const double *pt, const double *w)
+{
+   cudaMemcpyToSymbol(c_gauss_pt, pt, 12 * sizeof(double));
+   cudaMemcpyToSymbol(c_gauss_w, w, 12 * sizeof(double));
+}
+
+int launch_planck(int G, int ncell, const double *d_e_edge, const double *d_T, double *d_B, double *d_dBdT, cudaStream_t st)
+{
+   int launches = 0;
+   if (G > 1)
+   {
+      const long long total = (long long)ncell * (G - 1);
+      dim3 grid((unsigned)((total + 127) / 128), 2);
+      planck_integrals_kernel<<<grid, 128, 0, st>>>(G, ncell, d_e_edge, d_T, d_B, d_dBdT);
+      ++launches;
+   }
+   planck_finalize_kernel<<<(ncell + 127) / 128, 128, 0, st>>>(G, ncell, d_T, d_B, d_dBdT);
+   return launches + 1;
+}
+
+int launch_group_terms(const GroupTermsArgs &a, cudaStream_t st)
+{
+   group_terms_kernel<<<1, 1024, 0, st>>>(a);
+   return 1;
+}
+
+int launch_boundary_table(int M, int G, int bc_left, int bc_right, int use_mg_equilib, double V, const double *mu,
+                          const double *B, const double *dEB, double *psi_source, double *bdry, cudaStream_t st)
+{
+   boundary_table_kernel<<<(M * G + 255) / 256, 256, 0, st>>>(M, G, bc_left, bc_right, use_mg_equilib, V, mu, B, dEB,
+                                                             psi_source, bdry);
+   return 1;
+}
+} // namespace rtk

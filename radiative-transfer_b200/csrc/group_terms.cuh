@@ -1,0 +1,28 @@
+// group_terms.cuh -- launch interface of the G-length kernels (group_terms.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+namespace rtk
+{
+struct GroupTermsArgs
+{
+   int G;
+   double T, rho;
+   const double *e_edge; // G+1
+   const double *kappa;  // G
+   const double *B;      // G   (jk units, after the Planck kernels)
+   const double *dBdT;   // G
+   double *kappa_edge;   // G+1
+   double *epf;          // G+1 scratch: E*pf(E,T) at the group edges
+   double *dEB, *dsigEdE, *dkapEB, *cor1, *cor2, *cor3, *sigma, *srcB, *de_ave; // G each
+   double *sums;         // 3: sum B, sum dBdT, sum kappa*B
+};
+
+// 12-point Gauss-Legendre rule (computed on the host in long double like the reference, rounded to fp64)
+void upload_gauss_rule(const double *pt, const double *w);
+// B,dBdT: [ncell][G]; returns the number of kernels launched
+int launch_planck(int G, int ncell, const double *d_e_edge, const double *d_T, double *d_B, double *d_dBdT, cudaStream_t st);
+int launch_group_terms(const GroupTermsArgs &a, cudaStream_t st);
+int launch_boundary_table(int M, int G, int bc_left, int bc_right, int use_mg_equilib, double V, const double *mu,
+                          const double *B, const double *dEB, double *psi_source, double *bdry, cudaStream_t st);
+} // namespace rtk

@@ -1,0 +1,865 @@
+// rt_capi.cu -- host side of librt_cuda.so: the C ABI declared in include/rt_cuda.h.
+//
+// Owns the device tables, the four rotating time-level buffers, the look-back state and the stage
+// schedule of rt::Solver::solve (reference src/solver.cpp:590-823).  No CPU compute path exists:
+// every numerical result comes from the kernels in group_terms.cu, sweep_kernel.cu and moments.cu.
+#include "../../include/rt_cuda.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "group_terms.cuh"
+#include "moments.cuh"
+#include "rt_common.cuh"
+#include "sweep_kernel.cuh"
+
+using namespace rtk;
+
+static thread_local std::string g_err;
+
+static int fail(const char *fmt, ...)
+{
+   char buf[1024];
+   va_list ap;
+   va_start(ap, fmt);
+   vsnprintf(buf, sizeof buf, fmt, ap);
+   va_end(ap);
+   g_err = buf;
+   return 1;
+}
+
+#define CK(call)                                                                                              \
+   do                                                                                                         \
+   {                                                                                                          \
+      cudaError_t e_ = (call);                                                                                \
+      if (e_ != cudaSuccess) return fail("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+   } while (0)
+
+struct EventPair
+{
+   cudaEvent_t a, b;
+   int kind; // 0..2 sweep kinds, 3 moments
+};
+
+struct rt_solver
+{
+   rt_params p;
+   std::vector<double> mu, wt, e_edge, kappa, psi_source;
+   int num_sms = 0;
+   cudaStream_t st = nullptr, copy_st = nullptr;
+   // G-length tables
+   double *d_mu = nullptr, *d_wt = nullptr, *d_e_edge = nullptr, *d_kappa = nullptr, *d_T = nullptr;
+   double *d_B = nullptr, *d_dBdT = nullptr, *d_kappa_edge = nullptr, *d_epf = nullptr, *d_dEB = nullptr;
+   double *d_dsig = nullptr, *d_dkap = nullptr, *d_cor1 = nullptr, *d_cor2 = nullptr, *d_cor3 = nullptr;
+   double *d_sigma = nullptr, *d_srcB = nullptr, *d_de_ave = nullptr, *d_sums = nullptr;
+   double *d_psi_source = nullptr, *d_bdry = nullptr;
+   double sums[3] = {0, 0, 0};
+   // batching
+   int Gl = 0, Gb = 0, n_batches = 0, Np = 0, tiles_per_row = 0;
+   size_t buf_elems = 0; // double2 elements per time-level buffer
+   double2 *E[4] = {nullptr, nullptr, nullptr, nullptr};
+   int i_ends = 0, i_prev = -1, i_half_neg = -1, i_half_pos = -1;
+   int batch_start = 0, batch_groups = 0; // local group range of the batch currently on the device
+   int stages_done = 0;
+   // look-back state
+   double *d_tile_agg = nullptr, *d_tile_incl = nullptr;
+   unsigned *d_tile_flag = nullptr;
+   unsigned long long *d_ticket = nullptr;
+   unsigned long long ticket_base = 0;
+   unsigned epoch = 0;
+   int last_grid = 0;
+   // results retained across batches (group-major [gl][c]) and per-group diagnostics
+   double *d_phi = nullptr, *d_phip = nullptr, *d_F = nullptr;
+   double *d_balance = nullptr, *d_left = nullptr, *d_right = nullptr;
+   bool results_valid = false;
+   double *d_stage = nullptr; // staging for layout conversion
+   size_t stage_elems = 0;
+   // per-step output
+   double *step_phi_host = nullptr;
+   int step_group_major = 1;
+   double *d_step_phi[2] = {nullptr, nullptr};
+   cudaEvent_t step_ev[2] = {nullptr, nullptr};
+   int step_parity = 0;
+   // timing
+   rt_timing tm;
+   std::vector<EventPair> ev_pool;
+   size_t ev_used = 0;
+   bool timing_on = true;
+   bool lookback_walk = false; // RT_CUDA_LOOKBACK=walk: aggregate walk-back (faster with very few rows, not bitwise reproducible)
+};
+
+// ---------------------------------------------------------------------------------------------
+extern "C" const char *rt_last_error(void) { return g_err.c_str(); }
+extern "C" int rt_abi_version(void) { return RT_ABI_VERSION; }
+
+// 12-point Gauss-Legendre rule computed like the reference's Planck::gauss_quad_setup
+// (src/Planck.cpp:231-337): long double Newton iteration with the derivative scaled by 13/12 (the loop
+// counter after the recurrence), weights renormalised to sum to 2.  Rounded to fp64 for the device.
+static void gauss12_host(double *pt, double *w)
+{
+   const int order = 12;
+   long double lp[order], lw[order], wsum = 0;
+   for (int i = 0; i < (order + 1) / 2; i++)
+   {
+      long double mu = std::cos((double)3.1415926546 * (i + 0.75) / (order + 0.5)), old_mu, pj = 0, pjm1 = 0, pjm2 = 0, dp = 0;
+      bool conv = false;
+      while (!conv)
+      {
+         pjm1 = 0;
+         pj = 1;
+         int j;
+         for (j = 1; j <= order; j++)
+         {
+            pjm2 = pjm1;
+            pjm1 = pj;
+            pj = ((2 * j - 1) * mu * pjm1 - (j - 1) * pjm2) / j;
+         }
+         dp = j * (mu * pj - pjm1) / (mu * mu - 1);
+         old_mu = mu;
+         mu = old_mu - pj / dp;
+         if (fabsl(mu - old_mu) < 2.220446049250313e-16L) conv = true;
+      }
+      lp[i] = -mu;
+      lp[order - 1 - i] = mu;
+      lw[i] = 1 / ((1 - mu * mu) * dp * dp);
+      lw[order - 1 - i] = lw[i];
+      wsum += lw[i] + lw[order - 1 - i];
+   }
+   for (int i = 0; i < order; i++)
+   {
+      pt[i] = (double)lp[i];
+      w[i] = (double)(lw[i] * 2 / wsum);
+   }
+}
+
+template <typename T>
+static int dalloc(T **p, size_t n)
+{
+   CK(cudaMalloc((void **)p, std::max<size_t>(n, 1) * sizeof(T)));
+   return 0;
+}
+
+static int upload(rt_solver *s, double *dst, const double *src, size_t n)
+{
+   CK(cudaMemcpyAsync(dst, src, n * sizeof(double), cudaMemcpyHostToDevice, s->st));
+   s->tm.h2d_bytes += (long long)(n * sizeof(double));
+   return 0;
+}
+
+static int download(rt_solver *s, double *dst, const double *src, size_t n)
+{
+   CK(cudaMemcpyAsync(dst, src, n * sizeof(double), cudaMemcpyDeviceToHost, s->st));
+   CK(cudaStreamSynchronize(s->st));
+   s->tm.d2h_bytes += (long long)(n * sizeof(double));
+   return 0;
+}
+
+static int flush_events(rt_solver *s)
+{
+   if (s->ev_used == 0) return 0;
+   CK(cudaStreamSynchronize(s->st));
+   for (size_t k = 0; k < s->ev_used; ++k)
+   {
+      float ms = 0.f;
+      CK(cudaEventElapsedTime(&ms, s->ev_pool[k].a, s->ev_pool[k].b));
+      if (s->ev_pool[k].kind < 3) s->tm.sweep_ms[s->ev_pool[k].kind] += ms;
+      else s->tm.moments_ms += ms;
+   }
+   s->ev_used = 0;
+   return 0;
+}
+
+static int event_begin(rt_solver *s, int kind, EventPair **out)
+{
+   *out = nullptr;
+   if (!s->timing_on) return 0;
+   if (s->ev_used == s->ev_pool.size())
+   {
+      if (s->ev_pool.size() >= 2048) { if (flush_events(s)) return 1; }
+      else
+      {
+         EventPair ep;
+         CK(cudaEventCreate(&ep.a));
+         CK(cudaEventCreate(&ep.b));
+         ep.kind = 0;
+         s->ev_pool.push_back(ep);
+      }
+   }
+   EventPair *ep = &s->ev_pool[s->ev_used++];
+   ep->kind = kind;
+   CK(cudaEventRecord(ep->a, s->st));
+   *out = ep;
+   return 0;
+}
+
+static int event_end(rt_solver *s, EventPair *ep)
+{
+   if (ep) CK(cudaEventRecord(ep->b, s->st));
+   return 0;
+}
+
+// Planck integrals, edge stencils, correction terms, validation sums, boundary table -- all on the device.
+static int compute_group_tables(rt_solver *s)
+{
+   const rt_params &p = s->p;
+   s->tm.kernel_launches += launch_planck(p.G, 1, s->d_e_edge, s->d_T, s->d_B, s->d_dBdT, s->st);
+   GroupTermsArgs a;
+   a.G = p.G; a.T = p.T; a.rho = p.rho;
+   a.e_edge = s->d_e_edge; a.kappa = s->d_kappa; a.B = s->d_B; a.dBdT = s->d_dBdT;
+   a.kappa_edge = s->d_kappa_edge; a.epf = s->d_epf; a.dEB = s->d_dEB; a.dsigEdE = s->d_dsig; a.dkapEB = s->d_dkap;
+   a.cor1 = s->d_cor1; a.cor2 = s->d_cor2; a.cor3 = s->d_cor3; a.sigma = s->d_sigma; a.srcB = s->d_srcB;
+   a.de_ave = s->d_de_ave; a.sums = s->d_sums;
+   s->tm.kernel_launches += launch_group_terms(a, s->st);
+   s->tm.kernel_launches += launch_boundary_table(p.M, p.G, p.bc_left, p.bc_right, p.use_mg_equilib, p.V, s->d_mu, s->d_B,
+                                                  s->d_dEB, s->d_psi_source, s->d_bdry, s->st);
+   CK(cudaGetLastError());
+   if (download(s, s->sums, s->d_sums, 3)) return 1;
+   return 0;
+}
+
+static bool sums_ok(const rt_solver *s)
+{
+   const double ac = RAD_A * C_LIGHT, T = s->p.T;
+   const double acT4 = ac * std::pow(T, 4), dacT4 = 4.0 * ac * std::pow(T, 3);
+   if (std::fabs(acT4 - s->sums[0]) > VALIDATION_TOL || std::fabs(dacT4 - s->sums[1]) > VALIDATION_TOL) return false;
+   if (std::fabs(s->sums[2] - s->p.kappa_grey * acT4) > VALIDATION_TOL) return false;
+   return true;
+}
+
+// psi = ends = B_g for the batch starting at local group `start` (solver.cpp:166-181)
+static int load_batch(rt_solver *s, int start)
+{
+   s->batch_start = start;
+   s->batch_groups = std::min(s->Gb, s->Gl - start);
+   s->i_ends = 0;
+   s->i_prev = s->i_half_neg = s->i_half_pos = -1;
+   s->stages_done = 0;
+   launch_init_state(s->E[0], s->d_B, s->p.M, s->p.N, s->Np, s->p.group_begin + start, s->batch_groups, s->st);
+   s->tm.kernel_launches += 1;
+   CK(cudaGetLastError());
+   return 0;
+}
+
+extern "C" int rt_destroy(rt_solver *s)
+{
+   if (!s) return 0;
+   cudaSetDevice(s->p.device);
+   if (s->st) cudaStreamSynchronize(s->st);
+   double *tabs[] = {s->d_mu, s->d_wt, s->d_e_edge, s->d_kappa, s->d_T, s->d_B, s->d_dBdT, s->d_kappa_edge, s->d_epf,
+                     s->d_dEB, s->d_dsig, s->d_dkap, s->d_cor1, s->d_cor2, s->d_cor3, s->d_sigma, s->d_srcB, s->d_de_ave,
+                     s->d_sums, s->d_psi_source, s->d_bdry, s->d_tile_agg, s->d_tile_incl, s->d_phi, s->d_phip, s->d_F,
+                     s->d_balance, s->d_left, s->d_right, s->d_stage, s->d_step_phi[0], s->d_step_phi[1]};
+   for (double *t : tabs) if (t) cudaFree(t);
+   for (int k = 0; k < 4; ++k) if (s->E[k]) cudaFree(s->E[k]);
+   if (s->d_tile_flag) cudaFree(s->d_tile_flag);
+   if (s->d_ticket) cudaFree(s->d_ticket);
+   for (auto &ep : s->ev_pool) { cudaEventDestroy(ep.a); cudaEventDestroy(ep.b); }
+   for (int k = 0; k < 2; ++k) if (s->step_ev[k]) cudaEventDestroy(s->step_ev[k]);
+   if (s->copy_st) cudaStreamDestroy(s->copy_st);
+   if (s->st) cudaStreamDestroy(s->st);
+   delete s;
+   return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// creation
+static int validate_params(const rt_params *p)
+{
+   if (!p) return fail("rt_create: null params");
+   if (p->M < 2 || (p->M & 1)) return fail("rt_create: M must be even and >= 2 (got %d)", p->M);
+   if (p->N < 1 || p->G < 1) return fail("rt_create: N and G must be >= 1");
+   if (p->group_begin < 0 || p->group_count < 1 || p->group_begin + p->group_count > p->G)
+      return fail("rt_create: group shard [%d,%d) outside [0,%d)", p->group_begin, p->group_begin + p->group_count, p->G);
+   if (p->ts_method < 1 || p->ts_method > 3) return fail("Incorrect timestepping method provided.");
+   if (p->bc_left < 0 || p->bc_left > 2 || p->bc_right < 0 || p->bc_right > 2) return fail("Incorrect boundary conditions provided.");
+   if (!p->mu || !p->wt || !p->e_edge || !p->kappa) return fail("rt_create: mu, wt, e_edge and kappa are required");
+   for (int i = 0; i < p->M; ++i)
+      if (p->mu[i] == 0.0 || (i < p->M / 2) != (p->mu[i] < 0.0)) return fail("mu should not be 0 and must be ascending with M/2 negative nodes");
+   if (p->max_timesteps < 0) return fail("rt_create: max_timesteps < 0");
+   return 0;
+}
+
+extern "C" int rt_create(const rt_params *p, rt_solver **out)
+{
+   if (!out) return fail("rt_create: null out");
+   *out = nullptr;
+   if (validate_params(p)) return 1;
+   int ndev = 0;
+   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+      return fail("rt_create: no CUDA device available (librt_cuda has no CPU fallback)");
+   if (p->device < 0 || p->device >= ndev) return fail("rt_create: device %d not in [0,%d)", p->device, ndev);
+   CK(cudaSetDevice(p->device));
+   cudaDeviceProp prop;
+   CK(cudaGetDeviceProperties(&prop, p->device));
+   if (prop.major < 10) return fail("rt_create: device %d is sm_%d%d; librt_cuda is built for sm_100a only", p->device, prop.major, prop.minor);
+
+   rt_solver *s = new rt_solver();
+   std::memset(&s->tm, 0, sizeof s->tm);
+   s->p = *p;
+   const int M = p->M, N = p->N, G = p->G;
+   s->mu.assign(p->mu, p->mu + M);
+   s->wt.assign(p->wt, p->wt + M);
+   s->e_edge.assign(p->e_edge, p->e_edge + G + 1);
+   s->kappa.assign(p->kappa, p->kappa + G);
+   s->psi_source.assign((size_t)M * G, 0.0); // zero when absent
+   if (p->psi_source) std::copy(p->psi_source, p->psi_source + (size_t)M * G, s->psi_source.begin());
+   s->p.mu = s->mu.data(); s->p.wt = s->wt.data(); s->p.e_edge = s->e_edge.data(); s->p.kappa = s->kappa.data();
+   s->p.psi_source = s->psi_source.data();
+   s->num_sms = prop.multiProcessorCount;
+   s->Gl = p->group_count;
+   s->Np = (N + 7) & ~7;
+   s->tiles_per_row = (N + TILE_CELLS - 1) / TILE_CELLS;
+   const char *tenv = getenv("RT_CUDA_TIMING");
+   s->timing_on = !(tenv && tenv[0] == '0');
+   const char *lenv = getenv("RT_CUDA_LOOKBACK");
+   s->lookback_walk = lenv && std::strcmp(lenv, "walk") == 0;
+
+#define CKD(x) do { if (x) { rt_destroy(s); return 1; } } while (0)
+#define CKC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { fail("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); rt_destroy(s); return 1; } } while (0)
+   CKC(cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking));
+   CKC(cudaStreamCreateWithFlags(&s->copy_st, cudaStreamNonBlocking));
+   CKD(dalloc(&s->d_mu, M)); CKD(dalloc(&s->d_wt, M)); CKD(dalloc(&s->d_e_edge, G + 1)); CKD(dalloc(&s->d_kappa, G));
+   CKD(dalloc(&s->d_T, 1)); CKD(dalloc(&s->d_B, G)); CKD(dalloc(&s->d_dBdT, G)); CKD(dalloc(&s->d_kappa_edge, G + 1));
+   CKD(dalloc(&s->d_epf, G + 1)); CKD(dalloc(&s->d_dEB, G)); CKD(dalloc(&s->d_dsig, G)); CKD(dalloc(&s->d_dkap, G));
+   CKD(dalloc(&s->d_cor1, G)); CKD(dalloc(&s->d_cor2, G)); CKD(dalloc(&s->d_cor3, G)); CKD(dalloc(&s->d_sigma, G));
+   CKD(dalloc(&s->d_srcB, G)); CKD(dalloc(&s->d_de_ave, G)); CKD(dalloc(&s->d_sums, 3));
+   CKD(dalloc(&s->d_psi_source, (size_t)M * G)); CKD(dalloc(&s->d_bdry, (size_t)M * G));
+   CKD(dalloc(&s->d_balance, s->Gl)); CKD(dalloc(&s->d_left, s->Gl)); CKD(dalloc(&s->d_right, s->Gl));
+   CKD(dalloc(&s->d_ticket, 1));
+   CKC(cudaMemsetAsync(s->d_ticket, 0, sizeof(unsigned long long), s->st));
+   CKC(cudaMemsetAsync(s->d_B, 0, G * sizeof(double), s->st));
+   CKC(cudaMemsetAsync(s->d_dBdT, 0, G * sizeof(double), s->st));
+   CKD(upload(s, s->d_mu, s->mu.data(), M)); CKD(upload(s, s->d_wt, s->wt.data(), M));
+   CKD(upload(s, s->d_e_edge, s->e_edge.data(), G + 1)); CKD(upload(s, s->d_kappa, s->kappa.data(), G));
+   CKD(upload(s, s->d_T, &s->p.T, 1)); CKD(upload(s, s->d_psi_source, s->psi_source.data(), (size_t)M * G));
+   {
+      double pt[12], w[12];
+      gauss12_host(pt, w);
+      upload_gauss_rule(pt, w);
+   }
+
+   // ---- memory plan: 4 time-level buffers of (u,v) per unknown + look-back state
+   size_t free_b = 0, total_b = 0;
+   CKC(cudaMemGetInfo(&free_b, &total_b));
+   const size_t per_group = (size_t)4 * M * s->Np * sizeof(double2) + (size_t)M * s->tiles_per_row * 20;
+   const size_t reserve = (size_t)1 << 30; // results staging, allocator slack
+   int gb = p->groups_per_batch;
+   if (gb <= 0)
+   {
+      const size_t usable = free_b > reserve ? free_b - reserve : free_b / 2;
+      size_t fit = usable / per_group;
+      // when the groups do not all fit, phi/phi_plus/F of every owned group are retained on the device as well
+      if (fit < (size_t)s->Gl)
+      {
+         const size_t keep = (size_t)3 * s->Gl * N * sizeof(double);
+         fit = usable > keep ? (usable - keep) / per_group : 0;
+      }
+      gb = (int)std::min<size_t>(fit, (size_t)s->Gl);
+      if (gb < 1) { fail("rt_create: not even one group (%zu bytes) fits in %zu free bytes", per_group, free_b); rt_destroy(s); return 1; }
+   }
+   gb = std::min(gb, s->Gl);
+   s->Gb = gb;
+   s->n_batches = (s->Gl + gb - 1) / gb;
+   s->buf_elems = (size_t)gb * M * s->Np;
+   for (int k = 0; k < 4; ++k) CKD(dalloc(&s->E[k], s->buf_elems));
+   const size_t ntiles = (size_t)gb * M * s->tiles_per_row;
+   CKD(dalloc(&s->d_tile_agg, ntiles)); CKD(dalloc(&s->d_tile_incl, ntiles)); CKD(dalloc(&s->d_tile_flag, ntiles));
+   CKC(cudaMemsetAsync(s->d_tile_flag, 0, ntiles * sizeof(unsigned), s->st));
+   if (s->n_batches > 1)
+   {
+      CKD(dalloc(&s->d_phi, (size_t)s->Gl * N)); CKD(dalloc(&s->d_phip, (size_t)s->Gl * N)); CKD(dalloc(&s->d_F, (size_t)s->Gl * N));
+   }
+   CKD(compute_group_tables(s));
+   CKD(load_batch(s, 0));
+   CKC(cudaStreamSynchronize(s->st));
+#undef CKD
+#undef CKC
+   *out = s;
+   return 0;
+}
+
+extern "C" int rt_get_plan(const rt_solver *s, rt_plan *plan)
+{
+   if (!s || !plan) return fail("rt_get_plan: null argument");
+   plan->groups_per_batch = s->Gb;
+   plan->n_batches = s->n_batches;
+   plan->resident = s->n_batches == 1;
+   plan->tile_cells = TILE_CELLS;
+   plan->tiles_per_row = s->tiles_per_row;
+   plan->sweep_grid = s->last_grid;
+   plan->sweep_block = SWEEP_THREADS;
+   plan->bytes_per_group = (size_t)4 * s->p.M * s->Np * sizeof(double2);
+   plan->state_bytes = 4 * s->buf_elems * sizeof(double2);
+   cudaSetDevice(s->p.device);
+   cudaMemGetInfo(&plan->free_bytes, &plan->total_bytes);
+   return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// stage schedule (solver.cpp:606-820)
+static int pick_free(int a, int b, int c, int d)
+{
+   for (int k = 0; k < 4; ++k)
+      if (k != a && k != b && k != c && k != d) return k;
+   return -1;
+}
+
+static int total_stages(const rt_solver *s) { return s->p.max_timesteps * (s->p.ts_method == 3 ? 4 : 1); }
+
+// one stage sweep of the batch currently on the device
+static int run_one_stage(rt_solver *s)
+{
+   const rt_params &p = s->p;
+   const int it = s->stages_done;
+   int kind, out;
+   double tau;
+   const double2 *x1n, *x1p, *x2 = nullptr, *xc = nullptr;
+   const bool corr = p.use_correction && p.V != 0.0; // V == 0 makes total_correction exactly zero
+   if (p.ts_method == 1)
+   {
+      kind = KIND_BE; tau = p.dt;
+      out = pick_free(s->i_ends, -1, -1, -1);
+      x1n = x1p = s->E[s->i_ends];
+      s->i_prev = s->i_ends; // prev_ends = ends (solver.cpp:624), by aliasing instead of copying
+   }
+   else if (p.ts_method == 2)
+   {
+      kind = KIND_CN; tau = p.dt;
+      out = pick_free(s->i_ends, -1, -1, -1);
+      x1n = x1p = x2 = s->E[s->i_ends];
+      s->i_prev = s->i_ends;
+   }
+   else
+   {
+      tau = p.dt / 2.;
+      switch (it % 4)
+      {
+      case 0: // BE predictor; prev_ends = ends
+         kind = KIND_BE;
+         out = pick_free(s->i_ends, s->i_half_neg, s->i_half_pos, -1);
+         x1n = x1p = s->E[s->i_ends];
+         s->i_prev = s->i_ends;
+         break;
+      case 1: // CN corrector; afterwards half_ends = CN result for mu<0 rows, stage-0 result for mu>0 rows
+         kind = KIND_CN;
+         out = pick_free(s->i_ends, s->i_prev, -1, -1);
+         x1n = x1p = s->E[s->i_ends];
+         x2 = s->E[s->i_prev];
+         s->i_half_pos = s->i_ends;
+         s->i_half_neg = out;
+         break;
+      case 2: // second BE predictor
+         kind = KIND_BE;
+         out = pick_free(s->i_ends, s->i_prev, s->i_half_neg, s->i_half_pos);
+         x1n = x1p = s->E[s->i_ends];
+         break;
+      default: // BDF corrector, written in place over the stage-2 result (only read for the correction source, same cell)
+         kind = KIND_BDF;
+         out = s->i_ends;
+         x1n = s->E[s->i_half_neg];
+         x1p = s->E[s->i_half_pos];
+         x2 = s->E[s->i_prev];
+         xc = s->E[s->i_ends];
+         break;
+      }
+   }
+   if (out < 0) return fail("internal: no free time-level buffer");
+
+   SweepArgs a;
+   a.x1[0] = x1n; a.x1[1] = x1p;
+   a.x2[0] = a.x2[1] = x2;
+   a.xc[0] = a.xc[1] = xc;
+   a.out[0] = a.out[1] = s->E[out];
+   a.sigma = s->d_sigma; a.srcB = s->d_srcB; a.cor1 = s->d_cor1; a.cor2 = s->d_cor2; a.cor3 = s->d_cor3;
+   a.mu = s->d_mu; a.bdry = s->d_bdry;
+   a.tile_agg = s->d_tile_agg; a.tile_incl = s->d_tile_incl; a.tile_flag = s->d_tile_flag;
+   a.ticket = s->d_ticket; a.ticket_base = s->ticket_base;
+   a.epoch = ++s->epoch;
+   a.M = p.M; a.N = p.N; a.Np = s->Np; a.G0 = p.group_begin + s->batch_start;
+   a.rows = s->batch_groups * p.M;
+   a.tiles_per_row = s->tiles_per_row;
+   a.reflective_left = (p.bc_left == 2) ? 1 : 0;
+   a.n_chains = a.reflective_left ? a.rows / 2 : a.rows;
+   a.tiles_per_chain = a.reflective_left ? 2 * s->tiles_per_row : s->tiles_per_row;
+   a.lookback_walk = s->lookback_walk ? 1 : 0;
+   a.dx = p.dx; a.tau = tau; a.dt = p.dt; a.beta = p.V / C_LIGHT;
+
+   EventPair *ep;
+   if (event_begin(s, kind, &ep)) return 1;
+   int grid = 0;
+   CK(launch_sweep(kind, corr, a, s->num_sms, s->st, &grid));
+   if (event_end(s, ep)) return 1;
+   s->ticket_base += (unsigned long long)a.n_chains * a.tiles_per_chain + (unsigned long long)grid;
+   s->last_grid = grid;
+   s->i_ends = out;
+   s->stages_done++;
+   s->tm.sweep_launches[kind]++;
+   s->tm.kernel_launches++;
+   s->tm.stages++;
+   s->tm.unknown_stages += (long long)a.rows * p.N;
+   s->results_valid = false;
+   return 0;
+}
+
+static int step_output(rt_solver *s);
+static int finish_batch(rt_solver *s);
+
+static int run_stages(rt_solver *s, int n)
+{
+   const int per_step = s->p.ts_method == 3 ? 4 : 1;
+   for (int k = 0; k < n; ++k)
+   {
+      if (run_one_stage(s)) return 1;
+      if (s->step_phi_host && s->stages_done % per_step == 0)
+         if (step_output(s)) return 1;
+   }
+   return 0;
+}
+
+extern "C" int rt_run_stages(rt_solver *s, int n)
+{
+   if (!s) return fail("rt_run_stages: null handle");
+   if (s->n_batches != 1) return fail("rt_run_stages: only available when all owned groups are resident (use rt_solve)");
+   CK(cudaSetDevice(s->p.device));
+   if (run_stages(s, n)) return 1;
+   if (flush_events(s)) return 1;
+   CK(cudaStreamSynchronize(s->st));
+   if (s->step_phi_host) CK(cudaStreamSynchronize(s->copy_st));
+   return 0;
+}
+
+extern "C" int rt_solve(rt_solver *s)
+{
+   if (!s) return fail("rt_solve: null handle");
+   CK(cudaSetDevice(s->p.device));
+   if (s->p.validate && !sums_ok(s))
+      return fail("Invalid Correction Terms: sum B = %.17g, sum dBdT = %.17g, sum kappa*B = %.17g", s->sums[0], s->sums[1], s->sums[2]);
+   if (s->n_batches == 1)
+   {
+      if (run_stages(s, total_stages(s) - s->stages_done)) return 1;
+   }
+   else
+   {
+      for (int b = 0; b < s->n_batches; ++b)
+      {
+         if (load_batch(s, b * s->Gb)) return 1;
+         if (run_stages(s, total_stages(s))) return 1;
+         if (finish_batch(s)) return 1;
+      }
+      s->results_valid = true;
+   }
+   if (flush_events(s)) return 1;
+   CK(cudaStreamSynchronize(s->st));
+   if (s->step_phi_host) CK(cudaStreamSynchronize(s->copy_st));
+   return 0;
+}
+
+extern "C" int rt_stages_done(const rt_solver *s, int *n) { if (!s || !n) return fail("null argument"); *n = s->stages_done; return 0; }
+extern "C" int rt_total_stages(const rt_solver *s, int *n) { if (!s || !n) return fail("null argument"); *n = total_stages(s); return 0; }
+
+extern "C" int rt_reset(rt_solver *s)
+{
+   if (!s) return fail("rt_reset: null handle");
+   CK(cudaSetDevice(s->p.device));
+   if (load_batch(s, 0)) return 1;
+   s->results_valid = false;
+   CK(cudaStreamSynchronize(s->st));
+   return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// results
+static int ensure_result_arrays(rt_solver *s)
+{
+   const size_t n = (size_t)s->Gl * s->p.N;
+   if (!s->d_phi) { if (dalloc(&s->d_phi, n)) return 1; }
+   if (!s->d_phip) { if (dalloc(&s->d_phip, n)) return 1; }
+   if (!s->d_F) { if (dalloc(&s->d_F, n)) return 1; }
+   return 0;
+}
+
+// moments and diagnostics of the batch on the device into the retained result arrays
+static int finish_batch(rt_solver *s)
+{
+   const rt_params &p = s->p;
+   if (ensure_result_arrays(s)) return 1;
+   const size_t off = (size_t)s->batch_start * p.N;
+   EventPair *ep;
+   if (event_begin(s, 3, &ep)) return 1;
+   launch_moments(s->E[s->i_ends], s->d_mu, s->d_wt, p.M, p.N, s->Np, s->batch_groups, s->d_phi + off, s->d_phip + off,
+                  s->d_F + off, s->st);
+   launch_diagnostics(s->E[s->i_ends], s->d_mu, s->d_wt, s->d_sigma, s->d_de_ave, p.M, p.N, s->Np,
+                      p.group_begin + s->batch_start, s->batch_groups, p.dx, p.T, s->d_balance + s->batch_start,
+                      s->d_left + s->batch_start, s->d_right + s->batch_start, s->st);
+   if (event_end(s, ep)) return 1;
+   s->tm.kernel_launches += 2;
+   CK(cudaGetLastError());
+   return 0;
+}
+
+static int ensure_results(rt_solver *s)
+{
+   if (s->results_valid) return 0;
+   if (s->n_batches != 1) return fail("results are only available after rt_solve in batched mode");
+   if (finish_batch(s)) return 1;
+   s->results_valid = true;
+   return 0;
+}
+
+// group-major device array [Gl][N] -> host array in reference order g + Gl*c, through a bounded staging buffer
+static int download_reference_order(rt_solver *s, const double *d_src, double *host)
+{
+   const int Gl = s->Gl, N = s->p.N;
+   const size_t budget = (size_t)32 << 20; // doubles (256 MB)
+   int chunk = (int)std::min<size_t>((size_t)N, std::max<size_t>(32, budget / (size_t)Gl));
+   const size_t need = (size_t)chunk * Gl;
+   if (s->stage_elems < need)
+   {
+      if (s->d_stage) CK(cudaFree(s->d_stage));
+      s->d_stage = nullptr;
+      if (dalloc(&s->d_stage, need)) return 1;
+      s->stage_elems = need;
+   }
+   for (int c0 = 0; c0 < N; c0 += chunk)
+   {
+      const int nc = std::min(chunk, N - c0);
+      launch_transpose_gn(d_src, s->d_stage, Gl, N, c0, nc, s->st);
+      s->tm.kernel_launches++;
+      CK(cudaGetLastError());
+      if (download(s, host + (size_t)Gl * c0, s->d_stage, (size_t)Gl * nc)) return 1;
+   }
+   return 0;
+}
+
+extern "C" int rt_moments(rt_solver *s, double *phi, double *phi_plus, double *F)
+{
+   if (!s) return fail("rt_moments: null handle");
+   CK(cudaSetDevice(s->p.device));
+   if (ensure_results(s)) return 1;
+   if (phi && download_reference_order(s, s->d_phi, phi)) return 1;
+   if (phi_plus && download_reference_order(s, s->d_phip, phi_plus)) return 1;
+   if (F && download_reference_order(s, s->d_F, F)) return 1;
+   return flush_events(s);
+}
+
+extern "C" int rt_moments_group_major(rt_solver *s, double *phi, double *phi_plus, double *F)
+{
+   if (!s) return fail("rt_moments_group_major: null handle");
+   CK(cudaSetDevice(s->p.device));
+   if (ensure_results(s)) return 1;
+   const size_t n = (size_t)s->Gl * s->p.N;
+   if (phi && download(s, phi, s->d_phi, n)) return 1;
+   if (phi_plus && download(s, phi_plus, s->d_phip, n)) return 1;
+   if (F && download(s, F, s->d_F, n)) return 1;
+   return flush_events(s);
+}
+
+extern "C" int rt_balance(rt_solver *s, double *balance)
+{
+   if (!s || !balance) return fail("rt_balance: null argument");
+   CK(cudaSetDevice(s->p.device));
+   if (ensure_results(s)) return 1;
+   return download(s, balance, s->d_balance, s->Gl);
+}
+
+extern "C" int rt_group_ends(rt_solver *s, double *left, double *right)
+{
+   if (!s) return fail("rt_group_ends: null handle");
+   CK(cudaSetDevice(s->p.device));
+   if (ensure_results(s)) return 1;
+   if (left && download(s, left, s->d_left, s->Gl)) return 1;
+   if (right && download(s, right, s->d_right, s->Gl)) return 1;
+   return 0;
+}
+
+static int need_resident(const rt_solver *s, const char *what)
+{
+   if (s->n_batches != 1) return fail("%s: only available when all owned groups are resident on the device", what);
+   return 0;
+}
+
+extern "C" int rt_get_psi(rt_solver *s, double *psi)
+{
+   if (!s || !psi) return fail("rt_get_psi: null argument");
+   if (need_resident(s, "rt_get_psi")) return 1;
+   CK(cudaSetDevice(s->p.device));
+   const size_t n = (size_t)s->p.M * s->Gl * s->p.N;
+   double *d_tmp = nullptr;
+   if (dalloc(&d_tmp, n)) return 1;
+   launch_export_psi(s->E[s->i_ends], d_tmp, s->p.M, s->p.N, s->Np, s->Gl, s->st);
+   s->tm.kernel_launches++;
+   int rc = download(s, psi, d_tmp, n);
+   cudaFree(d_tmp);
+   return rc;
+}
+
+extern "C" int rt_get_ends(rt_solver *s, int which, double *ends)
+{
+   if (!s || !ends) return fail("rt_get_ends: null argument");
+   if (need_resident(s, "rt_get_ends")) return 1;
+   CK(cudaSetDevice(s->p.device));
+   const size_t n = (size_t)2 * s->p.M * s->Gl * s->p.N;
+   int ineg, ipos;
+   if (which == 0) ineg = ipos = s->i_ends;
+   else if (which == 1) ineg = ipos = s->i_prev;
+   else if (which == 2) { ineg = s->i_half_neg; ipos = s->i_half_pos; }
+   else return fail("rt_get_ends: which must be 0, 1 or 2");
+   if (ineg < 0 || ipos < 0) { std::fill(ends, ends + n, 0.0); return 0; } // never assigned yet: zero (like a fresh resize in the oracle)
+   double *d_tmp = nullptr;
+   if (dalloc(&d_tmp, n)) return 1;
+   launch_export_ends(s->E[ineg], s->E[ipos], d_tmp, s->p.M, s->p.N, s->Np, s->Gl, s->st);
+   s->tm.kernel_launches++;
+   int rc = download(s, ends, d_tmp, n);
+   cudaFree(d_tmp);
+   return rc;
+}
+
+extern "C" int rt_get_group_terms(rt_solver *s, double *B, double *dBdT, double *dEB, double *dsigEdE, double *dkapEB,
+                                  double *kappa_edge)
+{
+   if (!s) return fail("rt_get_group_terms: null handle");
+   CK(cudaSetDevice(s->p.device));
+   const int G = s->p.G;
+   if (B && download(s, B, s->d_B, G)) return 1;
+   if (dBdT && download(s, dBdT, s->d_dBdT, G)) return 1;
+   if (dEB && download(s, dEB, s->d_dEB, G)) return 1;
+   if (dsigEdE && download(s, dsigEdE, s->d_dsig, G)) return 1;
+   if (dkapEB && download(s, dkapEB, s->d_dkap, G)) return 1;
+   if (kappa_edge && download(s, kappa_edge, s->d_kappa_edge, G + 1)) return 1;
+   return 0;
+}
+
+extern "C" int rt_get_psi_source(rt_solver *s, double *psi_source)
+{
+   if (!s || !psi_source) return fail("rt_get_psi_source: null argument");
+   CK(cudaSetDevice(s->p.device));
+   return download(s, psi_source, s->d_psi_source, (size_t)s->p.M * s->p.G);
+}
+
+extern "C" int rt_validate(rt_solver *s, double *sums3, int *ok)
+{
+   if (!s) return fail("rt_validate: null handle");
+   if (sums3) { sums3[0] = s->sums[0]; sums3[1] = s->sums[1]; sums3[2] = s->sums[2]; }
+   if (ok) *ok = sums_ok(s) ? 1 : 0;
+   return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// per-step output: phi of the step just completed -> host, overlapped with the next step's sweeps
+extern "C" int rt_set_step_output(rt_solver *s, double *phi_host, int group_major)
+{
+   if (!s) return fail("rt_set_step_output: null handle");
+   CK(cudaSetDevice(s->p.device));
+   if (phi_host && !group_major && s->n_batches != 1)
+      return fail("rt_set_step_output: reference-order output needs all owned groups resident; use group_major=1");
+   s->step_phi_host = phi_host;
+   s->step_group_major = group_major;
+   if (phi_host)
+   {
+      const size_t n = (size_t)s->Gb * s->p.N;
+      for (int k = 0; k < 2; ++k)
+      {
+         if (!s->d_step_phi[k]) { if (dalloc(&s->d_step_phi[k], n)) return 1; }
+         if (!s->step_ev[k]) CK(cudaEventCreateWithFlags(&s->step_ev[k], cudaEventDisableTiming));
+      }
+   }
+   return 0;
+}
+
+static int step_output(rt_solver *s)
+{
+   const rt_params &p = s->p;
+   const size_t n = (size_t)s->batch_groups * p.N;
+   if (s->step_group_major)
+   {
+      const int k = s->step_parity;
+      s->step_parity ^= 1;
+      // the copy that last used this staging buffer must have finished before it is overwritten
+      CK(cudaStreamWaitEvent(s->st, s->step_ev[k], 0));
+      EventPair *ep;
+      if (event_begin(s, 3, &ep)) return 1;
+      launch_moments(s->E[s->i_ends], s->d_mu, s->d_wt, p.M, p.N, s->Np, s->batch_groups, s->d_step_phi[k], nullptr, nullptr, s->st);
+      if (event_end(s, ep)) return 1;
+      s->tm.kernel_launches++;
+      cudaEvent_t done;
+      CK(cudaEventCreateWithFlags(&done, cudaEventDisableTiming));
+      CK(cudaEventRecord(done, s->st));
+      CK(cudaStreamWaitEvent(s->copy_st, done, 0));
+      CK(cudaEventDestroy(done));
+      CK(cudaMemcpyAsync(s->step_phi_host + (size_t)s->batch_start * p.N, s->d_step_phi[k], n * sizeof(double),
+                         cudaMemcpyDeviceToHost, s->copy_st));
+      CK(cudaEventRecord(s->step_ev[k], s->copy_st));
+   }
+   else
+   {
+      launch_moments(s->E[s->i_ends], s->d_mu, s->d_wt, p.M, p.N, s->Np, s->batch_groups, s->d_step_phi[0], nullptr, nullptr, s->st);
+      s->tm.kernel_launches++;
+      if (download_reference_order(s, s->d_step_phi[0], s->step_phi_host)) return 1;
+      return 0;
+   }
+   s->tm.d2h_bytes += (long long)(n * sizeof(double));
+   return 0;
+}
+
+extern "C" int rt_get_timing(const rt_solver *s, rt_timing *t)
+{
+   if (!s || !t) return fail("rt_get_timing: null argument");
+   *t = s->tm;
+   return 0;
+}
+
+extern "C" int rt_reset_timing(rt_solver *s)
+{
+   if (!s) return fail("rt_reset_timing: null handle");
+   if (flush_events(s)) return 1;
+   std::memset(&s->tm, 0, sizeof s->tm);
+   return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// standalone Planck evaluation for ncell temperatures (the per-cell extension of SURVEY 8(f).2; with
+// ncell = 1 it is exactly what rt_create runs)
+extern "C" int rt_planck_groups(int device, int G, const double *e_edge, int ncell, const double *T, double *B, double *dBdT,
+                                double *kernel_ms)
+{
+   if (!e_edge || !T || !B || !dBdT || G < 1 || ncell < 1) return fail("rt_planck_groups: bad argument");
+   int ndev = 0;
+   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail("rt_planck_groups: no CUDA device available");
+   CK(cudaSetDevice(device));
+   double *d_e = nullptr, *d_T = nullptr, *d_B = nullptr, *d_dB = nullptr;
+   const size_t n = (size_t)ncell * G;
+   int rc = 1;
+   cudaEvent_t a = nullptr, b = nullptr;
+   do
+   {
+      if (dalloc(&d_e, G + 1) || dalloc(&d_T, ncell) || dalloc(&d_B, n) || dalloc(&d_dB, n)) break;
+      if (cudaMemcpy(d_e, e_edge, (G + 1) * sizeof(double), cudaMemcpyHostToDevice) != cudaSuccess) { fail("rt_planck_groups: H2D failed"); break; }
+      if (cudaMemcpy(d_T, T, ncell * sizeof(double), cudaMemcpyHostToDevice) != cudaSuccess) { fail("rt_planck_groups: H2D failed"); break; }
+      cudaMemset(d_B, 0, n * sizeof(double));
+      cudaMemset(d_dB, 0, n * sizeof(double));
+      double pt[12], w[12];
+      gauss12_host(pt, w);
+      upload_gauss_rule(pt, w);
+      cudaEventCreate(&a);
+      cudaEventCreate(&b);
+      cudaEventRecord(a, 0);
+      launch_planck(G, ncell, d_e, d_T, d_B, d_dB, 0);
+      cudaEventRecord(b, 0);
+      if (cudaDeviceSynchronize() != cudaSuccess) { fail("rt_planck_groups: kernel failed: %s", cudaGetErrorString(cudaGetLastError())); break; }
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, a, b);
+      if (kernel_ms) *kernel_ms = ms;
+      if (cudaMemcpy(B, d_B, n * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) { fail("rt_planck_groups: D2H failed"); break; }
+      if (cudaMemcpy(dBdT, d_dB, n * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) { fail("rt_planck_groups: D2H failed"); break; }
+      rc = 0;
+   } while (0);
+   if (a) cudaEventDestroy(a);
+   if (b) cudaEventDestroy(b);
+   cudaFree(d_e); cudaFree(d_T); cudaFree(d_B); cudaFree(d_dB);
+   return rc;
+}

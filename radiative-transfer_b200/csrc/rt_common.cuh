@@ -1,0 +1,67 @@
+// rt_common.cuh -- shared definitions for the sm_100a kernels of librt_cuda.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rtk
+{
+// Physical constants, bit-identical to the reference's (include/Constants.h:9-23).
+// PI is the reference's truncated value on purpose.
+constexpr double H_KEV_SH = 4.141895e-10;
+constexpr double K_JPK = 1.601558e-25;
+constexpr double C_LIGHT = 299.79245800;
+constexpr double PI_TRUNC = 3.1415926546;
+constexpr double RAD_A = 1.3653104e-2;
+constexpr double VALIDATION_TOL = 1.e-6;
+
+// ---------------------------------------------------------------------------------------------
+// Device data layout ("group-major, sweep-ordered rows")
+//
+//   One ROW per (local group gl, direction i):  row = gl*M + i.
+//   A row holds the N cells of that (group, direction) in SWEEP ORDER -- storage index j is the
+//   j-th cell the upwind sweep visits: cell = j for mu>0, cell = N-1-j for mu<0 -- padded to a
+//   pitch of Np = round_up(N, 8) cells.
+//   Each cell is one double2 (u, v) = (inflow-side node, outflow-side node):
+//        mu>0: (u,v) = (psi_L, psi_R)        mu<0: (u,v) = (psi_R, psi_L)
+//   With this ordering the three steppers are the SAME formulas for both signs of mu with |mu| as
+//   streaming constant (mirror symmetry of the reference's mu<0 / mu>0 branches, solver.cpp:327-399).
+//   The cell average psi = (u+v)/2 is never stored (solver.cpp:352: psi is exactly 0.5*(L+R)).
+// ---------------------------------------------------------------------------------------------
+
+constexpr int SWEEP_THREADS = 256;
+constexpr int CELLS_PER_THREAD = 8;
+constexpr int TILE_CELLS = SWEEP_THREADS * CELLS_PER_THREAD; // 2048 cells = 32 KB of (u,v) per time level
+
+enum StageKind : int { KIND_BE = 0, KIND_CN = 1, KIND_BDF = 2 };
+
+// Arguments of one stage-sweep launch.
+struct SweepArgs
+{
+   // time levels, per direction sign s (0: mu<0 rows, 1: mu>0 rows) because the BDF stage reads a
+   // different `half` buffer for the two signs.  All are row-indexed with pitch Np.
+   const double2 *x1[2]; // BE/CN: ends before the stage ; BDF: half_ends
+   const double2 *x2[2]; // CN/BDF: prev_ends             ; BE: unused
+   const double2 *xc[2]; // BDF with live correction: ends before the stage (psi for the source)
+   double2 *out[2];      // ends after the stage
+   // per-group tables, indexed by GLOBAL group
+   const double *sigma;  // rho*kappa_g
+   const double *srcB;   // rho*kappa_g*B_g  (reference: rho*kappa*B, solver.cpp:337)
+   const double *cor1, *cor2, *cor3;
+   const double *mu;     // M
+   const double *bdry;   // M*G inflow values psi_source(i,g) already masked by the BC switch (0 where vacuum)
+   // look-back state
+   double *tile_agg;              // [chains*tiles_per_chain] zero-carry value at the tile's last cell
+   double *tile_incl;             // [..] true outflow at the tile's last cell
+   unsigned int *tile_flag;       // [..] epoch*2+1 = aggregate ready, epoch*2+2 = inclusive ready
+   unsigned long long *ticket;    // monotonically increasing work counter
+   unsigned long long ticket_base;
+   unsigned int epoch;
+   int M, N, Np, G0;     // G0 = global index of local group 0 of this batch
+   int rows;             // groups_in_batch * M
+   int tiles_per_row;
+   int reflective_left;  // 1: mu>0 rows take their inflow from the mirrored mu<0 row of the same stage
+   int n_chains, tiles_per_chain;
+   int lookback_walk;    // 0: deterministic (wait for the predecessor's inclusive value) ; 1: classic aggregate walk-back
+   double dx, tau, dt, beta;
+};
+} // namespace rtk

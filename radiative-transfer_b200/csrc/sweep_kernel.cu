@@ -1,0 +1,465 @@
+// sweep_kernel.cu -- the stage sweep (BE / CN / BDF) as a single-pass affine-recurrence scan.
+//
+// What the reference does (src/solver.cpp:628-811 with the steppers at 319-587): for every
+// direction i and group g it walks the N cells in upwind order and solves a 2x2 system per cell;
+// the outflow node of cell j is the inflow of cell j+1 -- a serial first-order recurrence.
+//
+// What this kernel does: in all three steppers the matrix is [[d, o], [-o, d]] with o = k/2 and k
+// the stepper's streaming constant, so with (u,v) = (inflow node, outflow node)
+//
+//        v_j = alpha * v_{j-1} + beta_j ,   alpha = (o/det) * k ,  det = d^2 + o^2
+//        u_j = gamma * v_{j-1} + U_j    ,   gamma = (d/det) * k
+//
+// where beta_j, U_j depend only on old time levels of cell j (and, for CN/BDF, on old-time-level
+// outflow nodes of cell j-1).  alpha is constant along a row (uniform rho, kappa_g, dx).  Rows are
+// cut into tiles of TILE cells; a tile is scanned by one CTA (thread-serial chunks of 8 cells,
+// warp-shuffle scan of the chunk aggregates, cross-warp combine) and tiles of a row are chained
+// with a decoupled look-back through global memory, so every cell is read once and written once.
+//
+// Work distribution: persistent CTAs draw tickets from a global counter; ticket t maps to
+// (tile position p = t / n_chains, chain = t % n_chains), i.e. all chains advance together and the
+// predecessor tile of a chain has normally been finished long before its successor starts -- the
+// look-back then costs one flag read.  With few chains (small problems) the same code degrades
+// gracefully to the classic aggregate walk-back.  Tickets are handed out in dependency order, so a
+// CTA only ever waits on a CTA that is already running: no deadlock, no cooperative launch.
+//
+// Reflective left boundary (solver.cpp:677-685): the mu>0 row takes its inflow from the SAME
+// stage's result of the mirrored mu<0 row at cell 0, i.e. from the end of that row's sweep.  The two
+// rows are simply linked into one chain of 2*tiles_per_row tiles.
+//
+// Boundary rule common to all BCs (solver.cpp:695-697): at the first cell of a row the three inflow
+// carries (n+1, n+1/2, n) all equal bdry_cond.  In scan form: effective inflow = kbc * bdry with
+// kbc = 1 (BE), 2 (CN), 6 (BDF), and no old-time-level upstream terms for that cell.
+#include "rt_common.cuh"
+#include "sweep_kernel.cuh"
+
+namespace rtk
+{
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p)
+{
+   unsigned v;
+   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+   return v;
+}
+__device__ __forceinline__ void st_release_u32(unsigned *p, unsigned v)
+{
+   asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem)
+{
+   const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all()
+{
+   asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
+// padded shared-memory slot of cell j of the tile: one 16-byte pad slot per 8 cells makes both the
+// striped (coalesced) and the blocked (8 consecutive cells per thread) access patterns conflict-free
+__device__ __forceinline__ int slot(int j) { return j + (j >> 3); }
+
+template <int THREADS>
+struct TileShape
+{
+   static constexpr int CPT = CELLS_PER_THREAD;
+   static constexpr int TILE = THREADS * CPT;
+   static constexpr int SLOTS = TILE + TILE / 8;
+   static constexpr int WARPS = THREADS / 32;
+};
+
+// Per-row stepper constants (identical formulas for both signs of mu, see rt_common.cuh).
+struct RowCoef
+{
+   double alpha, gamma, id, io; // recurrence factors and d/det, o/det
+   double qa, qb;               // q = qa + qb*(u+v) of the cell the source is evaluated at
+   double c_uu, c_uv, c_vu, c_vv;     // weights of X1 (ends or half_ends) in (ru, rv)
+   double p_uu, p_uv, p_vu, p_vv;     // weights of X2 (prev_ends) in (ru, rv)   [BDF]
+   double up1, up2;                   // weights of the upstream old-level outflow nodes X1(j-1).v, X2(j-1).v in ru
+   double kbc;                        // boundary multiplier
+};
+
+template <int KIND, bool CORR>
+__device__ __forceinline__ RowCoef make_coef(const SweepArgs &a, int g, int i)
+{
+   RowCoef c;
+   const double mu = a.mu[i], amu = fabs(mu), sig = a.sigma[g];
+   const double ctau = C_LIGHT * a.tau;
+   const double hq = 0.5 * ctau * a.dx; // 0.5*c*timestep*dx (solver.cpp:337)
+   c.qa = hq * a.srcB[g];
+   c.qb = 0.0;
+   if (CORR)
+   {
+      // total_correction = (cor1*psi + cor2)*mu*beta - cor3*mu^2*beta^2 (correction.cpp:392-394), psi = (u+v)/2
+      const double mb = mu * a.beta;
+      c.qa += hq * (a.cor2[g] * mb - a.cor3[g] * mb * mb);
+      c.qb = 0.5 * hq * a.cor1[g] * mb;
+   }
+   double k, d;
+   c.p_uu = c.p_uv = c.p_vu = c.p_vv = 0.0;
+   c.up1 = c.up2 = 0.0;
+   if (KIND == KIND_BE)
+   {
+      // solver.cpp:324-334,344-345,381-382
+      k = ctau * amu;
+      d = 0.5 * ((1.0 + ctau * sig) * a.dx + k);
+      c.c_uu = 0.5 * a.dx; c.c_uv = 0.0; c.c_vu = 0.0; c.c_vv = 0.5 * a.dx;
+      c.kbc = 1.0;
+   }
+   else if (KIND == KIND_CN)
+   {
+      // solver.cpp:411-425,435-436,469-470
+      const double t = 0.5 * ctau * sig;
+      k = 0.5 * C_LIGHT * amu * a.tau;
+      d = 0.5 * ((1.0 + t) * a.dx + k);
+      const double e1 = 0.5 * ((1.0 - t) * a.dx - k);
+      c.c_uu = e1; c.c_uv = -0.5 * k; c.c_vu = 0.5 * k; c.c_vv = e1;
+      c.up2 = k; // a * in_prev, in_prev = prev_ends(j-1).v
+      c.kbc = 2.0;
+   }
+   else
+   {
+      // solver.cpp:498-512,522-527,561-566 ; streaming constant uses the FULL dt
+      const double t = C_LIGHT * sig * a.tau / 6.0;
+      k = C_LIGHT * amu * a.dt / 6.0;
+      d = 0.5 * ((1.0 + t) * a.dx + k);
+      const double f1 = 0.5 * ((1.0 - 4.0 * t) * a.dx - 4.0 * k), g1 = 0.5 * (k + t * a.dx);
+      c.c_uu = f1; c.c_uv = -2.0 * k; c.c_vu = 2.0 * k; c.c_vv = f1;
+      c.p_uu = -g1; c.p_uv = -0.5 * k; c.p_vu = 0.5 * k; c.p_vv = -g1;
+      c.up1 = 4.0 * k; // b * 4 * in_half, in_half = half_ends(j-1).v
+      c.up2 = k;       // b * in_prev
+      c.kbc = 6.0;
+   }
+   const double o = 0.5 * k, det = d * d + o * o;
+   c.id = d / det;
+   c.io = o / det;
+   c.alpha = c.io * k;
+   c.gamma = c.id * k;
+   return c;
+}
+
+template <int KIND, bool CORR, int THREADS>
+__global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
+{
+   using TS = TileShape<THREADS>;
+   constexpr int CPT = TS::CPT, TILE = TS::TILE, SLOTS = TS::SLOTS, WARPS = TS::WARPS;
+   constexpr bool NEED_X2 = (KIND != KIND_BE);
+   constexpr bool NEED_XC = (KIND == KIND_BDF) && CORR;
+
+   extern __shared__ double2 smem[];
+   double2 *s1 = smem;                          // X1 tile, later the result tile
+   double2 *s2 = smem + SLOTS;                  // X2 tile
+   double2 *sc = smem + (NEED_X2 ? 2 : 1) * SLOTS; // ends-before-stage tile for the BDF correction source
+   __shared__ double s_warp_tot[WARPS];
+   __shared__ double s_halo1, s_halo2, s_agg, s_alast, s_ctile;
+   __shared__ long long s_ticket;
+
+   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+   const unsigned flag_agg = a.epoch * 2u + 1u, flag_incl = a.epoch * 2u + 2u;
+   const long long total_tiles = (long long)a.n_chains * a.tiles_per_chain;
+
+   while (true)
+   {
+      if (tid == 0) s_ticket = (long long)(atomicAdd(a.ticket, 1ull) - a.ticket_base);
+      __syncthreads();
+      const long long ticket = s_ticket;
+      if (ticket >= total_tiles) break;
+
+      // ---- decode ticket -> (chain, position) -> (row, tile in row)
+      const int p = (int)(ticket / a.n_chains), chain = (int)(ticket % a.n_chains);
+      int row, t;
+      if (a.reflective_left)
+      {
+         const int half_m = a.M >> 1, gl = chain / half_m, pp = chain % half_m;
+         if (p < a.tiles_per_row) { row = gl * a.M + (half_m - 1 - pp); t = p; }
+         else { row = gl * a.M + (half_m + pp); t = p - a.tiles_per_row; }
+      }
+      else { row = chain; t = p; }
+      const int gl = row / a.M, i = row % a.M, g = a.G0 + gl, sgn = (i >= (a.M >> 1)) ? 1 : 0;
+      const int tile_start = t * TILE;
+      const int valid = min(TILE, a.N - tile_start);
+      const size_t row_off = (size_t)row * a.Np + tile_start;
+      const RowCoef c = make_coef<KIND, CORR>(a, g, i);
+
+      // ---- stage the tile(s) in shared memory, coalesced 16-byte async copies
+      {
+         const double2 *g1 = a.x1[sgn] + row_off;
+         const double2 *g2 = NEED_X2 ? a.x2[sgn] + row_off : nullptr;
+         const double2 *gc = NEED_XC ? a.xc[sgn] + row_off : nullptr;
+#pragma unroll
+         for (int k = 0; k < CPT; ++k)
+         {
+            const int j = k * THREADS + tid, s = slot(j);
+            if (j < valid)
+            {
+               cp_async16(&s1[s], g1 + j);
+               if (NEED_X2) cp_async16(&s2[s], g2 + j);
+               if (NEED_XC) cp_async16(&sc[s], gc + j);
+            }
+            else
+            {
+               s1[s] = make_double2(0.0, 0.0);
+               if (NEED_X2) s2[s] = make_double2(0.0, 0.0);
+               if (NEED_XC) sc[s] = make_double2(0.0, 0.0);
+            }
+         }
+         if (tid == 0)
+         {
+            // old-time-level outflow nodes of the cell upstream of the tile (CN: prev ; BDF: half and prev)
+            double h1 = 0.0, h2 = 0.0;
+            if (NEED_X2 && tile_start > 0)
+            {
+               h2 = __ldcg(&(g2 - 1)->y);
+               if (KIND == KIND_BDF) h1 = __ldcg(&(g1 - 1)->y);
+            }
+            s_halo1 = h1;
+            s_halo2 = h2;
+         }
+         cp_async_wait_all();
+      }
+      __syncthreads();
+
+      // ---- pass 1: per-cell beta_j / U_j and the thread-local scan with zero inflow
+      double wl[CPT], U[CPT];
+      {
+         const int j0 = tid * CPT;
+         double up1, up2; // X1(j-1).v and X2(j-1).v
+         if (tid == 0) { up1 = s_halo1; up2 = s_halo2; }
+         else
+         {
+            up1 = (KIND == KIND_BDF) ? s1[slot(j0 - 1)].y : 0.0;
+            up2 = NEED_X2 ? s2[slot(j0 - 1)].y : 0.0;
+         }
+         const bool row_first = (tile_start == 0) && (tid == 0);
+         double w = 0.0;
+#pragma unroll
+         for (int jj = 0; jj < CPT; ++jj)
+         {
+            const int s = slot(j0 + jj);
+            const double2 x1 = s1[s];
+            double2 x2 = make_double2(0.0, 0.0);
+            if (NEED_X2) x2 = s2[s];
+            double q = c.qa;
+            if (CORR)
+            {
+               const double2 xs = NEED_XC ? sc[s] : x1;
+               q = fma(c.qb, xs.x + xs.y, c.qa);
+            }
+            double ru = q + c.c_uu * x1.x + c.c_uv * x1.y;
+            double rv = q + c.c_vu * x1.x + c.c_vv * x1.y;
+            if (KIND == KIND_BDF)
+            {
+               ru += c.p_uu * x2.x + c.p_uv * x2.y;
+               rv += c.p_vu * x2.x + c.p_vv * x2.y;
+            }
+            if (NEED_X2 && !(row_first && jj == 0)) ru += c.up1 * up1 + c.up2 * up2;
+            const double beta = c.io * ru + c.id * rv;
+            U[jj] = c.id * ru - c.io * rv;
+            w = fma(c.alpha, w, beta);
+            wl[jj] = w;
+            if (KIND == KIND_BDF) up1 = x1.y;
+            if (NEED_X2) up2 = x2.y;
+         }
+      }
+
+      // ---- block scan of the chunk aggregates (factor alpha^CPT per chunk)
+      double a2 = c.alpha * c.alpha, a4 = a2 * a2, a8 = a4 * a4; // CPT == 8
+      static_assert(CPT == 8, "chunk power assumes 8 cells per thread");
+      double pw[5];
+      double incl = wl[CPT - 1], f = a8;
+#pragma unroll
+      for (int s = 0; s < 5; ++s)
+      {
+         pw[s] = f;
+         const double o = __shfl_up_sync(0xffffffffu, incl, 1 << s);
+         if (lane >= (1 << s)) incl = fma(f, o, incl);
+         f = f * f;
+      }
+      const double warp_factor = f; // alpha^(32*CPT)
+      double excl = __shfl_up_sync(0xffffffffu, incl, 1);
+      if (lane == 0) excl = 0.0;
+      if (lane == 31) s_warp_tot[warp] = incl;
+      double lane_pow = 1.0; // alpha^(CPT*lane)
+#pragma unroll
+      for (int s = 0; s < 5; ++s)
+         if ((lane >> s) & 1) lane_pow *= pw[s];
+      __syncthreads();
+      double warp_carry = 0.0, warp_pow = 1.0; // inflow of this warp with zero tile inflow ; alpha^(32*CPT*warp)
+      for (int w2 = 0; w2 < warp; ++w2)
+      {
+         warp_carry = fma(warp_factor, warp_carry, s_warp_tot[w2]);
+         warp_pow *= warp_factor;
+      }
+      const double E_t = fma(lane_pow, warp_carry, excl); // inflow of this thread's chunk for zero tile inflow
+      const double tpow = lane_pow * warp_pow;            // alpha^(CPT*tid)
+
+      // ---- tile aggregate at the last valid cell
+      {
+         const int last = valid - 1;
+         if (tid == last / CPT)
+         {
+            const int jo = last % CPT;
+            double wsel = wl[0], apow = c.alpha;
+#pragma unroll
+            for (int jj = 1; jj < CPT; ++jj)
+               if (jj <= jo) { wsel = wl[jj]; apow *= c.alpha; }
+            s_agg = fma(apow, E_t, wsel);
+            s_alast = apow * tpow;
+         }
+      }
+      __syncthreads();
+
+      // ---- decoupled look-back (one thread)
+      if (tid == 0)
+      {
+         const size_t sidx = (size_t)chain * a.tiles_per_chain + p;
+         double ctile;
+         bool have = false;
+         if (t == 0)
+         {
+            if (p == 0)
+            {
+               ctile = c.kbc * a.bdry[(size_t)i + (size_t)a.M * g];
+               have = true;
+            }
+            else
+            {
+               // reflective: inflow = kbc * (outflow of the mirrored mu<0 row at its last cell, this stage)
+               const unsigned *fp = a.tile_flag + sidx - 1;
+               while ((int)(ld_acquire_u32(fp) - flag_incl) < 0) __nanosleep(20);
+               ctile = c.kbc * __ldcg(a.tile_incl + sidx - 1);
+               have = true;
+            }
+         }
+         else
+         {
+            // fast path: predecessor already holds its inclusive value
+            const unsigned fl = ld_acquire_u32(a.tile_flag + sidx - 1);
+            if ((int)(fl - flag_incl) >= 0) { ctile = __ldcg(a.tile_incl + sidx - 1); have = true; }
+         }
+         if (!have && !a.lookback_walk)
+         {
+            // deterministic mode: always take the predecessor's inclusive value, so the result does not
+            // depend on CTA timing (bitwise run-to-run reproducible); costs one L2 round trip per hop
+            // when a chain's tiles are in flight at the same time (few chains only)
+            const unsigned *fp = a.tile_flag + sidx - 1;
+            while ((int)(ld_acquire_u32(fp) - flag_incl) < 0) __nanosleep(20);
+            ctile = __ldcg(a.tile_incl + sidx - 1);
+            have = true;
+         }
+         if (!have)
+         {
+            __stcg(a.tile_agg + sidx, s_agg);
+            st_release_u32(a.tile_flag + sidx, flag_agg);
+            // alpha^TILE : aggregate factor of a full predecessor tile
+            double afull = warp_factor;
+#pragma unroll
+            for (int w2 = 1; w2 < WARPS; w2 <<= 1) afull *= afull;
+            static_assert((WARPS & (WARPS - 1)) == 0, "WARPS must be a power of two");
+            double carry = 0.0, fac = 1.0;
+            int q = t - 1; // tile index in the row
+            size_t qi = sidx - 1;
+            while (true)
+            {
+               unsigned fl;
+               while ((int)((fl = ld_acquire_u32(a.tile_flag + qi)) - flag_agg) < 0) __nanosleep(20);
+               if ((int)(fl - flag_incl) >= 0) { carry = fma(fac, __ldcg(a.tile_incl + qi), carry); break; }
+               if (q == 0)
+               {
+                  // first tile of a row always ends up inclusive; wait for it rather than walking past the row
+                  while ((int)(ld_acquire_u32(a.tile_flag + qi) - flag_incl) < 0) __nanosleep(20);
+                  carry = fma(fac, __ldcg(a.tile_incl + qi), carry);
+                  break;
+               }
+               carry = fma(fac, __ldcg(a.tile_agg + qi), carry);
+               fac *= afull;
+               if (fac == 0.0) break; // everything further upstream has underflowed out of fp64 range
+               --q;
+               --qi;
+            }
+            ctile = carry;
+         }
+         __stcg(a.tile_incl + sidx, fma(s_alast, ctile, s_agg));
+         st_release_u32(a.tile_flag + sidx, flag_incl);
+         s_ctile = ctile;
+      }
+      __syncthreads();
+
+      // ---- pass 2: true nodes, written back into the X1 tile (blocked, conflict-free)
+      {
+         const double cin = fma(tpow, s_ctile, E_t); // true inflow of this thread's chunk
+         const int j0 = tid * CPT;
+         double vin = cin, ap = c.alpha;
+#pragma unroll
+         for (int jj = 0; jj < CPT; ++jj)
+         {
+            const double v = fma(ap, cin, wl[jj]);
+            const double u = fma(c.gamma, vin, U[jj]);
+            s1[slot(j0 + jj)] = make_double2(u, v);
+            vin = v;
+            ap *= c.alpha;
+         }
+      }
+      __syncthreads();
+
+      // ---- coalesced store
+      {
+         double2 *go = a.out[sgn] + row_off;
+#pragma unroll
+         for (int k = 0; k < CPT; ++k)
+         {
+            const int j = k * THREADS + tid;
+            if (j < valid) __stcs(go + j, s1[slot(j)]);
+         }
+      }
+      __syncthreads(); // smem is reused by the next tile
+   }
+}
+
+// ------------------------------------------------------------------------------------------ host side
+template <int KIND, bool CORR, int THREADS>
+static size_t smem_bytes()
+{
+   const int narr = 1 + (KIND != KIND_BE ? 1 : 0) + ((KIND == KIND_BDF && CORR) ? 1 : 0);
+   return (size_t)narr * TileShape<THREADS>::SLOTS * sizeof(double2);
+}
+
+template <int KIND, bool CORR, int THREADS>
+static cudaError_t launch_one(const SweepArgs &a, int num_sms, cudaStream_t st, int *grid_out)
+{
+   static int ctas_per_sm = -1;
+   const size_t smem = smem_bytes<KIND, CORR, THREADS>();
+   auto kern = sweep_kernel<KIND, CORR, THREADS>;
+   if (ctas_per_sm < 0)
+   {
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return e;
+      int occ = 0;
+      e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, THREADS, smem);
+      if (e != cudaSuccess) return e;
+      ctas_per_sm = occ > 0 ? occ : 1;
+   }
+   const long long total = (long long)a.n_chains * a.tiles_per_chain;
+   long long grid = (long long)num_sms * ctas_per_sm;
+   if (grid > total) grid = total;
+   if (grid < 1) grid = 1;
+   if (grid_out) *grid_out = (int)grid;
+   kern<<<(unsigned)grid, THREADS, smem, st>>>(a);
+   return cudaGetLastError();
+}
+
+cudaError_t launch_sweep(int kind, bool corr, const SweepArgs &a, int num_sms, cudaStream_t st, int *grid_out)
+{
+   constexpr int T = SWEEP_THREADS;
+   switch (kind * 2 + (corr ? 1 : 0))
+   {
+   case 0: return launch_one<KIND_BE, false, T>(a, num_sms, st, grid_out);
+   case 1: return launch_one<KIND_BE, true, T>(a, num_sms, st, grid_out);
+   case 2: return launch_one<KIND_CN, false, T>(a, num_sms, st, grid_out);
+   case 3: return launch_one<KIND_CN, true, T>(a, num_sms, st, grid_out);
+   case 4: return launch_one<KIND_BDF, false, T>(a, num_sms, st, grid_out);
+   case 5: return launch_one<KIND_BDF, true, T>(a, num_sms, st, grid_out);
+   }
+   return cudaErrorInvalidValue;
+}
+} // namespace rtk

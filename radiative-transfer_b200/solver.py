@@ -1,0 +1,238 @@
+"""Python mirror of the reference's rt::Solver class surface (reference include/solver.h:76-98),
+implemented on librt_cuda.so.  Same method names, argument meaning and error behaviour; the caller
+owns psi_mat / phi / F exactly as in reference src/main.cc:88-113.
+
+    ph = prm.load("prm/single_group.prm")
+    psi = np.zeros((ph.M, ph.G, ph.N), order="F"); phi = np.zeros((ph.G, ph.N), order="F"); F = phi.copy()
+    s = Solver(ph, psi, phi, F)
+    s.solve(); s.compute_angle_integrated_intensity(); s.compute_radiative_flux(); s.compute_balance()
+
+Arrays use the reference's index order (Eigen column-major == numpy Fortran order).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import numpy as np
+
+from . import capi, grid
+from .prm import Parameters
+
+
+def _f(shape):
+    return np.zeros(shape, dtype=np.float64, order="F")
+
+
+class Solver:
+    def __init__(self, parameter_handler: Parameters, psi_mat: Optional[np.ndarray] = None,
+                 phi: Optional[np.ndarray] = None, F: Optional[np.ndarray] = None, *, device: int = 0,
+                 group_begin: int = 0, group_count: Optional[int] = None, groups_per_batch: int = 0,
+                 fetch_psi: bool = True):
+        ph = self.ph = parameter_handler
+        self.M, self.N, self.num_groups = ph.M, ph.N, ph.G
+        self.group_begin = group_begin
+        self.group_count = ph.G - group_begin if group_count is None else group_count
+        Gl = self.group_count
+        # solver.cpp:76-78 quadrature, 96-104 energy grid, 145-152 opacities
+        self.m_mu, self.m_wt = grid.gauss_legendre(ph.M, grid.FOUR_PI)
+        if ph.have_group_bounds:
+            self.e_edge = np.ascontiguousarray(ph.group_bounds, dtype=np.float64)
+        else:
+            self.e_edge = self.generate_group_edges()
+        self.e_ave, self.de_ave = self.generate_group_averages()
+        if ph.have_group_absorption_opacities:
+            self.kappa_vec = np.ascontiguousarray(ph.group_kappa, dtype=np.float64)
+        else:
+            self.kappa_vec = np.full(ph.G, ph.kappa_grey, dtype=np.float64)
+        # solver.cpp:67-73: psi_source is only fetched when some BC is a source; otherwise it is 0
+        src = None
+        if ph.bc_left_indicator == 1 or ph.bc_right_indicator == 1:
+            src = np.asfortranarray(np.asarray(ph.psi_source, dtype=np.float64).reshape(ph.M, ph.G))
+        self._src = src
+        self._fetch_psi = fetch_psi
+
+        def own(a, shape, name):
+            if a is None:
+                return _f(shape)
+            if a.shape != shape or a.dtype != np.float64 or not a.flags.f_contiguous:
+                raise ValueError(f"{name} must be a float64 Fortran-ordered array of shape {shape}")
+            return a
+
+        self.psi_mat_ref = own(psi_mat, (ph.M, Gl, ph.N), "psi_mat") if fetch_psi else psi_mat
+        self.phi_ref = own(phi, (Gl, ph.N), "phi")
+        self.F_ref = own(F, (Gl, ph.N), "F")
+        self.phi_plus = _f((Gl, ph.N))
+        self.balance = np.zeros(Gl)
+        self.left_ends = np.zeros(Gl)
+        self.right_ends = np.zeros(Gl)
+
+        p = capi.RtParams()
+        p.M, p.N, p.G = ph.M, ph.N, ph.G
+        p.group_begin, p.group_count = group_begin, Gl
+        p.ts_method, p.max_timesteps = ph.ts_method, ph.max_timesteps
+        p.bc_left, p.bc_right = ph.bc_left_indicator, ph.bc_right_indicator
+        p.use_correction, p.use_mg_equilib = int(ph.use_correction), int(ph.use_mg_equilib)
+        p.validate = int(ph.include_validation)
+        p.device, p.groups_per_batch = device, groups_per_batch
+        p.dx, p.dt, p.rho, p.T, p.V, p.kappa_grey = ph.dx, ph.dt, ph.rho, ph.T, ph.V, ph.kappa_grey
+        p.mu, p.wt = capi.ptr(self.m_mu), capi.ptr(self.m_wt)
+        p.e_edge, p.kappa = capi.ptr(self.e_edge), capi.ptr(self.kappa_vec)
+        p.psi_source = capi.ptr(src) if src is not None else None
+        self._h = C.c_void_p()
+        capi.check(capi.lib().rt_create(C.byref(p), C.byref(self._h)))
+        self.resident = self.plan().resident == 1
+        if fetch_psi and self.resident:
+            self._pull_psi()  # initial condition psi = B_g (solver.cpp:166-181)
+
+    # ------------------------------------------------------------------ lifetime
+    def close(self):
+        if getattr(self, "_h", None):
+            capi.lib().rt_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # ------------------------------------------------------------------ reference public surface
+    def generate_group_edges(self):
+        """solver.cpp:6-19"""
+        return grid.group_edges(self.ph.G, self.ph.efirst, self.ph.elast)
+
+    def generate_group_averages(self):
+        """solver.cpp:22-32"""
+        return grid.group_averages(self.e_edge)
+
+    def fill_energy_bound_arrays(self):
+        """solver.cpp:35-43: (G,2) array of [lower, upper] edges"""
+        return np.asfortranarray(np.stack([self.e_edge[:-1], self.e_edge[1:]], axis=1))
+
+    def solve(self):
+        """solver.cpp:590-823"""
+        capi.check(capi.lib().rt_solve(self._h))
+        if self._fetch_psi and self.resident:
+            self._pull_psi()
+
+    def compute_angle_integrated_intensity(self):
+        capi.check(capi.lib().rt_moments(self._h, capi.ptr(self.phi_ref), None, None))
+
+    def compute_positive_angle_integrated_intensity(self):
+        capi.check(capi.lib().rt_moments(self._h, None, capi.ptr(self.phi_plus), None))
+
+    def compute_radiative_flux(self):
+        capi.check(capi.lib().rt_moments(self._h, None, None, capi.ptr(self.F_ref)))
+
+    def compute_balance(self):
+        capi.check(capi.lib().rt_balance(self._h, capi.ptr(self.balance)))
+
+    def get_balance(self):
+        return self.balance.copy()
+
+    def get_phi_plus(self):
+        return self.phi_plus.copy(order="F")
+
+    def get_e_ave(self):
+        return self.e_ave.copy()
+
+    def compute_group_ends(self):
+        capi.check(capi.lib().rt_group_ends(self._h, capi.ptr(self.left_ends), capi.ptr(self.right_ends)))
+
+    def get_ends(self, side: str):
+        assert side in ("left", "right"), "Invalid option for 'side'."
+        return (self.left_ends if side == "left" else self.right_ends).copy()
+
+    # ------------------------------------------------------------------ extras used by tests / bench
+    def _pull_psi(self):
+        capi.check(capi.lib().rt_get_psi(self._h, capi.ptr(self.psi_mat_ref)))
+
+    def run_stages(self, n: int):
+        capi.check(capi.lib().rt_run_stages(self._h, int(n)))
+        if self._fetch_psi and self.resident:
+            self._pull_psi()
+
+    def reset(self):
+        capi.check(capi.lib().rt_reset(self._h))
+
+    @property
+    def stages_done(self) -> int:
+        n = C.c_int()
+        capi.check(capi.lib().rt_stages_done(self._h, C.byref(n)))
+        return n.value
+
+    @property
+    def total_stages(self) -> int:
+        n = C.c_int()
+        capi.check(capi.lib().rt_total_stages(self._h, C.byref(n)))
+        return n.value
+
+    def ends(self, which: int = 0):
+        a = _f((self.M, self.group_count, self.N, 2))
+        capi.check(capi.lib().rt_get_ends(self._h, which, capi.ptr(a)))
+        return a
+
+    def moments(self):
+        phi, pp, F = (_f((self.group_count, self.N)) for _ in range(3))
+        capi.check(capi.lib().rt_moments(self._h, capi.ptr(phi), capi.ptr(pp), capi.ptr(F)))
+        return phi, pp, F
+
+    def moments_group_major(self):
+        phi, pp, F = (np.zeros((self.group_count, self.N)) for _ in range(3))
+        capi.check(capi.lib().rt_moments_group_major(self._h, capi.ptr(phi), capi.ptr(pp), capi.ptr(F)))
+        return phi, pp, F
+
+    def group_terms(self):
+        G = self.num_groups
+        out = {k: np.zeros(G) for k in ("B", "dBdT", "dEB", "dsigEdE", "dkapEB")}
+        out["kappa_edge"] = np.zeros(G + 1)
+        capi.check(capi.lib().rt_get_group_terms(
+            self._h, *[capi.ptr(out[k]) for k in ("B", "dBdT", "dEB", "dsigEdE", "dkapEB", "kappa_edge")]))
+        return out
+
+    def psi_source(self):
+        a = _f((self.M, self.num_groups))
+        capi.check(capi.lib().rt_get_psi_source(self._h, capi.ptr(a)))
+        return a
+
+    def validate(self):
+        sums = np.zeros(3)
+        ok = C.c_int()
+        capi.check(capi.lib().rt_validate(self._h, capi.ptr(sums), C.byref(ok)))
+        return bool(ok.value), sums
+
+    def set_step_output(self, phi_host_ptr, group_major: bool = True):
+        capi.check(capi.lib().rt_set_step_output(self._h, phi_host_ptr, int(group_major)))
+
+    def timing(self) -> capi.RtTiming:
+        t = capi.RtTiming()
+        capi.check(capi.lib().rt_get_timing(self._h, C.byref(t)))
+        return t
+
+    def reset_timing(self):
+        capi.check(capi.lib().rt_reset_timing(self._h))
+
+    def plan(self) -> capi.RtPlan:
+        pl = capi.RtPlan()
+        capi.check(capi.lib().rt_get_plan(self._h, C.byref(pl)))
+        return pl
+
+
+def planck_groups(e_edge, T, device: int = 0):
+    """Device Planck group integrals for an array of temperatures: returns (B, dBdT, kernel_ms), B[cell, g]."""
+    e_edge = np.ascontiguousarray(e_edge, dtype=np.float64)
+    T = np.ascontiguousarray(np.atleast_1d(T), dtype=np.float64)
+    G = e_edge.size - 1
+    B = np.zeros((T.size, G))
+    dB = np.zeros((T.size, G))
+    ms = C.c_double()
+    capi.check(capi.lib().rt_planck_groups(device, G, capi.ptr(e_edge), T.size, capi.ptr(T), capi.ptr(B), capi.ptr(dB),
+                                           C.cast(C.byref(ms), C.POINTER(C.c_double))))
+    return B, dB, ms.value

@@ -1,0 +1,76 @@
+"""Helpers shared by the parity tests (TEST INFRASTRUCTURE)."""
+import os
+
+import numpy as np
+
+from conftest import GOLDEN, PRM_DIR, host_setup
+
+#: north_star tolerance: 1e-9 relative on scalar intensity / radiation energy at each BDF2 step
+RTOL = 1e-9
+
+
+def load_golden(name):
+    return dict(np.load(os.path.join(GOLDEN, name + ".npz")))
+
+
+def load_case(rt, name):
+    cwd = os.getcwd()
+    os.chdir(GOLDEN)  # table files are looked up as ../prm/<name> like the reference does
+    try:
+        return rt.prm.load(os.path.join(PRM_DIR, name + ".prm"))
+    finally:
+        os.chdir(cwd)
+
+
+def rel_err(a, b):
+    """max elementwise |a-b|/|b| ; entries where both are exactly equal (incl. 0 == 0) count as 0"""
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    d = np.abs(a - b)
+    den = np.abs(b)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        r = np.where(d == 0.0, 0.0, d / den)
+    return float(np.max(r)) if r.size else 0.0
+
+
+def state_err(a, b, group_axis=1, floor=1e-3):
+    """max |a-b| / (|b| + floor*gmax), gmax = max |b| over the entry's energy group.
+
+    <= RTOL means: 1e-9 relative elementwise, with an absolute floor of 1e-12 x the group's scale for entries that
+    are more than 1000x smaller than the group's largest one (zero crossings of the oscillating DG solution, where
+    an elementwise relative error is meaningless for reference and reformulation alike)."""
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    if b.size == 0:
+        return 0.0
+    axes = tuple(k for k in range(b.ndim) if k != group_axis)
+    gmax = np.max(np.abs(b), axis=axes, keepdims=True)
+    d = np.abs(a - b)
+    den = np.abs(b) + floor * gmax
+    with np.errstate(divide="ignore", invalid="ignore"):
+        r = np.where(d == 0.0, 0.0, d / den)
+    return float(np.max(r))
+
+
+def scaled_err(a, b, scale):
+    """max |a-b| / scale -- for quantities that are differences of large terms (flux, balance)"""
+    return float(np.max(np.abs(np.asarray(a) - np.asarray(b)))) / float(scale) if np.size(a) else 0.0
+
+
+def make_oracle(oracle, rt, p, num_threads=1):
+    mu, wt, e, kap = host_setup(rt, p)
+    return oracle.oracle_from_parameters(p, mu, wt, e, kap, num_threads=num_threads)
+
+
+def synthetic_parameters(rt, *, M, G, N, dt, V=1.0, steps=2, bc_left=2, bc_right=1, ts_method=3, dx=0.01, seed=20261104,
+                         use_correction=True, use_mg_equilib=True, efirst=0.01, elast=30.0):
+    """The synthetic slab of SURVEY 8(d): uniform slab dx=0.01, rho=T=1, log-spaced groups efirst=0.01..elast=30,
+    kappa_g = 10^U(-1,2) from PCG64(seed), correction live (V != 0), equilibrium boundary sources."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    kap = 10.0 ** rng.uniform(-1.0, 2.0, size=G)
+    p = rt.Parameters(M=M, G=G, N=N, X=N * dx, efirst=efirst, elast=elast, bc_left_indicator=bc_left,
+                      bc_right_indicator=bc_right, use_mg_equilib=use_mg_equilib, V=V, use_correction=use_correction,
+                      ts_method=ts_method, dt=dt, max_timesteps=steps, include_validation=False, rho=1.0, T=1.0)
+    p.have_group_absorption_opacities = True
+    p.group_kappa = kap
+    return p

@@ -1,0 +1,190 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI, via the Python mirror of rt::Solver) against
+ (a) the golden vectors dumped by the UNMODIFIED reference (tests/golden/*.npz), and
+ (b) the CPU oracle (oracle-2) on seeded synthetic slabs at sizes the oracle finishes in seconds.
+
+Tolerance (north_star): 1e-9 relative on psi / ends / scalar intensity at every BDF2 step, with the SAME number of
+stage sweeps as the reference.  The radiative flux F and the balance are differences of O(phi) terms; they are held to
+1e-9 of that scale.
+"""
+import numpy as np
+import pytest
+
+from conftest import GOLDEN_CASES
+from parity_util import RTOL, load_case, load_golden, make_oracle, rel_err, scaled_err, state_err, synthetic_parameters
+
+pytestmark = pytest.mark.gpu
+
+
+def _compare_state(tag, s, ref_psi, ref_ends):
+    e_psi = state_err(s.psi_mat_ref, ref_psi)
+    e_ends = state_err(s.ends(0), ref_ends)
+    print(f"{tag}: psi err {e_psi:.2e} ends err {e_ends:.2e} (pure elementwise rel: {rel_err(s.psi_mat_ref, ref_psi):.2e})")
+    assert e_psi <= RTOL, f"{tag}: psi off by {e_psi:.3e}"
+    assert e_ends <= RTOL, f"{tag}: ends off by {e_ends:.3e}"
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_golden_final_state(rt, name):
+    """every buffer the reference exposes or owns, after the reference's full stage count"""
+    p = load_case(rt, name)
+    g = load_golden(name)
+    with rt.Solver(p) as s:
+        assert np.array_equal(s.m_mu, g["mu"]) and np.array_equal(s.m_wt, g["wt"])
+        assert np.array_equal(s.e_edge, g["e_edge"]) and np.array_equal(s.kappa_vec, g["kappa"])
+        assert rel_err(s.psi_mat_ref, np.broadcast_to(g["B_init"][None, :, None], s.psi_mat_ref.shape)) <= 1e-12
+        assert s.total_stages == p.max_timesteps * (4 if p.ts_method == 3 else 1)
+        s.solve()
+        assert s.stages_done == s.total_stages  # identical iteration count
+        _compare_state(name, s, g["psi"], g["ends"])
+        for which, key in ((1, "prev_ends"), (2, "half_ends")):
+            e = state_err(s.ends(which), g[key])
+            assert e <= RTOL, f"{name}: {key} off by {e:.3e}"
+        s.compute_angle_integrated_intensity()
+        s.compute_positive_angle_integrated_intensity()
+        s.compute_radiative_flux()
+        s.compute_balance()
+        s.compute_group_ends()
+        scale = float(np.max(np.abs(g["phi"])))
+        assert state_err(s.phi_ref, g["phi"], group_axis=0) <= RTOL
+        assert state_err(s.get_phi_plus(), g["phi_plus"], group_axis=0) <= RTOL
+        assert scaled_err(s.F_ref, g["F"], scale) <= RTOL
+        assert scaled_err(s.get_balance(), g["balance"], 1.0) <= 1e-8
+        assert rel_err(s.get_ends("left"), g["left_ends"]) <= RTOL
+        assert rel_err(s.get_ends("right"), g["right_ends"]) <= RTOL
+        assert np.array_equal(s.get_e_ave(), g["e_ave"])
+        gt = s.group_terms()
+        for k in ("B", "dBdT", "dEB", "dsigEdE", "dkapEB", "kappa_edge"):
+            bscale = float(np.max(np.abs(g[k]))) or 1.0
+            assert scaled_err(gt[k], g[k], bscale) <= 1e-12, f"{name}: {k}"
+        # B and dB/dT group by group (the small groups too); the last group is a remainder of the grey total
+        assert rel_err(gt["B"][:-1], g["B"][:-1]) <= RTOL and rel_err(gt["dBdT"][:-1], g["dBdT"][:-1]) <= RTOL
+        assert scaled_err(s.psi_source(), g["psi_source"], float(np.max(np.abs(g["psi_source"]))) or 1.0) <= 1e-12
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_golden_step_snapshots(rt, name):
+    """parity at intermediate time steps against reference runs with max_timesteps = k"""
+    p = load_case(rt, name)
+    g = load_golden(name)
+    per_step = 4 if p.ts_method == 3 else 1
+    ks = sorted(int(k[len("psi_steps"):]) for k in g if k.startswith("psi_steps"))
+    assert ks
+    with rt.Solver(p) as s:
+        done = 0
+        for k in ks:
+            s.run_stages((k - done) * per_step)
+            done = k
+            _compare_state(f"{name}@step{k}", s, g[f"psi_steps{k}"], g[f"ends_steps{k}"])
+
+
+SYNTH = [
+    # name,                         M,  G,  N,     dt,   V,  steps, bcl, bcr
+    ("c4like_local_reflect",        16, 6,  4096,  1e-5, 1.0, 2,    2,   1),
+    ("c4like_longrange_reflect",    16, 6,  5000,  1e-3, 1.0, 2,    2,   1),
+    ("c5like_longrange_source",     32, 4,  6151,  1e-3, 1.0, 2,    1,   1),
+    ("very_long_range_vacuum",      4,  3,  20000, 5e-2, 0.5, 1,    0,   0),
+    ("v0_reflect_multitile",        8,  5,  2049,  1e-4, 0.0, 2,    2,   1),
+]
+
+
+@pytest.mark.parametrize("name,M,G,N,dt,V,steps,bcl,bcr", SYNTH)
+def test_synthetic_vs_oracle_each_step(rt, oracle, name, M, G, N, dt, V, steps, bcl, bcr):
+    """multi-tile rows (N > 2048), ragged N, alpha close to 1 (long-range coupling through the look-back), every BC"""
+    p = synthetic_parameters(rt, M=M, G=G, N=N, dt=dt, V=V, steps=steps, bc_left=bcl, bc_right=bcr)
+    o = make_oracle(oracle, rt, p, num_threads=8)
+    with rt.Solver(p) as s:
+        for step in range(steps):
+            for stage in range(4):
+                o.run_stages(1)
+                s.run_stages(1)
+                _compare_state(f"{name}@step{step}.{stage}", s, o.psi(), o.ends(0))
+        phi, pp, F = s.moments()
+        ophi, opp, oF = o.moments()
+        assert state_err(phi, ophi, group_axis=0) <= RTOL and state_err(pp, opp, group_axis=0) <= RTOL
+        assert scaled_err(F, oF, float(np.max(np.abs(ophi)))) <= RTOL
+        gm = s.moments_group_major()
+        assert np.array_equal(np.asfortranarray(gm[0]), phi)
+    o.close()
+
+
+@pytest.mark.parametrize("ts_method", [1, 2])
+def test_synthetic_be_cn_only(rt, oracle, ts_method):
+    p = synthetic_parameters(rt, M=8, G=3, N=4500, dt=2e-4, V=2.0, steps=5, ts_method=ts_method)
+    o = make_oracle(oracle, rt, p, num_threads=8)
+    o.solve()
+    with rt.Solver(p) as s:
+        s.solve()
+        _compare_state(f"ts{ts_method}", s, o.psi(), o.ends(0))
+        assert state_err(s.ends(1), o.ends(1)) <= RTOL
+    o.close()
+
+
+def test_batched_equals_resident(rt):
+    """group batching inside one GPU is exact (groups never couple): bit-identical moments"""
+    p = synthetic_parameters(rt, M=8, G=7, N=3000, dt=1e-3, steps=2)
+    with rt.Solver(p) as a:
+        a.solve()
+        a.compute_balance()
+        ra = a.moments() + (a.get_balance(),)
+        a.compute_group_ends()
+        la, rra = a.get_ends("left"), a.get_ends("right")
+    with rt.Solver(p, groups_per_batch=3, fetch_psi=False) as b:
+        assert b.plan().n_batches == 3 and not b.resident
+        b.solve()
+        rb = b.moments()
+        b.compute_balance()
+        b.compute_group_ends()
+        for x, y in zip(ra[:3], rb):
+            assert np.array_equal(x, y)
+        assert np.array_equal(ra[3], b.get_balance())
+        assert np.array_equal(la, b.get_ends("left")) and np.array_equal(rra, b.get_ends("right"))
+
+
+def test_group_shards_equal_whole(rt):
+    """a handle that owns groups [g0, g0+n) reproduces exactly those rows of the whole-problem solve"""
+    p = synthetic_parameters(rt, M=4, G=9, N=2500, dt=1e-3, steps=1)
+    with rt.Solver(p) as whole:
+        whole.solve()
+        phi = whole.moments()[0]
+        psi = whole.psi_mat_ref.copy(order="F")
+    for g0, n in ((0, 4), (4, 5)):
+        with rt.Solver(p, group_begin=g0, group_count=n) as part:
+            part.solve()
+            assert np.array_equal(part.moments()[0], phi[g0:g0 + n])
+            assert np.array_equal(part.psi_mat_ref, psi[:, g0:g0 + n])
+
+
+def test_step_output_matches_moments(rt):
+    import ctypes as C
+    p = synthetic_parameters(rt, M=4, G=5, N=2100, dt=1e-3, steps=3)
+    with rt.Solver(p, groups_per_batch=2, fetch_psi=False) as s:
+        buf = np.zeros((p.G, p.N))
+        s.set_step_output(buf.ctypes.data_as(C.c_void_p), True)
+        s.solve()
+        assert np.array_equal(buf, s.moments_group_major()[0])
+
+
+def test_validation_failure_is_loud(rt):
+    """include_validation with opacities that violate the emission identity -> rt_solve reports it (solver.cpp:609-612)"""
+    p = synthetic_parameters(rt, M=2, G=4, N=64, dt=1e-4, steps=1)
+    p.include_validation = True
+    with rt.Solver(p) as s:
+        ok, sums = s.validate()
+        assert not ok
+        with pytest.raises(rt.capi.RtError, match="Invalid Correction Terms"):
+            s.solve()
+
+
+def test_planck_kernel_vs_oracle(rt, oracle):
+    """device Planck integrals vs the CPU restatement over a temperature sweep (all three branches of Planck.cpp:131-150)"""
+    e = rt.grid.group_edges(64, 0.001, 60.0)
+    T = np.array([0.05, 0.3, 1.0, 2.5, 10.0])
+    B, dB, _ = rt.planck_groups(e, T)
+    for k, t in enumerate(T):
+        oB, odB = oracle.planck(float(t), e)
+        tot, dtot = float(np.sum(oB)), float(np.sum(odB))
+        assert scaled_err(B[k], oB, tot) <= 1e-12 and scaled_err(dB[k], odB, dtot) <= 1e-12
+        big = oB[:-1] > 1e-250
+        assert rel_err(B[k][:-1][big], oB[:-1][big]) <= RTOL
+        bigd = odB[:-1] > 1e-250
+        assert rel_err(dB[k][:-1][bigd], odB[:-1][bigd]) <= RTOL
