@@ -1,0 +1,347 @@
+#!/usr/bin/env python
+"""bench.py -- sweep throughput of the multigroup S_N slab solve on B200 (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W            # own arm (CUDA path through the C ABI)
+    python bench.py --impl reference --gpus N --steps K ...   # the reference's own CPU implementation
+
+A "step" is one BDF2 time step (4 stage sweeps: BE, CN, BE, BDF) of the whole synthetic slab.
+Workloads:   c4 = 2^20 cells x S16 x 256 groups  (N=1 default; group-batched on one GPU)
+                           c5 = 2^20 cells x S32 x 4096 groups (N>1 default; groups sharded over the ranks)
+`value` = unknown-stages/s = M*G*N*4*K / (device time of exactly K steps, max over ranks), state resident in HBM.
+`e2e`   = the same metric through the public API with HOST buffers: Solver(params) -> solve() with the scalar
+          intensity of every step read back into pinned host memory -> wall clock, setup included.
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import ctypes as C
+import importlib
+import json
+import math
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "sweep_unknown_stages_per_s"
+UNIT = "unknown-stages/s"
+BYTES_PER_UNKNOWN = {"BE": 32, "CN": 48, "BDF": 64}  # algorithmic fp64 traffic per (cell,angle,group), correction live
+
+WORKLOADS = {
+    # name: (M, G, N, bc_left, bc_right)
+    "c4": (16, 256, 1 << 20, 2, 1),
+    "c5": (32, 4096, 1 << 20, 1, 1),
+    "small": (16, 32, 1 << 16, 2, 1),
+}
+
+
+def synthetic_parameters(rt, M, G, N, bc_left, bc_right, dt, steps, seed=20261104):
+    """uniform slab dx=0.01, rho=T=1, V=1 (correction live), log groups 0.01..30 keV,
+    kappa_g = 10^U(-1,2) from PCG64(seed), equilibrium boundary sources, BDF2."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    kap = 10.0 ** rng.uniform(-1.0, 2.0, size=G)
+    p = rt.Parameters(M=M, G=G, N=N, X=N * 0.01, efirst=0.01, elast=30.0, bc_left_indicator=bc_left,
+                      bc_right_indicator=bc_right, use_mg_equilib=True, V=1.0, use_correction=True, ts_method=3,
+                      dt=dt, max_timesteps=steps, include_validation=False, rho=1.0, T=1.0)
+    p.have_group_absorption_opacities = True
+    p.group_kappa = kap
+    return p
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device, self.proc, self.lines = device, None, []
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def __exit__(self, *exc):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+
+    def summary(self):
+        sm, smax, power, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); smax.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for k, nm in enumerate(names):
+                if f[5 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(smax)), "power_w_max": float(max(power)),
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_baseline_port(rt, M, dt, cores, budget_s=12.0):
+    """oracle-2 (CPU restatement, bit-identical to the reference on its .prm cases) with OpenMP over groups on all
+    host cores, on a bounded sample of the same workload: same M, dt, physics; G = 2*cores groups, N = 2^14 cells."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_py
+    oracle_py.build()
+    G, N = max(16, 2 * cores), 1 << 14
+    p = synthetic_parameters(rt, M, G, N, 2, 1, dt, 1000)
+    mu, wt = rt.grid.gauss_legendre(M)
+    e = rt.grid.group_edges(G, p.efirst, p.elast)
+    o = oracle_py.oracle_from_parameters(p, mu, wt, e, p.group_kappa, num_threads=cores)
+    t0 = time.perf_counter()
+    o.run_stages(4)
+    t1 = time.perf_counter() - t0
+    steps = int(min(50, max(1, math.ceil(budget_s / max(t1, 1e-3)) - 1)))
+    t0 = time.perf_counter()
+    o.run_stages(4 * steps)
+    dtm = time.perf_counter() - t0
+    o.close()
+    return {"value": M * G * N * 4 * steps / dtm, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"oracle-2 (OpenMP over groups, {cores} threads): {steps} BDF2 steps of {N} cells x S{M} x {G} groups, dt={dt}"}
+
+
+def run_reference_arm(args, rt, M, G, N, bcl, bcr, workload):
+    """The reference's own CPU implementation (oracle/_ref/ref_dump = unmodified reference sources compiled in place)
+    on the box's host cores.  The reference is single-threaded, so `cores` independent instances run side by side, each
+    on a 2-group slice (groups never couple).  Its BDF2 mode copies the whole `ends` tensor once per cell
+    (solver.cpp:733, O(N^2)), so the sample is bounded at N = 1024 cells."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_py
+    cores = host_cores()
+    kind = "reference" if oracle_py.reference_available() else "port"
+    Ns, Gs = 1024, 2
+    t_all = None
+    if kind == "reference":
+        tmp = tempfile.mkdtemp(prefix="rtbench_ref_")
+        try:
+            os.makedirs(os.path.join(tmp, "prm"))
+            rng = np.random.Generator(np.random.PCG64(20261104))
+            kap_all = 10.0 ** rng.uniform(-1.0, 2.0, size=Gs * cores)
+
+            def launch(steps):
+                procs = []
+                for c in range(cores):
+                    p = synthetic_parameters(rt, M, Gs, Ns, bcl, bcr, args.dt, steps)
+                    p.filename_group_kappa = f"kap_{c}.txt"
+                    with open(os.path.join(tmp, "prm", p.filename_group_kappa), "w") as fh:
+                        fh.write("\n".join(repr(float(v)) for v in kap_all[c * Gs:(c + 1) * Gs]) + "\n")
+                    prm_path = os.path.join(tmp, "prm", f"case_{c}.prm")
+                    rt.prm.dump(p, prm_path)
+                    run_dir = os.path.join(tmp, f"run_{c}")
+                    os.makedirs(run_dir, exist_ok=True)
+                    procs.append((subprocess.Popen([oracle_py.REF_DUMP, prm_path, os.path.join(run_dir, "out.bin")],
+                                                   cwd=run_dir, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL), run_dir))
+                secs = []
+                for pr, run_dir in procs:
+                    if pr.wait() != 0:
+                        raise RuntimeError("reference instance failed")
+                    secs.append(float(oracle_py.read_dump(os.path.join(run_dir, "out.bin"))["solve_seconds"][0]))
+                return max(secs)
+
+            launch(args.warmup)
+            t_all = launch(args.steps)
+        finally:
+            shutil.rmtree(tmp, ignore_errors=True)
+        sample = (f"unmodified reference (oracle/_ref/ref_dump), {cores} single-thread instances x {args.steps} BDF2 steps of "
+                  f"{Ns} cells x S{M} x {Gs} groups, dt={args.dt}; time = slowest instance's Solver::solve()")
+    else:
+        oracle_py.build()
+        p = synthetic_parameters(rt, M, Gs * cores, Ns, bcl, bcr, args.dt, 10 ** 6)
+        mu, wt = rt.grid.gauss_legendre(M)
+        o = oracle_py.oracle_from_parameters(p, mu, wt, rt.grid.group_edges(p.G, p.efirst, p.elast), p.group_kappa, num_threads=cores)
+        o.run_stages(4 * args.warmup)
+        t0 = time.perf_counter()
+        o.run_stages(4 * args.steps)
+        t_all = time.perf_counter() - t0
+        o.close()
+        sample = f"oracle-2 port, OpenMP {cores} threads, {args.steps} BDF2 steps of {Ns} cells x S{M} x {Gs * cores} groups"
+    value = M * Gs * cores * Ns * 4 * args.steps / t_all
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * t_all / args.steps, "higher_is_better": True,
+            "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload, "M": M, "G": G, "N": N, "dt": args.dt, "ts_method": "BDF2",
+                       "sample": sample},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="own", choices=["own", "reference"])
+    ap.add_argument("--workload", default="auto", choices=["auto"] + sorted(WORKLOADS))
+    ap.add_argument("--dt", type=float, default=1e-3, help="1e-3: alpha~0.9 long-range coupling (default); 1e-5: local")
+    ap.add_argument("--groups-per-batch", type=int, default=0)
+    ap.add_argument("--cells", type=int, default=0, help="override the number of cells (debug)")
+    ap.add_argument("--groups", type=int, default=0, help="override the number of groups (debug)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    rt = importlib.import_module("radiative-transfer_b200")
+
+    workload = args.workload if args.workload != "auto" else ("c4" if max(world, args.gpus) == 1 else "c5")
+    M, G, N, bcl, bcr = WORKLOADS[workload]
+    if args.cells:
+        N = args.cells
+    if args.groups:
+        G = args.groups
+
+    if args.impl == "reference":
+        if rank == 0:
+            run_reference_arm(args, rt, M, G, N, bcl, bcr, workload)
+        return
+
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    sharding = importlib.import_module("radiative-transfer_b200.sharding")
+    g0, gn = sharding.group_range(G, world, rank)
+    K, W = args.steps, args.warmup
+    p = synthetic_parameters(rt, M, G, N, bcl, bcr, args.dt, K)
+
+    # ------------------------------------------------------------- device-resident timing (`value`)
+    s = rt.Solver(p, device=local_rank, group_begin=g0, group_count=gn, groups_per_batch=args.groups_per_batch, fetch_psi=False)
+    plan = s.plan()
+    if dist is not None:
+        dist.barrier()
+    with ClockSampler(local_rank) as clk:
+        ms = s.bench_steps(W, K)
+    tm = s.timing()
+    plan = s.plan()
+    s.close()
+    ms_max = ms
+    if dist is not None:
+        import torch
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_max = float(t.item())
+    unknown_stages = M * G * N * 4 * K
+    value = unknown_stages / (ms_max * 1e-3)
+
+    # roofline of the dominant kernel (the stage sweep): algorithmic bytes / event time of the launches, this rank
+    kinds = ["BE", "CN", "BDF"]
+    per_unknown_launch = M * gn * N
+    alg_bytes = sum(BYTES_PER_UNKNOWN[k] * per_unknown_launch * K * (2 if k == "BE" else 1) for k in kinds)
+    sweep_ms = sum(tm.sweep_ms)
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    achieved = alg_bytes / (sweep_ms * 1e-3) / 1e9 if sweep_ms > 0 else None
+    by_kind = {}
+    for i, k in enumerate(kinds):
+        if tm.sweep_ms[i] > 0:
+            nl = tm.sweep_launches[i]
+            by_kind[k] = {"launches": int(nl), "avg_ms": tm.sweep_ms[i] / nl,
+                          "GBps": BYTES_PER_UNKNOWN[k] * M * N * (tm.unknown_stages / tm.stages / (M * N)) * nl / (tm.sweep_ms[i] * 1e-3) / 1e9}
+    traffic = None
+    tr_path = os.path.join(ROOT, "profiles", "sweep_traffic.json")
+    if os.path.exists(tr_path):
+        traffic = json.load(open(tr_path)).get("dram_bytes_per_launch")
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
+                "traffic": traffic, "peak_source": peak_src, "kernel": "rtk::sweep_kernel<KIND,CORR,256> (BE,CN,BE,BDF per step)",
+                "algorithmic_bytes_per_unknown": BYTES_PER_UNKNOWN, "by_kind": by_kind}
+    gpu_launches = int(tm.kernel_launches)
+
+    # ------------------------------------------------------------- end to end through the public API (`e2e`)
+    e2e = None
+    if not args.no_e2e:
+        pin = C.c_void_p()
+        nbytes = gn * N * 8
+        rt.capi.check(rt.capi.lib().rt_host_alloc(C.byref(pin), nbytes))
+        try:
+            if dist is not None:
+                dist.barrier()
+            t0 = time.perf_counter()
+            s2 = rt.Solver(p, device=local_rank, group_begin=g0, group_count=gn, groups_per_batch=args.groups_per_batch, fetch_psi=False)
+            s2.set_step_output(pin, True)
+            s2.solve()
+            tm2 = s2.timing()
+            wall = time.perf_counter() - t0
+            s2.close()
+        finally:
+            rt.capi.lib().rt_host_free(pin)
+        wall_max = wall
+        if dist is not None:
+            import torch
+            t = torch.tensor([wall], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            wall_max = float(t.item())
+        e2e = {"value": unknown_stages / wall_max, "unit": UNIT, "h2d_bytes_per_step": int(tm2.h2d_bytes // K),
+               "d2h_bytes_per_step": int(tm2.d2h_bytes // K), "wall_s": wall_max,
+               "what": "Solver(params) [tables H2D, Planck+correction terms, state init] + solve() of K steps with phi of every "
+                       "step copied to pinned host memory; wall clock incl. allocation"}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline_port(rt, M, args.dt, host_cores())
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+                "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "strong" if workload == "c5" else "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": workload, "M": M, "G": G, "N": N, "dt": args.dt, "ts_method": "BDF2 (BE,CN,BE,BDF)",
+                           "bc": [bcl, bcr], "V": 1.0, "use_correction": True, "parallelism": f"groups sharded x{world}",
+                           "groups_per_rank": gn, "groups_per_batch": plan.groups_per_batch, "batches": plan.n_batches,
+                           "l2": "inputs larger than L2 (each launch streams >= 10 GB)" if M * min(plan.groups_per_batch, gn) * N * 32 > 2e8 else "inputs smaller than L2"},
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": gpu_launches,
+                "clocks": clk.summary(), "s_per_bdf2_step": ms_max / K * 1e-3,
+                "sweep_grid": plan.sweep_grid, "sweep_block": plan.sweep_block}
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

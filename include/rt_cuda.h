@@ -120,6 +120,14 @@ int rt_validate(rt_solver *s, double *sums3, int *ok);
  * end-to-end measurement: the device->host read of each step's result is inside rt_solve. */
 int rt_set_step_output(rt_solver *s, double *phi_host, int group_major);
 
+/* Measurement: for every batch of owned groups re-initialise, run `warmup_steps` untimed time steps, then time
+ * exactly `timed_steps` time steps (BDF2: 4 stage sweeps each) with CUDA events on the launching stream.
+ * *device_ms is the sum over batches; rt_timing afterwards covers the timed regions only. */
+int rt_bench_steps(rt_solver *s, int warmup_steps, int timed_steps, double *device_ms);
+/* pinned host memory for caller-owned result buffers (cudaMallocHost / cudaFreeHost) */
+int rt_host_alloc(void **p, size_t bytes);
+int rt_host_free(void *p);
+
 int rt_get_timing(const rt_solver *s, rt_timing *t);
 int rt_reset_timing(rt_solver *s);
 

@@ -22,7 +22,8 @@ EXPORTS = (
     "rt_last_error", "rt_abi_version", "rt_create", "rt_destroy", "rt_get_plan", "rt_solve", "rt_run_stages",
     "rt_stages_done", "rt_total_stages", "rt_reset", "rt_get_psi", "rt_get_ends", "rt_moments",
     "rt_moments_group_major", "rt_balance", "rt_group_ends", "rt_get_group_terms", "rt_get_psi_source",
-    "rt_validate", "rt_set_step_output", "rt_get_timing", "rt_reset_timing", "rt_planck_groups",
+    "rt_validate", "rt_set_step_output", "rt_get_timing", "rt_reset_timing", "rt_planck_groups", "rt_bench_steps",
+    "rt_host_alloc", "rt_host_free",
 )
 
 
@@ -97,6 +98,9 @@ def lib():
         L.rt_set_step_output.argtypes = [vp, C.c_void_p, C.c_int]
         L.rt_get_timing.argtypes = [vp, C.POINTER(RtTiming)]
         L.rt_reset_timing.argtypes = [vp]
+        L.rt_bench_steps.argtypes = [vp, C.c_int, C.c_int, _dp]
+        L.rt_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
+        L.rt_host_free.argtypes = [C.c_void_p]
         L.rt_planck_groups.argtypes = [C.c_int, C.c_int, _dp, C.c_int, _dp, _dp, _dp, _dp]
         _lib = L
     return _lib

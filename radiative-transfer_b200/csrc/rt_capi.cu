@@ -361,6 +361,9 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       }
       gb = (int)std::min<size_t>(fit, (size_t)s->Gl);
       if (gb < 1) { fail("rt_create: not even one group (%zu bytes) fits in %zu free bytes", per_group, free_b); rt_destroy(s); return 1; }
+      // balance the batches: same number of batches, equal sizes
+      const int nb = (s->Gl + gb - 1) / gb;
+      gb = (s->Gl + nb - 1) / nb;
    }
    gb = std::min(gb, s->Gl);
    s->Gb = gb;
@@ -862,4 +865,61 @@ extern "C" int rt_planck_groups(int device, int G, const double *e_edge, int nce
    if (b) cudaEventDestroy(b);
    cudaFree(d_e); cudaFree(d_T); cudaFree(d_B); cudaFree(d_dB);
    return rc;
+}
+
+// ---------------------------------------------------------------------------------------------
+// measurement helpers
+// For every batch of owned groups: re-initialise, run `warmup_steps` untimed time steps, then time exactly
+// `timed_steps` time steps with CUDA events on the launching stream (all launches and the gaps between them).
+// *device_ms = sum over batches -- the device time of `timed_steps` steps of ALL owned groups.
+// rt_timing is reset at the start and afterwards covers the timed regions only.
+extern "C" int rt_bench_steps(rt_solver *s, int warmup_steps, int timed_steps, double *device_ms)
+{
+   if (!s || !device_ms) return fail("rt_bench_steps: null argument");
+   CK(cudaSetDevice(s->p.device));
+   const int per_step = s->p.ts_method == 3 ? 4 : 1;
+   if (rt_reset_timing(s)) return 1;
+   cudaEvent_t e0, e1;
+   CK(cudaEventCreate(&e0));
+   CK(cudaEventCreate(&e1));
+   double total = 0.0;
+   const bool timing_was_on = s->timing_on;
+   for (int b = 0; b < s->n_batches; ++b)
+   {
+      if (load_batch(s, b * s->Gb)) return 1;
+      s->timing_on = false;
+      const rt_timing keep = s->tm;
+      if (run_stages(s, warmup_steps * per_step)) return 1;
+      CK(cudaStreamSynchronize(s->st));
+      CK(cudaStreamSynchronize(s->copy_st));
+      s->tm = keep; // warm-up work is not counted
+      s->timing_on = timing_was_on;
+      CK(cudaEventRecord(e0, s->st));
+      if (run_stages(s, timed_steps * per_step)) return 1;
+      CK(cudaEventRecord(e1, s->st));
+      CK(cudaStreamSynchronize(s->st));
+      CK(cudaStreamSynchronize(s->copy_st));
+      float ms = 0.f;
+      CK(cudaEventElapsedTime(&ms, e0, e1));
+      total += ms;
+      if (flush_events(s)) return 1;
+   }
+   CK(cudaEventDestroy(e0));
+   CK(cudaEventDestroy(e1));
+   s->results_valid = false;
+   *device_ms = total;
+   return 0;
+}
+
+// pinned host memory for the caller-owned result buffers of the end-to-end path
+extern "C" int rt_host_alloc(void **p, size_t bytes)
+{
+   if (!p) return fail("rt_host_alloc: null argument");
+   CK(cudaMallocHost(p, bytes));
+   return 0;
+}
+extern "C" int rt_host_free(void *p)
+{
+   if (p) CK(cudaFreeHost(p));
+   return 0;
 }

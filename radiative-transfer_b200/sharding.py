@@ -1,0 +1,58 @@
+"""Energy-group sharding across ranks (one process per GPU).
+
+Groups never couple in the solve (no scattering, no temperature update), so the path shards by
+contiguous blocks of groups with NO data-path collective; every rank keeps the G-length tables for all groups (the
+edge stencils of correction.cpp:125-249 and the "remainder into the last group" of Planck.cpp:58-76 need them).
+The only communication is the final gather of per-group results, done with torch.distributed (NCCL on GPUs, gloo in the
+CPU tests)."""
+from __future__ import annotations
+
+from typing import List, Tuple
+
+import numpy as np
+
+
+def group_range(G: int, world: int, rank: int) -> Tuple[int, int]:
+    """(first group, number of groups) of `rank`: contiguous blocks, the first G % world ranks get one more."""
+    if world < 1 or not (0 <= rank < world):
+        raise ValueError("bad world/rank")
+    if G < world:
+        raise ValueError(f"{G} groups cannot be sharded over {world} ranks")
+    base, extra = divmod(G, world)
+    begin = rank * base + min(rank, extra)
+    return begin, base + (1 if rank < extra else 0)
+
+
+def all_ranges(G: int, world: int) -> List[Tuple[int, int]]:
+    return [group_range(G, world, r) for r in range(world)]
+
+
+def batches(group_count: int, groups_per_batch: int) -> List[Tuple[int, int]]:
+    """(local first group, size) of the batches a rank processes one after the other when its state exceeds HBM."""
+    if groups_per_batch < 1:
+        raise ValueError("groups_per_batch must be >= 1")
+    return [(b, min(groups_per_batch, group_count - b)) for b in range(0, group_count, groups_per_batch)]
+
+
+def gather_group_rows(local: np.ndarray, G: int, dist=None, device=None) -> np.ndarray:
+    """All-gather arrays whose FIRST axis is the rank's group block, e.g. phi in group-major order [gl, c], into the
+    full [G, ...] array on every rank.  `dist` is torch.distributed (initialised) or None for a single process."""
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        assert local.shape[0] == G
+        return local
+    import torch
+    world, rank = dist.get_world_size(), dist.get_rank()
+    ranges = all_ranges(G, world)
+    assert local.shape[0] == ranges[rank][1]
+    dev = device if device is not None else ("cuda" if dist.get_backend() == "nccl" else "cpu")
+    tail = local.shape[1:]
+    nmax = max(n for _, n in ranges)
+    pad = np.zeros((nmax,) + tail, dtype=local.dtype)
+    pad[: local.shape[0]] = local
+    mine = torch.from_numpy(pad).to(dev)
+    outs = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(outs, mine)
+    full = np.empty((G,) + tail, dtype=local.dtype)
+    for (b, n), t in zip(ranges, outs):
+        full[b:b + n] = t[:n].cpu().numpy()
+    return full

@@ -211,6 +211,12 @@ class Solver:
     def set_step_output(self, phi_host_ptr, group_major: bool = True):
         capi.check(capi.lib().rt_set_step_output(self._h, phi_host_ptr, int(group_major)))
 
+    def bench_steps(self, warmup_steps: int, timed_steps: int) -> float:
+        """device milliseconds of exactly `timed_steps` time steps of all owned groups (summed over batches)"""
+        ms = C.c_double()
+        capi.check(capi.lib().rt_bench_steps(self._h, warmup_steps, timed_steps, C.cast(C.byref(ms), C.POINTER(C.c_double))))
+        return ms.value
+
     def timing(self) -> capi.RtTiming:
         t = capi.RtTiming()
         capi.check(capi.lib().rt_get_timing(self._h, C.byref(t)))
