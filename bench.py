@@ -289,7 +289,7 @@ def main():
     if os.path.exists(tr_path):
         traffic = json.load(open(tr_path)).get("dram_bytes_per_launch")
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
-                "traffic": traffic, "peak_source": peak_src, "kernel": "rtk::sweep_kernel<KIND,CORR,256> (BE,CN,BE,BDF per step)",
+                "traffic": traffic, "peak_source": peak_src, "kernel": "rtk::sweep_kernel<KIND,CORR,T> (BE,CN,BE,BDF per step)",
                 "algorithmic_bytes_per_unknown": BYTES_PER_UNKNOWN, "by_kind": by_kind}
     gpu_launches = int(tm.kernel_launches)
 

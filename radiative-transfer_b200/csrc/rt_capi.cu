@@ -73,6 +73,7 @@ struct rt_solver
    unsigned long long ticket_base = 0;
    unsigned epoch = 0;
    int last_grid = 0;
+   int threads = SWEEP_THREADS_DEFAULT, tile_cells = SWEEP_THREADS_DEFAULT * CELLS_PER_THREAD;
    // results retained across batches (group-major [gl][c]) and per-group diagnostics
    double *d_phi = nullptr, *d_phip = nullptr, *d_F = nullptr;
    double *d_balance = nullptr, *d_left = nullptr, *d_right = nullptr;
@@ -313,7 +314,13 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
    s->num_sms = prop.multiProcessorCount;
    s->Gl = p->group_count;
    s->Np = (N + 7) & ~7;
-   s->tiles_per_row = (N + TILE_CELLS - 1) / TILE_CELLS;
+   if (const char *te = getenv("RT_CUDA_SWEEP_THREADS"))
+   {
+      const int t = atoi(te);
+      if (t == 32 || t == 64 || t == 128 || t == 256) s->threads = t;
+   }
+   s->tile_cells = s->threads * CELLS_PER_THREAD;
+   s->tiles_per_row = (N + s->tile_cells - 1) / s->tile_cells;
    const char *tenv = getenv("RT_CUDA_TIMING");
    s->timing_on = !(tenv && tenv[0] == '0');
    const char *lenv = getenv("RT_CUDA_LOOKBACK");
@@ -392,10 +399,10 @@ extern "C" int rt_get_plan(const rt_solver *s, rt_plan *plan)
    plan->groups_per_batch = s->Gb;
    plan->n_batches = s->n_batches;
    plan->resident = s->n_batches == 1;
-   plan->tile_cells = TILE_CELLS;
+   plan->tile_cells = s->tile_cells;
    plan->tiles_per_row = s->tiles_per_row;
    plan->sweep_grid = s->last_grid;
-   plan->sweep_block = SWEEP_THREADS;
+   plan->sweep_block = s->threads;
    plan->bytes_per_group = (size_t)4 * s->p.M * s->Np * sizeof(double2);
    plan->state_bytes = 4 * s->buf_elems * sizeof(double2);
    cudaSetDevice(s->p.device);
@@ -495,7 +502,7 @@ static int run_one_stage(rt_solver *s)
    EventPair *ep;
    if (event_begin(s, kind, &ep)) return 1;
    int grid = 0;
-   CK(launch_sweep(kind, corr, a, s->num_sms, s->st, &grid));
+   CK(launch_sweep(kind, corr, s->threads, a, s->num_sms, s->st, &grid));
    if (event_end(s, ep)) return 1;
    s->ticket_base += (unsigned long long)a.n_chains * a.tiles_per_chain + (unsigned long long)grid;
    s->last_grid = grid;

@@ -28,9 +28,8 @@ constexpr double VALIDATION_TOL = 1.e-6;
 //   The cell average psi = (u+v)/2 is never stored (solver.cpp:352: psi is exactly 0.5*(L+R)).
 // ---------------------------------------------------------------------------------------------
 
-constexpr int SWEEP_THREADS = 256;
-constexpr int CELLS_PER_THREAD = 8;
-constexpr int TILE_CELLS = SWEEP_THREADS * CELLS_PER_THREAD; // 2048 cells = 32 KB of (u,v) per time level
+constexpr int SWEEP_THREADS_DEFAULT = 64;  // CTA size of the sweep kernel (32/64/128/256 selectable, RT_CUDA_SWEEP_THREADS)
+constexpr int CELLS_PER_THREAD = 8;          // tile = 8 * threads cells (512 cells = 8 KB of (u,v) per time level)
 
 enum StageKind : int { KIND_BE = 0, KIND_CN = 1, KIND_BDF = 2 };
 

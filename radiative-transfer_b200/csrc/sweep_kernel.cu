@@ -448,9 +448,9 @@ static cudaError_t launch_one(const SweepArgs &a, int num_sms, cudaStream_t st, 
    return cudaGetLastError();
 }
 
-cudaError_t launch_sweep(int kind, bool corr, const SweepArgs &a, int num_sms, cudaStream_t st, int *grid_out)
+template <int T>
+static cudaError_t launch_threads(int kind, bool corr, const SweepArgs &a, int num_sms, cudaStream_t st, int *grid_out)
 {
-   constexpr int T = SWEEP_THREADS;
    switch (kind * 2 + (corr ? 1 : 0))
    {
    case 0: return launch_one<KIND_BE, false, T>(a, num_sms, st, grid_out);
@@ -459,6 +459,18 @@ cudaError_t launch_sweep(int kind, bool corr, const SweepArgs &a, int num_sms, c
    case 3: return launch_one<KIND_CN, true, T>(a, num_sms, st, grid_out);
    case 4: return launch_one<KIND_BDF, false, T>(a, num_sms, st, grid_out);
    case 5: return launch_one<KIND_BDF, true, T>(a, num_sms, st, grid_out);
+   }
+   return cudaErrorInvalidValue;
+}
+
+cudaError_t launch_sweep(int kind, bool corr, int threads, const SweepArgs &a, int num_sms, cudaStream_t st, int *grid_out)
+{
+   switch (threads)
+   {
+   case 32: return launch_threads<32>(kind, corr, a, num_sms, st, grid_out);
+   case 64: return launch_threads<64>(kind, corr, a, num_sms, st, grid_out);
+   case 128: return launch_threads<128>(kind, corr, a, num_sms, st, grid_out);
+   case 256: return launch_threads<256>(kind, corr, a, num_sms, st, grid_out);
    }
    return cudaErrorInvalidValue;
 }
