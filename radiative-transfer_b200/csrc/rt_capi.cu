@@ -67,8 +67,7 @@ struct rt_solver
    int batch_start = 0, batch_groups = 0; // local group range of the batch currently on the device
    int stages_done = 0;
    // look-back state
-   double *d_tile_agg = nullptr, *d_tile_incl = nullptr;
-   unsigned *d_tile_flag = nullptr;
+   double2 *d_tile_status = nullptr;
    unsigned long long *d_ticket = nullptr;
    unsigned long long ticket_base = 0;
    unsigned epoch = 0;
@@ -253,11 +252,11 @@ extern "C" int rt_destroy(rt_solver *s)
    if (s->st) cudaStreamSynchronize(s->st);
    double *tabs[] = {s->d_mu, s->d_wt, s->d_e_edge, s->d_kappa, s->d_T, s->d_B, s->d_dBdT, s->d_kappa_edge, s->d_epf,
                      s->d_dEB, s->d_dsig, s->d_dkap, s->d_cor1, s->d_cor2, s->d_cor3, s->d_sigma, s->d_srcB, s->d_de_ave,
-                     s->d_sums, s->d_psi_source, s->d_bdry, s->d_tile_agg, s->d_tile_incl, s->d_phi, s->d_phip, s->d_F,
+                     s->d_sums, s->d_psi_source, s->d_bdry, s->d_phi, s->d_phip, s->d_F,
                      s->d_balance, s->d_left, s->d_right, s->d_stage, s->d_step_phi[0], s->d_step_phi[1]};
    for (double *t : tabs) if (t) cudaFree(t);
    for (int k = 0; k < 4; ++k) if (s->E[k]) cudaFree(s->E[k]);
-   if (s->d_tile_flag) cudaFree(s->d_tile_flag);
+   if (s->d_tile_status) cudaFree(s->d_tile_status);
    if (s->d_ticket) cudaFree(s->d_ticket);
    for (auto &ep : s->ev_pool) { cudaEventDestroy(ep.a); cudaEventDestroy(ep.b); }
    for (int k = 0; k < 2; ++k) if (s->step_ev[k]) cudaEventDestroy(s->step_ev[k]);
@@ -378,8 +377,8 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
    s->buf_elems = (size_t)gb * M * s->Np;
    for (int k = 0; k < 4; ++k) CKD(dalloc(&s->E[k], s->buf_elems));
    const size_t ntiles = (size_t)gb * M * s->tiles_per_row;
-   CKD(dalloc(&s->d_tile_agg, ntiles)); CKD(dalloc(&s->d_tile_incl, ntiles)); CKD(dalloc(&s->d_tile_flag, ntiles));
-   CKC(cudaMemsetAsync(s->d_tile_flag, 0, ntiles * sizeof(unsigned), s->st));
+   CKD(dalloc(&s->d_tile_status, ntiles));
+   CKC(cudaMemsetAsync(s->d_tile_status, 0, ntiles * sizeof(double2), s->st));
    if (s->n_batches > 1)
    {
       CKD(dalloc(&s->d_phi, (size_t)s->Gl * N)); CKD(dalloc(&s->d_phip, (size_t)s->Gl * N)); CKD(dalloc(&s->d_F, (size_t)s->Gl * N));
@@ -487,7 +486,7 @@ static int run_one_stage(rt_solver *s)
    a.out[0] = a.out[1] = s->E[out];
    a.sigma = s->d_sigma; a.srcB = s->d_srcB; a.cor1 = s->d_cor1; a.cor2 = s->d_cor2; a.cor3 = s->d_cor3;
    a.mu = s->d_mu; a.bdry = s->d_bdry;
-   a.tile_agg = s->d_tile_agg; a.tile_incl = s->d_tile_incl; a.tile_flag = s->d_tile_flag;
+   a.tile_status = s->d_tile_status;
    a.ticket = s->d_ticket; a.ticket_base = s->ticket_base;
    a.epoch = ++s->epoch;
    a.M = p.M; a.N = p.N; a.Np = s->Np; a.G0 = p.group_begin + s->batch_start;

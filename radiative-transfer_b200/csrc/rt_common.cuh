@@ -49,9 +49,8 @@ struct SweepArgs
    const double *mu;     // M
    const double *bdry;   // M*G inflow values psi_source(i,g) already masked by the BC switch (0 where vacuum)
    // look-back state
-   double *tile_agg;              // [chains*tiles_per_chain] zero-carry value at the tile's last cell
-   double *tile_incl;             // [..] true outflow at the tile's last cell
-   unsigned int *tile_flag;       // [..] epoch*2+1 = aggregate ready, epoch*2+2 = inclusive ready
+   double2 *tile_status;          // [chains*tiles_per_chain] {value, flag}: flag = epoch*2+1 -> value is the tile's zero-inflow
+                                  // aggregate, epoch*2+2 -> value is the true outflow at the tile's last cell
    unsigned long long *ticket;    // monotonically increasing work counter
    unsigned long long ticket_base;
    unsigned int epoch;

@@ -19,9 +19,13 @@
 // Work distribution: persistent CTAs draw tickets from a global counter; ticket t maps to
 // (tile position p = t / n_chains, chain = t % n_chains), i.e. all chains advance together and the
 // predecessor tile of a chain has normally been finished long before its successor starts -- the
-// look-back then costs one flag read.  With few chains (small problems) the same code degrades
+// look-back then costs one 16-byte status read, issued before the local scan so its latency is hidden.  With few chains (small problems) the same code degrades
 // gracefully to the classic aggregate walk-back.  Tickets are handed out in dependency order, so a
 // CTA only ever waits on a CTA that is already running: no deadlock, no cooperative launch.
+//
+// Pipeline: each CTA double-buffers its tiles in shared memory -- the cp.async copies of the NEXT ticket's tile are
+// in flight while the current tile is scanned, and the ticket after that is being drawn -- so HBM reads never wait
+// for the scan, the look-back or the barriers of the tile in progress.
 //
 // Reflective left boundary (solver.cpp:677-685): the mu>0 row takes its inflow from the SAME
 // stage's result of the mirrored mu<0 row at cell 0, i.e. from the end of that row's sweep.  The two
@@ -35,24 +39,10 @@
 
 namespace rtk
 {
-__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p)
-{
-   unsigned v;
-   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-   return v;
-}
-__device__ __forceinline__ void st_release_u32(unsigned *p, unsigned v)
-{
-   asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
 __device__ __forceinline__ void cp_async16(void *smem, const void *gmem)
 {
    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all()
-{
-   asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
 }
 
 // padded shared-memory slot of cell j of the tile: one 16-byte pad slot per 8 cells makes both the
@@ -138,6 +128,60 @@ __device__ __forceinline__ RowCoef make_coef(const SweepArgs &a, int g, int i)
    return c;
 }
 
+// ---- tile status word: {value, flag} in ONE aligned 16-byte word, written and read with single 128-bit
+// accesses (the same single-copy-atomicity CUB's decoupled look-back relies on for 16-byte descriptors), so no
+// fence is needed between value and flag.
+__device__ __forceinline__ double2 ld_status(const double2 *p)
+{
+   double2 v;
+   asm volatile("ld.volatile.global.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p) : "memory");
+   return v;
+}
+__device__ __forceinline__ void st_status(double2 *p, double value, unsigned flag)
+{
+   const double f = __longlong_as_double((long long)flag);
+   asm volatile("st.volatile.global.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(value), "d"(f) : "memory");
+}
+__device__ __forceinline__ unsigned status_flag(const double2 &v) { return (unsigned)__double_as_longlong(v.y); }
+
+__device__ __forceinline__ void cp_async8(void *smem, const void *gmem)
+{
+   const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+struct TileInfo
+{
+   int chain, p, row, t, g, i, sgn, tile_start, valid;
+   size_t row_off;
+};
+
+// ticket -> (tile position p, chain) -> (row, tile in row); p-major so that all chains advance together
+__device__ __forceinline__ TileInfo decode_ticket(const SweepArgs &a, long long ticket, int tile_cells)
+{
+   TileInfo ti;
+   ti.p = (int)(ticket / a.n_chains);
+   ti.chain = (int)(ticket % a.n_chains);
+   if (a.reflective_left)
+   {
+      const int half_m = a.M >> 1, gl = ti.chain / half_m, pp = ti.chain % half_m;
+      if (ti.p < a.tiles_per_row) { ti.row = gl * a.M + (half_m - 1 - pp); ti.t = ti.p; }
+      else { ti.row = gl * a.M + (half_m + pp); ti.t = ti.p - a.tiles_per_row; }
+   }
+   else { ti.row = ti.chain; ti.t = ti.p; }
+   const int gl = ti.row / a.M;
+   ti.i = ti.row % a.M;
+   ti.g = a.G0 + gl;
+   ti.sgn = (ti.i >= (a.M >> 1)) ? 1 : 0;
+   ti.tile_start = ti.t * tile_cells;
+   ti.valid = min(tile_cells, a.N - ti.tile_start);
+   ti.row_off = (size_t)ti.row * a.Np + ti.tile_start;
+   return ti;
+}
+
 template <int KIND, bool CORR, int THREADS>
 __global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
 {
@@ -145,92 +189,110 @@ __global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
    constexpr int CPT = TS::CPT, TILE = TS::TILE, SLOTS = TS::SLOTS, WARPS = TS::WARPS;
    constexpr bool NEED_X2 = (KIND != KIND_BE);
    constexpr bool NEED_XC = (KIND == KIND_BDF) && CORR;
+   constexpr int NARR = 1 + (NEED_X2 ? 1 : 0) + (NEED_XC ? 1 : 0);
+   static_assert(CPT == 8, "chunk power assumes 8 cells per thread");
+   static_assert((WARPS & (WARPS - 1)) == 0, "WARPS must be a power of two");
 
-   extern __shared__ double2 smem[];
-   double2 *s1 = smem;                          // X1 tile, later the result tile
-   double2 *s2 = smem + SLOTS;                  // X2 tile
-   double2 *sc = smem + (NEED_X2 ? 2 : 1) * SLOTS; // ends-before-stage tile for the BDF correction source
+   extern __shared__ double2 smem[]; // [2 pipeline buffers][NARR arrays][SLOTS]
    __shared__ double s_warp_tot[WARPS];
-   __shared__ double s_halo1, s_halo2, s_agg, s_alast, s_ctile;
-   __shared__ long long s_ticket;
+   __shared__ double s_halo[2][2];
+   __shared__ double s_agg, s_alast, s_ctile;
+   __shared__ long long s_ticket[2];
 
    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
    const unsigned flag_agg = a.epoch * 2u + 1u, flag_incl = a.epoch * 2u + 2u;
    const long long total_tiles = (long long)a.n_chains * a.tiles_per_chain;
 
-   while (true)
-   {
-      if (tid == 0) s_ticket = (long long)(atomicAdd(a.ticket, 1ull) - a.ticket_base);
-      __syncthreads();
-      const long long ticket = s_ticket;
-      if (ticket >= total_tiles) break;
-
-      // ---- decode ticket -> (chain, position) -> (row, tile in row)
-      const int p = (int)(ticket / a.n_chains), chain = (int)(ticket % a.n_chains);
-      int row, t;
-      if (a.reflective_left)
-      {
-         const int half_m = a.M >> 1, gl = chain / half_m, pp = chain % half_m;
-         if (p < a.tiles_per_row) { row = gl * a.M + (half_m - 1 - pp); t = p; }
-         else { row = gl * a.M + (half_m + pp); t = p - a.tiles_per_row; }
-      }
-      else { row = chain; t = p; }
-      const int gl = row / a.M, i = row % a.M, g = a.G0 + gl, sgn = (i >= (a.M >> 1)) ? 1 : 0;
-      const int tile_start = t * TILE;
-      const int valid = min(TILE, a.N - tile_start);
-      const size_t row_off = (size_t)row * a.Np + tile_start;
-      const RowCoef c = make_coef<KIND, CORR>(a, g, i);
-
-      // ---- stage the tile(s) in shared memory, coalesced 16-byte async copies
-      {
-         const double2 *g1 = a.x1[sgn] + row_off;
-         const double2 *g2 = NEED_X2 ? a.x2[sgn] + row_off : nullptr;
-         const double2 *gc = NEED_XC ? a.xc[sgn] + row_off : nullptr;
+   // coalesced 16-byte async copies of one tile's time levels into pipeline buffer b
+   auto issue_loads = [&](const TileInfo &ti, int b) {
+      double2 *d1 = smem + (size_t)b * NARR * SLOTS;
+      double2 *d2 = d1 + SLOTS;
+      double2 *dc = d1 + (NEED_X2 ? 2 : 1) * SLOTS;
+      const double2 *g1 = a.x1[ti.sgn] + ti.row_off;
+      const double2 *g2 = NEED_X2 ? a.x2[ti.sgn] + ti.row_off : nullptr;
+      const double2 *gc = NEED_XC ? a.xc[ti.sgn] + ti.row_off : nullptr;
 #pragma unroll
-         for (int k = 0; k < CPT; ++k)
+      for (int k = 0; k < CPT; ++k)
+      {
+         const int j = k * THREADS + tid, s = slot(j);
+         if (j < ti.valid)
          {
-            const int j = k * THREADS + tid, s = slot(j);
-            if (j < valid)
-            {
-               cp_async16(&s1[s], g1 + j);
-               if (NEED_X2) cp_async16(&s2[s], g2 + j);
-               if (NEED_XC) cp_async16(&sc[s], gc + j);
-            }
-            else
-            {
-               s1[s] = make_double2(0.0, 0.0);
-               if (NEED_X2) s2[s] = make_double2(0.0, 0.0);
-               if (NEED_XC) sc[s] = make_double2(0.0, 0.0);
-            }
+            cp_async16(&d1[s], g1 + j);
+            if (NEED_X2) cp_async16(&d2[s], g2 + j);
+            if (NEED_XC) cp_async16(&dc[s], gc + j);
          }
-         if (tid == 0)
+         else
          {
-            // old-time-level outflow nodes of the cell upstream of the tile (CN: prev ; BDF: half and prev)
-            double h1 = 0.0, h2 = 0.0;
-            if (NEED_X2 && tile_start > 0)
-            {
-               h2 = __ldcg(&(g2 - 1)->y);
-               if (KIND == KIND_BDF) h1 = __ldcg(&(g1 - 1)->y);
-            }
-            s_halo1 = h1;
-            s_halo2 = h2;
+            d1[s] = make_double2(0.0, 0.0);
+            if (NEED_X2) d2[s] = make_double2(0.0, 0.0);
+            if (NEED_XC) dc[s] = make_double2(0.0, 0.0);
          }
-         cp_async_wait_all();
       }
-      __syncthreads();
+      if (NEED_X2 && tid == 0)
+      {
+         // old-time-level outflow nodes of the cell upstream of the tile (CN: prev ; BDF: half and prev)
+         if (ti.tile_start > 0)
+         {
+            cp_async8(&s_halo[b][1], &(g2 - 1)->y);
+            if (KIND == KIND_BDF) cp_async8(&s_halo[b][0], &(g1 - 1)->y);
+            else s_halo[b][0] = 0.0;
+         }
+         else { s_halo[b][0] = 0.0; s_halo[b][1] = 0.0; }
+      }
+   };
+
+   // every CTA draws tickets until it has seen ONE that is past the end (the host's ticket accounting relies on it)
+   long long last_taken = 0;
+   auto take_ticket = [&]() -> long long {
+      if (last_taken >= total_tiles) return last_taken;
+      last_taken = (long long)(atomicAdd(a.ticket, 1ull) - a.ticket_base);
+      return last_taken;
+   };
+
+   // ---- prologue: first tile in flight, second ticket drawn
+   if (tid == 0) s_ticket[0] = take_ticket();
+   __syncthreads();
+   long long cur = s_ticket[0];
+   int buf = 0;
+   if (cur < total_tiles) issue_loads(decode_ticket(a, cur, TILE), 0);
+   cp_async_commit();
+   if (tid == 0) s_ticket[1] = take_ticket();
+
+   while (cur < total_tiles)
+   {
+      __syncthreads(); // (A) next ticket visible ; everybody is done with the other pipeline buffer
+      const long long nxt = s_ticket[buf ^ 1];
+      if (nxt < total_tiles) issue_loads(decode_ticket(a, nxt, TILE), buf ^ 1);
+      cp_async_commit();
+      long long after_next = 0;
+      if (tid == 0) after_next = take_ticket(); // latency hidden behind this tile's work; published at the loop end
+
+      const TileInfo ti = decode_ticket(a, cur, TILE);
+      const RowCoef c = make_coef<KIND, CORR>(a, ti.g, ti.i);
+      double2 *s1 = smem + (size_t)buf * NARR * SLOTS; // X1 tile, later the result tile
+      double2 *s2 = s1 + SLOTS;                          // X2 tile
+      double2 *sc = s1 + (NEED_X2 ? 2 : 1) * SLOTS;      // ends-before-stage tile for the BDF correction source
+      double2 *status = a.tile_status + ((size_t)ti.chain * a.tiles_per_chain + ti.p);
+
+      // early look-back probe: by the time the local scan is done the predecessor's word has arrived
+      double2 early = make_double2(0.0, 0.0);
+      if (tid == 0 && ti.p > 0) early = ld_status(status - 1);
+
+      cp_async_wait<1>(); // this tile's copies (the group before the prefetch) have landed
+      __syncthreads();    // (B)
 
       // ---- pass 1: per-cell beta_j / U_j and the thread-local scan with zero inflow
       double wl[CPT], U[CPT];
       {
          const int j0 = tid * CPT;
          double up1, up2; // X1(j-1).v and X2(j-1).v
-         if (tid == 0) { up1 = s_halo1; up2 = s_halo2; }
+         if (tid == 0) { up1 = s_halo[buf][0]; up2 = s_halo[buf][1]; }
          else
          {
             up1 = (KIND == KIND_BDF) ? s1[slot(j0 - 1)].y : 0.0;
             up2 = NEED_X2 ? s2[slot(j0 - 1)].y : 0.0;
          }
-         const bool row_first = (tile_start == 0) && (tid == 0);
+         const bool row_first = (ti.tile_start == 0) && (tid == 0);
          double w = 0.0;
 #pragma unroll
          for (int jj = 0; jj < CPT; ++jj)
@@ -263,8 +325,7 @@ __global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
       }
 
       // ---- block scan of the chunk aggregates (factor alpha^CPT per chunk)
-      double a2 = c.alpha * c.alpha, a4 = a2 * a2, a8 = a4 * a4; // CPT == 8
-      static_assert(CPT == 8, "chunk power assumes 8 cells per thread");
+      const double a2 = c.alpha * c.alpha, a4 = a2 * a2, a8 = a4 * a4;
       double pw[5];
       double incl = wl[CPT - 1], f = a8;
 #pragma unroll
@@ -278,24 +339,35 @@ __global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
       const double warp_factor = f; // alpha^(32*CPT)
       double excl = __shfl_up_sync(0xffffffffu, incl, 1);
       if (lane == 0) excl = 0.0;
-      if (lane == 31) s_warp_tot[warp] = incl;
       double lane_pow = 1.0; // alpha^(CPT*lane)
 #pragma unroll
       for (int s = 0; s < 5; ++s)
          if ((lane >> s) & 1) lane_pow *= pw[s];
-      __syncthreads();
-      double warp_carry = 0.0, warp_pow = 1.0; // inflow of this warp with zero tile inflow ; alpha^(32*CPT*warp)
-      for (int w2 = 0; w2 < warp; ++w2)
+      double warp_carry = 0.0, warp_pow = 1.0; // inflow of this warp for zero tile inflow ; alpha^(32*CPT*warp)
+      if (WARPS > 1)
       {
-         warp_carry = fma(warp_factor, warp_carry, s_warp_tot[w2]);
-         warp_pow *= warp_factor;
+         if (lane == 31) s_warp_tot[warp] = incl;
+         __syncthreads(); // (C)
+         for (int w2 = 0; w2 < warp; ++w2)
+         {
+            warp_carry = fma(warp_factor, warp_carry, s_warp_tot[w2]);
+            warp_pow *= warp_factor;
+         }
       }
       const double E_t = fma(lane_pow, warp_carry, excl); // inflow of this thread's chunk for zero tile inflow
       const double tpow = lane_pow * warp_pow;            // alpha^(CPT*tid)
+      double afull = warp_factor;                         // alpha^TILE
+#pragma unroll
+      for (int w2 = 1; w2 < WARPS; w2 <<= 1) afull *= afull;
 
-      // ---- tile aggregate at the last valid cell
+      // ---- tile aggregate (zero-inflow value and inflow factor at the tile's last valid cell)
+      if (ti.valid == TILE)
       {
-         const int last = valid - 1;
+         if (tid == THREADS - 1) { s_agg = fma(a8, E_t, wl[CPT - 1]); s_alast = afull; }
+      }
+      else
+      {
+         const int last = ti.valid - 1;
          if (tid == last / CPT)
          {
             const int jo = last % CPT;
@@ -307,83 +379,55 @@ __global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
             s_alast = apow * tpow;
          }
       }
-      __syncthreads();
+      __syncthreads(); // (D)
 
       // ---- decoupled look-back (one thread)
       if (tid == 0)
       {
-         const size_t sidx = (size_t)chain * a.tiles_per_chain + p;
          double ctile;
-         bool have = false;
-         if (t == 0)
-         {
-            if (p == 0)
-            {
-               ctile = c.kbc * a.bdry[(size_t)i + (size_t)a.M * g];
-               have = true;
-            }
-            else
-            {
-               // reflective: inflow = kbc * (outflow of the mirrored mu<0 row at its last cell, this stage)
-               const unsigned *fp = a.tile_flag + sidx - 1;
-               while ((int)(ld_acquire_u32(fp) - flag_incl) < 0) __nanosleep(20);
-               ctile = c.kbc * __ldcg(a.tile_incl + sidx - 1);
-               have = true;
-            }
-         }
+         if (ti.p == 0) ctile = c.kbc * a.bdry[(size_t)ti.i + (size_t)a.M * ti.g];
          else
          {
-            // fast path: predecessor already holds its inclusive value
-            const unsigned fl = ld_acquire_u32(a.tile_flag + sidx - 1);
-            if ((int)(fl - flag_incl) >= 0) { ctile = __ldcg(a.tile_incl + sidx - 1); have = true; }
-         }
-         if (!have && !a.lookback_walk)
-         {
-            // deterministic mode: always take the predecessor's inclusive value, so the result does not
-            // depend on CTA timing (bitwise run-to-run reproducible); costs one L2 round trip per hop
-            // when a chain's tiles are in flight at the same time (few chains only)
-            const unsigned *fp = a.tile_flag + sidx - 1;
-            while ((int)(ld_acquire_u32(fp) - flag_incl) < 0) __nanosleep(20);
-            ctile = __ldcg(a.tile_incl + sidx - 1);
-            have = true;
-         }
-         if (!have)
-         {
-            __stcg(a.tile_agg + sidx, s_agg);
-            st_release_u32(a.tile_flag + sidx, flag_agg);
-            // alpha^TILE : aggregate factor of a full predecessor tile
-            double afull = warp_factor;
-#pragma unroll
-            for (int w2 = 1; w2 < WARPS; w2 <<= 1) afull *= afull;
-            static_assert((WARPS & (WARPS - 1)) == 0, "WARPS must be a power of two");
-            double carry = 0.0, fac = 1.0;
-            int q = t - 1; // tile index in the row
-            size_t qi = sidx - 1;
-            while (true)
+            const bool junction = (ti.t == 0); // reflective: first tile of the mu>0 row, fed by the mirrored mu<0 row
+            double2 w = early;
+            if (junction || !a.lookback_walk)
             {
-               unsigned fl;
-               while ((int)((fl = ld_acquire_u32(a.tile_flag + qi)) - flag_agg) < 0) __nanosleep(20);
-               if ((int)(fl - flag_incl) >= 0) { carry = fma(fac, __ldcg(a.tile_incl + qi), carry); break; }
-               if (q == 0)
-               {
-                  // first tile of a row always ends up inclusive; wait for it rather than walking past the row
-                  while ((int)(ld_acquire_u32(a.tile_flag + qi) - flag_incl) < 0) __nanosleep(20);
-                  carry = fma(fac, __ldcg(a.tile_incl + qi), carry);
-                  break;
-               }
-               carry = fma(fac, __ldcg(a.tile_agg + qi), carry);
-               fac *= afull;
-               if (fac == 0.0) break; // everything further upstream has underflowed out of fp64 range
-               --q;
-               --qi;
+               // deterministic: always the predecessor's inclusive value (bitwise run-to-run reproducible)
+               while ((int)(status_flag(w) - flag_incl) < 0) { __nanosleep(32); w = ld_status(status - 1); }
+               ctile = junction ? c.kbc * w.x : w.x;
             }
-            ctile = carry;
+            else if ((int)(status_flag(w) - flag_incl) >= 0) ctile = w.x;
+            else
+            {
+               // classic walk-back over aggregates (not bitwise reproducible; for very few chains)
+               st_status(status, s_agg, flag_agg);
+               double carry = 0.0, fac = 1.0;
+               int q = ti.t - 1;
+               const double2 *qp = status - 1;
+               while (true)
+               {
+                  w = ld_status(qp);
+                  while ((int)(status_flag(w) - flag_agg) < 0) { __nanosleep(32); w = ld_status(qp); }
+                  if ((int)(status_flag(w) - flag_incl) >= 0) { carry = fma(fac, w.x, carry); break; }
+                  if (q == 0)
+                  {
+                     while ((int)(status_flag(w) - flag_incl) < 0) { __nanosleep(32); w = ld_status(qp); }
+                     carry = fma(fac, w.x, carry);
+                     break;
+                  }
+                  carry = fma(fac, w.x, carry);
+                  fac *= afull;
+                  if (fac == 0.0) break; // everything further upstream has underflowed out of fp64 range
+                  --q;
+                  --qp;
+               }
+               ctile = carry;
+            }
          }
-         __stcg(a.tile_incl + sidx, fma(s_alast, ctile, s_agg));
-         st_release_u32(a.tile_flag + sidx, flag_incl);
+         st_status(status, fma(s_alast, ctile, s_agg), flag_incl);
          s_ctile = ctile;
       }
-      __syncthreads();
+      __syncthreads(); // (E)
 
       // ---- pass 2: true nodes, written back into the X1 tile (blocked, conflict-free)
       {
@@ -400,20 +444,23 @@ __global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
             ap *= c.alpha;
          }
       }
-      __syncthreads();
+      __syncthreads(); // (F)
 
       // ---- coalesced store
       {
-         double2 *go = a.out[sgn] + row_off;
+         double2 *go = a.out[ti.sgn] + ti.row_off;
 #pragma unroll
          for (int k = 0; k < CPT; ++k)
          {
             const int j = k * THREADS + tid;
-            if (j < valid) __stcs(go + j, s1[slot(j)]);
+            if (j < ti.valid) __stcs(go + j, s1[slot(j)]);
          }
       }
-      __syncthreads(); // smem is reused by the next tile
+      if (tid == 0) s_ticket[buf] = after_next;
+      cur = nxt;
+      buf ^= 1;
    }
+   cp_async_wait<0>();
 }
 
 // ------------------------------------------------------------------------------------------ host side
@@ -421,7 +468,7 @@ template <int KIND, bool CORR, int THREADS>
 static size_t smem_bytes()
 {
    const int narr = 1 + (KIND != KIND_BE ? 1 : 0) + ((KIND == KIND_BDF && CORR) ? 1 : 0);
-   return (size_t)narr * TileShape<THREADS>::SLOTS * sizeof(double2);
+   return (size_t)2 * narr * TileShape<THREADS>::SLOTS * sizeof(double2); // two pipeline buffers
 }
 
 template <int KIND, bool CORR, int THREADS>
