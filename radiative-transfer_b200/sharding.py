@@ -56,3 +56,27 @@ def gather_group_rows(local: np.ndarray, G: int, dist=None, device=None) -> np.n
     for (b, n), t in zip(ranges, outs):
         full[b:b + n] = t[:n].cpu().numpy()
     return full
+
+
+def reduce_scalar(value: float, op: str = "max", dist=None, device=None) -> float:
+    """max / sum of one fp64 scalar over the ranks (device time of a step = max over ranks; units = sum over ranks)."""
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        return float(value)
+    import torch
+    dev = device if device is not None else ("cuda" if dist.get_backend() == "nccl" else "cpu")
+    t = torch.tensor([float(value)], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.SUM)
+    return float(t.item())
+
+
+def reduce_vector_sum(local: np.ndarray, dist=None, device=None) -> np.ndarray:
+    """Element-wise fp64 sum over the ranks of a small vector -- the validation sums of correction.cpp:39-63,100-122
+    (sum_g B_g, sum_g dB/dT_g, sum_g kappa_g B_g) when every rank only contributes the groups it owns."""
+    local = np.ascontiguousarray(local, dtype=np.float64)
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        return local.copy()
+    import torch
+    dev = device if device is not None else ("cuda" if dist.get_backend() == "nccl" else "cpu")
+    t = torch.from_numpy(local.copy()).to(dev)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return t.cpu().numpy()
