@@ -258,12 +258,7 @@ def main():
     tm = s.timing()
     plan = s.plan()
     s.close()
-    ms_max = ms
-    if dist is not None:
-        import torch
-        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_max = float(t.item())
+    ms_max = sharding.reduce_scalar(ms, "max", dist)
     unknown_stages = M * G * N * 4 * K
     value = unknown_stages / (ms_max * 1e-3)
 
@@ -284,12 +279,19 @@ def main():
             nl = tm.sweep_launches[i]
             by_kind[k] = {"launches": int(nl), "avg_ms": tm.sweep_ms[i] / nl,
                           "GBps": BYTES_PER_UNKNOWN[k] * M * N * (tm.unknown_stages / tm.stages / (M * N)) * nl / (tm.sweep_ms[i] * 1e-3) / 1e9}
+    # measured DRAM traffic of the sweep launches (ncu --set full capture, per unknown and stage kind), scaled to the
+    # unknowns one launch of THIS run processes and averaged over the launches like `achieved`
     traffic = None
     tr_path = os.path.join(ROOT, "profiles", "sweep_traffic.json")
-    if os.path.exists(tr_path):
-        traffic = json.load(open(tr_path)).get("dram_bytes_per_launch")
+    n_launches = int(sum(tm.sweep_launches))
+    if os.path.exists(tr_path) and n_launches:
+        per_unknown = json.load(open(tr_path)).get("dram_bytes_per_unknown") or {}
+        if all(k in per_unknown for k in kinds):
+            unknowns_per_launch = tm.unknown_stages / tm.stages
+            traffic = sum(per_unknown[k] * tm.sweep_launches[i] for i, k in enumerate(kinds)) * unknowns_per_launch / n_launches
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
-                "traffic": traffic, "peak_source": peak_src, "kernel": "rtk::sweep_kernel<KIND,CORR,T> (BE,CN,BE,BDF per step)",
+                "traffic": traffic, "algorithmic_bytes_per_launch": (alg_bytes / n_launches) if n_launches else None,
+                "avg_launch_ms": (sweep_ms / n_launches) if n_launches else None, "peak_source": peak_src, "kernel": "rtk::sweep_kernel<KIND,CORR,T> (BE,CN,BE,BDF per step)",
                 "algorithmic_bytes_per_unknown": BYTES_PER_UNKNOWN, "by_kind": by_kind}
     gpu_launches = int(tm.kernel_launches)
 
@@ -311,12 +313,7 @@ def main():
             s2.close()
         finally:
             rt.capi.lib().rt_host_free(pin)
-        wall_max = wall
-        if dist is not None:
-            import torch
-            t = torch.tensor([wall], dtype=torch.float64, device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            wall_max = float(t.item())
+        wall_max = sharding.reduce_scalar(wall, "max", dist)
         e2e = {"value": unknown_stages / wall_max, "unit": UNIT, "h2d_bytes_per_step": int(tm2.h2d_bytes // K),
                "d2h_bytes_per_step": int(tm2.d2h_bytes // K), "wall_s": wall_max,
                "what": "Solver(params) [tables H2D, Planck+correction terms, state init] + solve() of K steps with phi of every "
