@@ -39,6 +39,7 @@ WORKLOADS = {
     "c4": (16, 256, 1 << 20, 2, 1),
     "c5": (32, 4096, 1 << 20, 1, 1),
     "small": (16, 32, 1 << 16, 2, 1),
+    "mid": (16, 64, 1 << 18, 2, 1),
 }
 
 

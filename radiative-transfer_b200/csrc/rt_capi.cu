@@ -58,6 +58,7 @@ struct rt_solver
    double *d_dsig = nullptr, *d_dkap = nullptr, *d_cor1 = nullptr, *d_cor2 = nullptr, *d_cor3 = nullptr;
    double *d_sigma = nullptr, *d_srcB = nullptr, *d_de_ave = nullptr, *d_sums = nullptr;
    double *d_psi_source = nullptr, *d_bdry = nullptr;
+   double *d_coef[3] = {nullptr, nullptr, nullptr}; // per stage kind: Gl*M entries of COEF_ENTRY_DOUBLES doubles
    double sums[3] = {0, 0, 0};
    // batching
    int Gl = 0, Gb = 0, n_batches = 0, Np = 0, tiles_per_row = 0;
@@ -72,7 +73,7 @@ struct rt_solver
    unsigned long long ticket_base = 0;
    unsigned epoch = 0;
    int last_grid = 0;
-   int threads = SWEEP_THREADS_DEFAULT, tile_cells = SWEEP_THREADS_DEFAULT * CELLS_PER_THREAD;
+   int threads = SWEEP_THREADS_DEFAULT, cpt = CELLS_PER_THREAD_DEFAULT, tile_cells = SWEEP_THREADS_DEFAULT * CELLS_PER_THREAD_DEFAULT;
    // results retained across batches (group-major [gl][c]) and per-group diagnostics
    double *d_phi = nullptr, *d_phip = nullptr, *d_F = nullptr;
    double *d_balance = nullptr, *d_left = nullptr, *d_right = nullptr;
@@ -90,6 +91,8 @@ struct rt_solver
    std::vector<EventPair> ev_pool;
    size_t ev_used = 0;
    bool timing_on = true;
+   int ticket_batch = 4;       // tickets per atomic draw (RT_CUDA_TICKET_BATCH)
+   bool l2_prefetch = true;    // RT_CUDA_L2_PREFETCH=0 switches the two-tiles-ahead L2 prefetch off
    bool lookback_walk = false; // RT_CUDA_LOOKBACK=walk: aggregate walk-back (faster with very few rows, not bitwise reproducible)
 };
 
@@ -219,6 +222,20 @@ static int compute_group_tables(rt_solver *s)
                                                   s->d_dEB, s->d_psi_source, s->d_bdry, s->st);
    CK(cudaGetLastError());
    if (download(s, s->sums, s->d_sums, 3)) return 1;
+   // stepper constants per (stage kind, owned group, direction); they never change during a solve
+   CoefArgs c;
+   c.sigma = s->d_sigma; c.srcB = s->d_srcB; c.cor1 = s->d_cor1; c.cor2 = s->d_cor2; c.cor3 = s->d_cor3;
+   c.mu = s->d_mu; c.bdry = s->d_bdry;
+   c.M = p.M; c.G0 = p.group_begin; c.groups = s->Gl;
+   c.dx = p.dx; c.dt = p.dt; c.beta = p.V / C_LIGHT;
+   c.tau = (p.ts_method == 3) ? p.dt / 2. : p.dt; // solver.cpp:708-806: BDF2 stages all advance dt/2
+   const bool corr = p.use_correction && p.V != 0.0;
+   for (int kind = 0; kind < 3; ++kind)
+   {
+      launch_coef_table(kind, corr, c, s->d_coef[kind], s->st);
+      s->tm.kernel_launches++;
+   }
+   CK(cudaGetLastError());
    return 0;
 }
 
@@ -253,7 +270,8 @@ extern "C" int rt_destroy(rt_solver *s)
    double *tabs[] = {s->d_mu, s->d_wt, s->d_e_edge, s->d_kappa, s->d_T, s->d_B, s->d_dBdT, s->d_kappa_edge, s->d_epf,
                      s->d_dEB, s->d_dsig, s->d_dkap, s->d_cor1, s->d_cor2, s->d_cor3, s->d_sigma, s->d_srcB, s->d_de_ave,
                      s->d_sums, s->d_psi_source, s->d_bdry, s->d_phi, s->d_phip, s->d_F,
-                     s->d_balance, s->d_left, s->d_right, s->d_stage, s->d_step_phi[0], s->d_step_phi[1]};
+                     s->d_balance, s->d_left, s->d_right, s->d_stage, s->d_step_phi[0], s->d_step_phi[1],
+                     s->d_coef[0], s->d_coef[1], s->d_coef[2]};
    for (double *t : tabs) if (t) cudaFree(t);
    for (int k = 0; k < 4; ++k) if (s->E[k]) cudaFree(s->E[k]);
    if (s->d_tile_status) cudaFree(s->d_tile_status);
@@ -316,12 +334,24 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
    if (const char *te = getenv("RT_CUDA_SWEEP_THREADS"))
    {
       const int t = atoi(te);
-      if (t == 32 || t == 64 || t == 128 || t == 256) s->threads = t;
+      if (sweep_shape_supported(t, s->cpt)) s->threads = t;
    }
-   s->tile_cells = s->threads * CELLS_PER_THREAD;
+   if (const char *ce = getenv("RT_CUDA_SWEEP_CPT"))
+   {
+      const int c = atoi(ce);
+      if (sweep_shape_supported(s->threads, c)) s->cpt = c;
+   }
+   s->tile_cells = s->threads * s->cpt;
    s->tiles_per_row = (N + s->tile_cells - 1) / s->tile_cells;
    const char *tenv = getenv("RT_CUDA_TIMING");
    s->timing_on = !(tenv && tenv[0] == '0');
+   if (const char *be = getenv("RT_CUDA_TICKET_BATCH"))
+   {
+      const int b = atoi(be);
+      if (b >= 1 && b <= 64) s->ticket_batch = b;
+   }
+   const char *penv = getenv("RT_CUDA_L2_PREFETCH");
+   s->l2_prefetch = !(penv && penv[0] == '0');
    const char *lenv = getenv("RT_CUDA_LOOKBACK");
    s->lookback_walk = lenv && std::strcmp(lenv, "walk") == 0;
 
@@ -336,6 +366,7 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
    CKD(dalloc(&s->d_srcB, G)); CKD(dalloc(&s->d_de_ave, G)); CKD(dalloc(&s->d_sums, 3));
    CKD(dalloc(&s->d_psi_source, (size_t)M * G)); CKD(dalloc(&s->d_bdry, (size_t)M * G));
    CKD(dalloc(&s->d_balance, s->Gl)); CKD(dalloc(&s->d_left, s->Gl)); CKD(dalloc(&s->d_right, s->Gl));
+   for (int k = 0; k < 3; ++k) CKD(dalloc(&s->d_coef[k], (size_t)s->Gl * M * COEF_ENTRY_DOUBLES));
    CKD(dalloc(&s->d_ticket, 1));
    CKC(cudaMemsetAsync(s->d_ticket, 0, sizeof(unsigned long long), s->st));
    CKC(cudaMemsetAsync(s->d_B, 0, G * sizeof(double), s->st));
@@ -484,26 +515,26 @@ static int run_one_stage(rt_solver *s)
    a.x2[0] = a.x2[1] = x2;
    a.xc[0] = a.xc[1] = xc;
    a.out[0] = a.out[1] = s->E[out];
-   a.sigma = s->d_sigma; a.srcB = s->d_srcB; a.cor1 = s->d_cor1; a.cor2 = s->d_cor2; a.cor3 = s->d_cor3;
-   a.mu = s->d_mu; a.bdry = s->d_bdry;
+   a.coef = reinterpret_cast<const double2 *>(s->d_coef[kind] + (size_t)s->batch_start * p.M * COEF_ENTRY_DOUBLES);
    a.tile_status = s->d_tile_status;
-   a.ticket = s->d_ticket; a.ticket_base = s->ticket_base;
+   a.ticket = s->d_ticket; a.ticket_base = s->ticket_base; a.ticket_batch = s->ticket_batch;
    a.epoch = ++s->epoch;
-   a.M = p.M; a.N = p.N; a.Np = s->Np; a.G0 = p.group_begin + s->batch_start;
+   a.M = p.M; a.N = p.N; a.Np = s->Np;
    a.rows = s->batch_groups * p.M;
    a.tiles_per_row = s->tiles_per_row;
    a.reflective_left = (p.bc_left == 2) ? 1 : 0;
    a.n_chains = a.reflective_left ? a.rows / 2 : a.rows;
    a.tiles_per_chain = a.reflective_left ? 2 * s->tiles_per_row : s->tiles_per_row;
    a.lookback_walk = s->lookback_walk ? 1 : 0;
-   a.dx = p.dx; a.tau = tau; a.dt = p.dt; a.beta = p.V / C_LIGHT;
+   a.l2_prefetch = s->l2_prefetch ? 1 : 0;
 
    EventPair *ep;
    if (event_begin(s, kind, &ep)) return 1;
    int grid = 0;
-   CK(launch_sweep(kind, corr, s->threads, a, s->num_sms, s->st, &grid));
+   CK(launch_sweep(kind, corr, s->threads, s->cpt, a, s->num_sms, s->st, &grid));
    if (event_end(s, ep)) return 1;
-   s->ticket_base += (unsigned long long)a.n_chains * a.tiles_per_chain + (unsigned long long)grid;
+   const unsigned long long total_tiles = (unsigned long long)a.n_chains * a.tiles_per_chain;
+   s->ticket_base += (total_tiles + s->ticket_batch - 1) / s->ticket_batch + (unsigned long long)grid;
    s->last_grid = grid;
    s->i_ends = out;
    s->stages_done++;

@@ -28,10 +28,24 @@ constexpr double VALIDATION_TOL = 1.e-6;
 //   The cell average psi = (u+v)/2 is never stored (solver.cpp:352: psi is exactly 0.5*(L+R)).
 // ---------------------------------------------------------------------------------------------
 
-constexpr int SWEEP_THREADS_DEFAULT = 64;  // CTA size of the sweep kernel (32/64/128/256 selectable, RT_CUDA_SWEEP_THREADS)
-constexpr int CELLS_PER_THREAD = 8;          // tile = 8 * threads cells (512 cells = 8 KB of (u,v) per time level)
+constexpr int SWEEP_THREADS_DEFAULT = 64;     // CTA size of the sweep kernel (64/128/256 selectable, RT_CUDA_SWEEP_THREADS)
+constexpr int CELLS_PER_THREAD_DEFAULT = 8;   // cells per thread (4/8, RT_CUDA_SWEEP_CPT); tile = threads * cpt cells
 
 enum StageKind : int { KIND_BE = 0, KIND_CN = 1, KIND_BDF = 2 };
+
+constexpr int COEF_ENTRY_DOUBLES = 18; // sizeof(RowCoef) / 8 (sweep_kernel.cu)
+
+// Inputs of the per-row stepper-constant table (one entry per owned (group, direction) and stage kind).
+struct CoefArgs
+{
+   const double *sigma;  // rho*kappa_g                                   (indexed by GLOBAL group)
+   const double *srcB;   // rho*kappa_g*B_g  (reference: rho*kappa*B, solver.cpp:337)
+   const double *cor1, *cor2, *cor3;
+   const double *mu;     // M
+   const double *bdry;   // M*G inflow values psi_source(i,g) already masked by the BC switch (0 where vacuum)
+   int M, G0, groups;    // G0 = global index of the first owned group
+   double dx, tau, dt, beta;
+};
 
 // Arguments of one stage-sweep launch.
 struct SweepArgs
@@ -42,24 +56,20 @@ struct SweepArgs
    const double2 *x2[2]; // CN/BDF: prev_ends             ; BE: unused
    const double2 *xc[2]; // BDF with live correction: ends before the stage (psi for the source)
    double2 *out[2];      // ends after the stage
-   // per-group tables, indexed by GLOBAL group
-   const double *sigma;  // rho*kappa_g
-   const double *srcB;   // rho*kappa_g*B_g  (reference: rho*kappa*B, solver.cpp:337)
-   const double *cor1, *cor2, *cor3;
-   const double *mu;     // M
-   const double *bdry;   // M*G inflow values psi_source(i,g) already masked by the BC switch (0 where vacuum)
+   const double2 *coef;  // stepper constants of this stage kind, entry `row` of the batch at coef + row*9 (144-byte entries)
    // look-back state
    double2 *tile_status;          // [chains*tiles_per_chain] {value, flag}: flag = epoch*2+1 -> value is the tile's zero-inflow
                                   // aggregate, epoch*2+2 -> value is the true outflow at the tile's last cell
-   unsigned long long *ticket;    // monotonically increasing work counter
+   unsigned long long *ticket;    // monotonically increasing counter of ticket DRAWS (ticket_batch tickets per draw)
    unsigned long long ticket_base;
+   int ticket_batch;
    unsigned int epoch;
-   int M, N, Np, G0;     // G0 = global index of local group 0 of this batch
+   int M, N, Np;
    int rows;             // groups_in_batch * M
    int tiles_per_row;
    int reflective_left;  // 1: mu>0 rows take their inflow from the mirrored mu<0 row of the same stage
    int n_chains, tiles_per_chain;
+   int l2_prefetch;      // 1: bulk-prefetch the tile two tickets ahead into L2
    int lookback_walk;    // 0: deterministic (wait for the predecessor's inclusive value) ; 1: classic aggregate walk-back
-   double dx, tau, dt, beta;
 };
 } // namespace rtk

@@ -49,16 +49,19 @@ __device__ __forceinline__ void cp_async16(void *smem, const void *gmem)
 // striped (coalesced) and the blocked (8 consecutive cells per thread) access patterns conflict-free
 __device__ __forceinline__ int slot(int j) { return j + (j >> 3); }
 
-template <int THREADS>
+template <int THREADS, int CPT_>
 struct TileShape
 {
-   static constexpr int CPT = CELLS_PER_THREAD;
+   static constexpr int CPT = CPT_; // cells per thread: 8 or 4 (4 doubles the warps per shared-memory byte)
    static constexpr int TILE = THREADS * CPT;
    static constexpr int SLOTS = TILE + TILE / 8;
    static constexpr int WARPS = THREADS / 32;
 };
 
-// Per-row stepper constants (identical formulas for both signs of mu, see rt_common.cuh).
+// Per-row stepper constants (identical formulas for both signs of mu, see rt_common.cuh).  They depend on
+// (stage kind, group, direction) only, so they are evaluated ONCE per solver by coef_table_kernel into a table of
+// 144-byte entries; the sweep kernel stages the entry of a tile's row in shared memory with the tile itself
+// (one cp.async group) -- no divisions, no dependent global loads of cross sections on the per-tile critical path.
 struct RowCoef
 {
    double alpha, gamma, id, io; // recurrence factors and d/det, o/det
@@ -67,10 +70,12 @@ struct RowCoef
    double p_uu, p_uv, p_vu, p_vv;     // weights of X2 (prev_ends) in (ru, rv)   [BDF]
    double up1, up2;                   // weights of the upstream old-level outflow nodes X1(j-1).v, X2(j-1).v in ru
    double kbc;                        // boundary multiplier
+   double inflow0;                    // kbc * bdry_cond of this (direction, group): inflow of the row's first cell
 };
+static_assert(sizeof(RowCoef) == COEF_ENTRY_DOUBLES * sizeof(double), "coefficient table entry size");
+static_assert(sizeof(RowCoef) % 16 == 0, "entries are staged with 16-byte cp.async copies");
 
-template <int KIND, bool CORR>
-__device__ __forceinline__ RowCoef make_coef(const SweepArgs &a, int g, int i)
+__device__ __forceinline__ RowCoef make_coef(int kind, bool corr, const CoefArgs &a, int g, int i)
 {
    RowCoef c;
    const double mu = a.mu[i], amu = fabs(mu), sig = a.sigma[g];
@@ -78,7 +83,7 @@ __device__ __forceinline__ RowCoef make_coef(const SweepArgs &a, int g, int i)
    const double hq = 0.5 * ctau * a.dx; // 0.5*c*timestep*dx (solver.cpp:337)
    c.qa = hq * a.srcB[g];
    c.qb = 0.0;
-   if (CORR)
+   if (corr)
    {
       // total_correction = (cor1*psi + cor2)*mu*beta - cor3*mu^2*beta^2 (correction.cpp:392-394), psi = (u+v)/2
       const double mb = mu * a.beta;
@@ -88,7 +93,7 @@ __device__ __forceinline__ RowCoef make_coef(const SweepArgs &a, int g, int i)
    double k, d;
    c.p_uu = c.p_uv = c.p_vu = c.p_vv = 0.0;
    c.up1 = c.up2 = 0.0;
-   if (KIND == KIND_BE)
+   if (kind == KIND_BE)
    {
       // solver.cpp:324-334,344-345,381-382
       k = ctau * amu;
@@ -96,7 +101,7 @@ __device__ __forceinline__ RowCoef make_coef(const SweepArgs &a, int g, int i)
       c.c_uu = 0.5 * a.dx; c.c_uv = 0.0; c.c_vu = 0.0; c.c_vv = 0.5 * a.dx;
       c.kbc = 1.0;
    }
-   else if (KIND == KIND_CN)
+   else if (kind == KIND_CN)
    {
       // solver.cpp:411-425,435-436,469-470
       const double t = 0.5 * ctau * sig;
@@ -125,7 +130,23 @@ __device__ __forceinline__ RowCoef make_coef(const SweepArgs &a, int g, int i)
    c.io = o / det;
    c.alpha = c.io * k;
    c.gamma = c.id * k;
+   c.inflow0 = c.kbc * a.bdry[(size_t)i + (size_t)a.M * g];
    return c;
+}
+
+// one thread per owned (group, direction): table[(gl*M + i)] for gl in [0, groups)
+__global__ void coef_table_kernel(int kind, int corr, CoefArgs a, RowCoef *__restrict__ table)
+{
+   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+   if (idx >= a.groups * a.M) return;
+   const int gl = idx / a.M, i = idx % a.M;
+   table[idx] = make_coef(kind, corr != 0, a, a.G0 + gl, i);
+}
+
+void launch_coef_table(int kind, bool corr, const CoefArgs &a, double *table, cudaStream_t st)
+{
+   const int n = a.groups * a.M;
+   coef_table_kernel<<<(n + 127) / 128, 128, 0, st>>>(kind, corr ? 1 : 0, a, reinterpret_cast<RowCoef *>(table));
 }
 
 // ---- tile status word: {value, flag} in ONE aligned 16-byte word, written and read with single 128-bit
@@ -149,48 +170,56 @@ __device__ __forceinline__ void cp_async8(void *smem, const void *gmem)
    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gmem) : "memory");
 }
+// HBM -> L2 only (no shared-memory landing zone needed): used two tiles ahead of the tile being scanned
+__device__ __forceinline__ void prefetch_l2_bulk(const void *gmem, unsigned bytes)
+{
+   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gmem), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-struct TileInfo
+// Everything the CTA needs to know about one ticket; decoded by ONE thread (the 64-bit divisions are not cheap) and
+// handed to the others through shared memory.
+struct TileDesc
 {
-   int chain, p, row, t, g, i, sgn, tile_start, valid;
-   size_t row_off;
+   long long row_off;    // element offset of the tile's first cell in a time-level buffer
+   long long status_idx; // index of the tile's look-back word
+   int row, p, t, sgn, tile_start, valid;
 };
 
 // ticket -> (tile position p, chain) -> (row, tile in row); p-major so that all chains advance together
-__device__ __forceinline__ TileInfo decode_ticket(const SweepArgs &a, long long ticket, int tile_cells)
+__device__ __forceinline__ TileDesc decode_ticket(const SweepArgs &a, long long ticket, int tile_cells)
 {
-   TileInfo ti;
+   TileDesc ti;
    ti.p = (int)(ticket / a.n_chains);
-   ti.chain = (int)(ticket % a.n_chains);
+   const int chain = (int)(ticket % a.n_chains);
    if (a.reflective_left)
    {
-      const int half_m = a.M >> 1, gl = ti.chain / half_m, pp = ti.chain % half_m;
+      const int half_m = a.M >> 1, gl = chain / half_m, pp = chain % half_m;
       if (ti.p < a.tiles_per_row) { ti.row = gl * a.M + (half_m - 1 - pp); ti.t = ti.p; }
       else { ti.row = gl * a.M + (half_m + pp); ti.t = ti.p - a.tiles_per_row; }
    }
-   else { ti.row = ti.chain; ti.t = ti.p; }
-   const int gl = ti.row / a.M;
-   ti.i = ti.row % a.M;
-   ti.g = a.G0 + gl;
-   ti.sgn = (ti.i >= (a.M >> 1)) ? 1 : 0;
+   else { ti.row = chain; ti.t = ti.p; }
+   ti.sgn = ((ti.row % a.M) >= (a.M >> 1)) ? 1 : 0;
    ti.tile_start = ti.t * tile_cells;
    ti.valid = min(tile_cells, a.N - ti.tile_start);
-   ti.row_off = (size_t)ti.row * a.Np + ti.tile_start;
+   ti.row_off = (long long)ti.row * a.Np + ti.tile_start;
+   ti.status_idx = (long long)chain * a.tiles_per_chain + ti.p;
    return ti;
 }
 
-template <int KIND, bool CORR, int THREADS>
+// (A single-buffered variant that relied on the L2 prefetch alone and doubled the resident CTAs was measured
+// 7 % slower on C4 -- gpurun_out exp2 -- and removed.)
+template <int KIND, bool CORR, int THREADS, int CPT>
 __global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
 {
-   using TS = TileShape<THREADS>;
-   constexpr int CPT = TS::CPT, TILE = TS::TILE, SLOTS = TS::SLOTS, WARPS = TS::WARPS;
+   using TS = TileShape<THREADS, CPT>;
+   constexpr int TILE = TS::TILE, SLOTS = TS::SLOTS, WARPS = TS::WARPS;
    constexpr bool NEED_X2 = (KIND != KIND_BE);
    constexpr bool NEED_XC = (KIND == KIND_BDF) && CORR;
    constexpr int NARR = 1 + (NEED_X2 ? 1 : 0) + (NEED_XC ? 1 : 0);
-   static_assert(CPT == 8, "chunk power assumes 8 cells per thread");
+   static_assert(CPT == 8 || CPT == 4, "the padded shared-memory layout is conflict-free for 4 or 8 cells per thread");
    static_assert((WARPS & (WARPS - 1)) == 0, "WARPS must be a power of two");
 
    extern __shared__ double2 smem[]; // [2 pipeline buffers][NARR arrays][SLOTS]
@@ -198,13 +227,15 @@ __global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
    __shared__ double s_halo[2][2];
    __shared__ double s_agg, s_alast, s_ctile;
    __shared__ long long s_ticket[2];
+   __shared__ TileDesc s_desc[3]; // [0],[1]: the tiles in the two pipeline buffers ; [2]: the tile two tickets ahead
+   __shared__ __align__(16) RowCoef s_coef[2];
 
    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
    const unsigned flag_agg = a.epoch * 2u + 1u, flag_incl = a.epoch * 2u + 2u;
    const long long total_tiles = (long long)a.n_chains * a.tiles_per_chain;
 
    // coalesced 16-byte async copies of one tile's time levels into pipeline buffer b
-   auto issue_loads = [&](const TileInfo &ti, int b) {
+   auto issue_loads = [&](const TileDesc &ti, int b) {
       double2 *d1 = smem + (size_t)b * NARR * SLOTS;
       double2 *d2 = d1 + SLOTS;
       double2 *dc = d1 + (NEED_X2 ? 2 : 1) * SLOTS;
@@ -228,6 +259,9 @@ __global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
             if (NEED_XC) dc[s] = make_double2(0.0, 0.0);
          }
       }
+      // the row's stepper constants travel with the tile (9 x 16 bytes)
+      if (tid < (int)(sizeof(RowCoef) / 16))
+         cp_async16(reinterpret_cast<double2 *>(&s_coef[b]) + tid, a.coef + (size_t)ti.row * (sizeof(RowCoef) / 16) + tid);
       if (NEED_X2 && tid == 0)
       {
          // old-time-level outflow nodes of the cell upstream of the tile (CN: prev ; BDF: half and prev)
@@ -241,38 +275,74 @@ __global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
       }
    };
 
+   // one thread: pull the time levels of a tile two tickets ahead from HBM into L2 (bulk prefetch, 16-byte granules)
+   auto prefetch_tile = [&](const TileDesc &ti) {
+      if (!a.l2_prefetch) return;
+      const unsigned bytes = (unsigned)ti.valid * (unsigned)sizeof(double2);
+      prefetch_l2_bulk(a.x1[ti.sgn] + ti.row_off, bytes);
+      if (NEED_X2) prefetch_l2_bulk(a.x2[ti.sgn] + ti.row_off, bytes);
+      if (NEED_XC) prefetch_l2_bulk(a.xc[ti.sgn] + ti.row_off, bytes);
+   };
+
    // every CTA draws tickets until it has seen ONE that is past the end (the host's ticket accounting relies on it)
-   long long last_taken = 0;
+   // Tickets are drawn in batches of a.ticket_batch consecutive tickets per atomic (one atomic per tile on a single
+   // address would be ~4e8 atomics/s at 6 TB/s with 8 KB tiles).  A batch is consumed in increasing order, so the
+   // dependency-order argument above still holds.  Host accounting: the counter advances by one per draw; every CTA
+   // makes exactly ONE draw that lies past the end (at the latest when it exits).
+   long long last_taken = 0, q_next = 0, q_end = 0;
+   bool drew_past_end = false;
    auto take_ticket = [&]() -> long long {
       if (last_taken >= total_tiles) return last_taken;
-      last_taken = (long long)(atomicAdd(a.ticket, 1ull) - a.ticket_base);
+      if (q_next == q_end)
+      {
+         q_next = (long long)(atomicAdd(a.ticket, 1ull) - a.ticket_base) * a.ticket_batch;
+         q_end = q_next + a.ticket_batch;
+         if (q_next >= total_tiles) drew_past_end = true;
+      }
+      last_taken = q_next++;
       return last_taken;
    };
 
-   // ---- prologue: first tile in flight, second ticket drawn
-   if (tid == 0) s_ticket[0] = take_ticket();
+   // ---- prologue: two tickets drawn and decoded, the first tile in flight, a third ticket drawn
+   long long ahead = 0; // thread 0: the ticket two tiles ahead (already drawn, value known)
+   if (tid == 0)
+   {
+      const long long t0 = take_ticket(), t1 = take_ticket();
+      s_ticket[0] = t0;
+      s_ticket[1] = t1;
+      if (t0 < total_tiles) s_desc[0] = decode_ticket(a, t0, TILE);
+      if (t1 < total_tiles) s_desc[1] = decode_ticket(a, t1, TILE);
+      ahead = take_ticket();
+   }
    __syncthreads();
    long long cur = s_ticket[0];
    int buf = 0;
-   if (cur < total_tiles) issue_loads(decode_ticket(a, cur, TILE), 0);
+   if (cur < total_tiles) issue_loads(s_desc[0], 0);
    cp_async_commit();
-   if (tid == 0) s_ticket[1] = take_ticket();
 
    while (cur < total_tiles)
    {
       __syncthreads(); // (A) next ticket visible ; everybody is done with the other pipeline buffer
       const long long nxt = s_ticket[buf ^ 1];
-      if (nxt < total_tiles) issue_loads(decode_ticket(a, nxt, TILE), buf ^ 1);
+      if (nxt < total_tiles) issue_loads(s_desc[buf ^ 1], buf ^ 1);
       cp_async_commit();
-      long long after_next = 0;
-      if (tid == 0) after_next = take_ticket(); // latency hidden behind this tile's work; published at the loop end
+      long long newer = 0;
+      if (tid == 0)
+      {
+         if (ahead < total_tiles)
+         {
+            const TileDesc d_ahead = decode_ticket(a, ahead, TILE);
+            prefetch_tile(d_ahead); // HBM -> L2 for the tile after next
+            s_desc[2] = d_ahead;
+         }
+         newer = take_ticket(); // three ahead; latency hidden behind this tile's work, consumed at the loop end
+      }
 
-      const TileInfo ti = decode_ticket(a, cur, TILE);
-      const RowCoef c = make_coef<KIND, CORR>(a, ti.g, ti.i);
+      const TileDesc ti = s_desc[buf];
       double2 *s1 = smem + (size_t)buf * NARR * SLOTS; // X1 tile, later the result tile
       double2 *s2 = s1 + SLOTS;                          // X2 tile
       double2 *sc = s1 + (NEED_X2 ? 2 : 1) * SLOTS;      // ends-before-stage tile for the BDF correction source
-      double2 *status = a.tile_status + ((size_t)ti.chain * a.tiles_per_chain + ti.p);
+      double2 *status = a.tile_status + ti.status_idx;
 
       // early look-back probe: by the time the local scan is done the predecessor's word has arrived
       double2 early = make_double2(0.0, 0.0);
@@ -280,6 +350,23 @@ __global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
 
       cp_async_wait<1>(); // this tile's copies (the group before the prefetch) have landed
       __syncthreads();    // (B)
+      // the row's constants from shared memory; entries that are structurally fixed for this stage kind are folded
+      // at compile time (BE: no cross terms, no X2 ; CN: no X2 cell terms ; symmetric / antisymmetric pairs)
+      RowCoef c;
+      {
+         const RowCoef &cs = s_coef[buf];
+         c.alpha = cs.alpha; c.gamma = cs.gamma; c.id = cs.id; c.io = cs.io;
+         c.qa = cs.qa;
+         c.qb = CORR ? cs.qb : 0.0;
+         c.c_uu = cs.c_uu; c.c_vv = c.c_uu;
+         c.c_uv = (KIND == KIND_BE) ? 0.0 : cs.c_uv; c.c_vu = -c.c_uv;
+         c.p_uu = (KIND == KIND_BDF) ? cs.p_uu : 0.0; c.p_vv = c.p_uu;
+         c.p_uv = (KIND == KIND_BDF) ? cs.p_uv : 0.0; c.p_vu = -c.p_uv;
+         c.up1 = (KIND == KIND_BDF) ? cs.up1 : 0.0;
+         c.up2 = (KIND != KIND_BE) ? cs.up2 : 0.0;
+         c.kbc = (KIND == KIND_BE) ? 1.0 : (KIND == KIND_CN ? 2.0 : 6.0);
+         c.inflow0 = cs.inflow0;
+      }
 
       // ---- pass 1: per-cell beta_j / U_j and the thread-local scan with zero inflow
       double wl[CPT], U[CPT];
@@ -325,9 +412,9 @@ __global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
       }
 
       // ---- block scan of the chunk aggregates (factor alpha^CPT per chunk)
-      const double a2 = c.alpha * c.alpha, a4 = a2 * a2, a8 = a4 * a4;
+      const double a2 = c.alpha * c.alpha, a4 = a2 * a2, achunk = (CPT == 8) ? a4 * a4 : a4; // alpha^CPT
       double pw[5];
-      double incl = wl[CPT - 1], f = a8;
+      double incl = wl[CPT - 1], f = achunk;
 #pragma unroll
       for (int s = 0; s < 5; ++s)
       {
@@ -363,7 +450,7 @@ __global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
       // ---- tile aggregate (zero-inflow value and inflow factor at the tile's last valid cell)
       if (ti.valid == TILE)
       {
-         if (tid == THREADS - 1) { s_agg = fma(a8, E_t, wl[CPT - 1]); s_alast = afull; }
+         if (tid == THREADS - 1) { s_agg = fma(achunk, E_t, wl[CPT - 1]); s_alast = afull; }
       }
       else
       {
@@ -385,7 +472,7 @@ __global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
       if (tid == 0)
       {
          double ctile;
-         if (ti.p == 0) ctile = c.kbc * a.bdry[(size_t)ti.i + (size_t)a.M * ti.g];
+         if (ti.p == 0) ctile = c.inflow0;
          else
          {
             const bool junction = (ti.t == 0); // reflective: first tile of the mu>0 row, fed by the mirrored mu<0 row
@@ -456,27 +543,33 @@ __global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
             if (j < ti.valid) __stcs(go + j, s1[slot(j)]);
          }
       }
-      if (tid == 0) s_ticket[buf] = after_next;
+      if (tid == 0)
+      {
+         s_ticket[buf] = ahead;
+         if (ahead < total_tiles) s_desc[buf] = s_desc[2];
+         ahead = newer;
+      }
       cur = nxt;
       buf ^= 1;
    }
    cp_async_wait<0>();
+   if (tid == 0 && !drew_past_end) atomicAdd(a.ticket, 1ull);
 }
 
 // ------------------------------------------------------------------------------------------ host side
-template <int KIND, bool CORR, int THREADS>
+template <int KIND, bool CORR, int THREADS, int CPT>
 static size_t smem_bytes()
 {
    const int narr = 1 + (KIND != KIND_BE ? 1 : 0) + ((KIND == KIND_BDF && CORR) ? 1 : 0);
-   return (size_t)2 * narr * TileShape<THREADS>::SLOTS * sizeof(double2); // two pipeline buffers
+   return (size_t)2 * narr * TileShape<THREADS, CPT>::SLOTS * sizeof(double2); // two pipeline buffers
 }
 
-template <int KIND, bool CORR, int THREADS>
+template <int KIND, bool CORR, int THREADS, int CPT>
 static cudaError_t launch_one(const SweepArgs &a, int num_sms, cudaStream_t st, int *grid_out)
 {
    static int ctas_per_sm = -1;
-   const size_t smem = smem_bytes<KIND, CORR, THREADS>();
-   auto kern = sweep_kernel<KIND, CORR, THREADS>;
+   const size_t smem = smem_bytes<KIND, CORR, THREADS, CPT>();
+   auto kern = sweep_kernel<KIND, CORR, THREADS, CPT>;
    if (ctas_per_sm < 0)
    {
       cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -495,29 +588,37 @@ static cudaError_t launch_one(const SweepArgs &a, int num_sms, cudaStream_t st, 
    return cudaGetLastError();
 }
 
-template <int T>
-static cudaError_t launch_threads(int kind, bool corr, const SweepArgs &a, int num_sms, cudaStream_t st, int *grid_out)
+template <int T, int CPT>
+static cudaError_t launch_shape(int kind, bool corr, const SweepArgs &a, int num_sms, cudaStream_t st, int *grid_out)
 {
    switch (kind * 2 + (corr ? 1 : 0))
    {
-   case 0: return launch_one<KIND_BE, false, T>(a, num_sms, st, grid_out);
-   case 1: return launch_one<KIND_BE, true, T>(a, num_sms, st, grid_out);
-   case 2: return launch_one<KIND_CN, false, T>(a, num_sms, st, grid_out);
-   case 3: return launch_one<KIND_CN, true, T>(a, num_sms, st, grid_out);
-   case 4: return launch_one<KIND_BDF, false, T>(a, num_sms, st, grid_out);
-   case 5: return launch_one<KIND_BDF, true, T>(a, num_sms, st, grid_out);
+   case 0: return launch_one<KIND_BE, false, T, CPT>(a, num_sms, st, grid_out);
+   case 1: return launch_one<KIND_BE, true, T, CPT>(a, num_sms, st, grid_out);
+   case 2: return launch_one<KIND_CN, false, T, CPT>(a, num_sms, st, grid_out);
+   case 3: return launch_one<KIND_CN, true, T, CPT>(a, num_sms, st, grid_out);
+   case 4: return launch_one<KIND_BDF, false, T, CPT>(a, num_sms, st, grid_out);
+   case 5: return launch_one<KIND_BDF, true, T, CPT>(a, num_sms, st, grid_out);
    }
    return cudaErrorInvalidValue;
 }
 
-cudaError_t launch_sweep(int kind, bool corr, int threads, const SweepArgs &a, int num_sms, cudaStream_t st, int *grid_out)
+bool sweep_shape_supported(int threads, int cpt)
 {
-   switch (threads)
+   return (threads == 64 || threads == 128 || threads == 256) && (cpt == 4 || cpt == 8);
+}
+
+cudaError_t launch_sweep(int kind, bool corr, int threads, int cpt, const SweepArgs &a, int num_sms, cudaStream_t st,
+                         int *grid_out)
+{
+   switch (threads * 16 + cpt)
    {
-   case 32: return launch_threads<32>(kind, corr, a, num_sms, st, grid_out);
-   case 64: return launch_threads<64>(kind, corr, a, num_sms, st, grid_out);
-   case 128: return launch_threads<128>(kind, corr, a, num_sms, st, grid_out);
-   case 256: return launch_threads<256>(kind, corr, a, num_sms, st, grid_out);
+   case 64 * 16 + 8: return launch_shape<64, 8>(kind, corr, a, num_sms, st, grid_out);
+   case 64 * 16 + 4: return launch_shape<64, 4>(kind, corr, a, num_sms, st, grid_out);
+   case 128 * 16 + 8: return launch_shape<128, 8>(kind, corr, a, num_sms, st, grid_out);
+   case 128 * 16 + 4: return launch_shape<128, 4>(kind, corr, a, num_sms, st, grid_out);
+   case 256 * 16 + 8: return launch_shape<256, 8>(kind, corr, a, num_sms, st, grid_out);
+   case 256 * 16 + 4: return launch_shape<256, 4>(kind, corr, a, num_sms, st, grid_out);
    }
    return cudaErrorInvalidValue;
 }

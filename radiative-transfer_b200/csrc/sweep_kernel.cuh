@@ -6,7 +6,11 @@ namespace rtk
 {
 // kind: KIND_BE / KIND_CN / KIND_BDF ; corr: correction source live (use_correction && V != 0).
 // Launches min(total tiles, num_sms * resident CTAs per SM) persistent CTAs on `st`.
-// The caller must advance its ticket base by (n_chains*tiles_per_chain + *grid_out) afterwards.
-// threads: CTA size 64 / 128 / 256 (tile = 8 * threads cells)
-cudaError_t launch_sweep(int kind, bool corr, int threads, const SweepArgs &a, int num_sms, cudaStream_t st, int *grid_out);
+// The caller must advance its ticket base by ceil(n_chains*tiles_per_chain / ticket_batch) + *grid_out afterwards.
+// Tile shape: threads (64 / 128 / 256) x cells per thread (4 / 8); tile = threads * cpt cells.
+bool sweep_shape_supported(int threads, int cpt);
+// table[(gl*M + i)*COEF_ENTRY_DOUBLES ...] for the a.groups owned groups: stepper constants of stage `kind`
+void launch_coef_table(int kind, bool corr, const CoefArgs &a, double *table, cudaStream_t st);
+cudaError_t launch_sweep(int kind, bool corr, int threads, int cpt, const SweepArgs &a, int num_sms, cudaStream_t st,
+                         int *grid_out);
 } // namespace rtk
