@@ -61,9 +61,10 @@ struct rt_solver
    double *d_coef[3] = {nullptr, nullptr, nullptr}; // per stage kind: Gl*M entries of COEF_ENTRY_DOUBLES doubles
    double sums[3] = {0, 0, 0};
    // batching
-   int Gl = 0, Gb = 0, n_batches = 0, Np = 0, tiles_per_row = 0;
+   int Gl = 0, Gb = 0, n_batches = 0, Np = 0;
    size_t buf_elems = 0; // double2 elements per time-level buffer
    double2 *E[4] = {nullptr, nullptr, nullptr, nullptr};
+   SweepMaps maps[3]; // per stage kind (tile shapes may differ): tensor maps of E[0..3]
    int i_ends = 0, i_prev = -1, i_half_neg = -1, i_half_pos = -1;
    int batch_start = 0, batch_groups = 0; // local group range of the batch currently on the device
    int stages_done = 0;
@@ -73,7 +74,10 @@ struct rt_solver
    unsigned long long ticket_base = 0;
    unsigned epoch = 0;
    int last_grid = 0;
-   int threads = SWEEP_THREADS_DEFAULT, cpt = CELLS_PER_THREAD_DEFAULT, tile_cells = SWEEP_THREADS_DEFAULT * CELLS_PER_THREAD_DEFAULT;
+   // tile shape per stage kind {BE, CN, BDF}: CTA size, cells per thread, X1 ring depth (0 = automatic)
+   // (measured on C4, gpurun exp8/exp9: 64 x 8 is best or equal for all three kinds)
+   int threads[3] = {64, 64, 64}, cpt[3] = {8, 8, 8}, ring[3] = {0, 0, 0};
+   int tile_cells[3] = {512, 512, 512}, tiles_per_row[3] = {0, 0, 0}, max_tiles_per_row = 0;
    // results retained across batches (group-major [gl][c]) and per-group diagnostics
    double *d_phi = nullptr, *d_phip = nullptr, *d_F = nullptr;
    double *d_balance = nullptr, *d_left = nullptr, *d_right = nullptr;
@@ -91,7 +95,7 @@ struct rt_solver
    std::vector<EventPair> ev_pool;
    size_t ev_used = 0;
    bool timing_on = true;
-   int ticket_batch = 4;       // tickets per atomic draw (RT_CUDA_TICKET_BATCH)
+   int ticket_batch = 8;       // tickets per atomic draw (RT_CUDA_TICKET_BATCH)
    bool l2_prefetch = true;    // RT_CUDA_L2_PREFETCH=0 switches the two-tiles-ahead L2 prefetch off
    bool lookback_walk = false; // RT_CUDA_LOOKBACK=walk: aggregate walk-back (faster with very few rows, not bitwise reproducible)
 };
@@ -331,18 +335,27 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
    s->num_sms = prop.multiProcessorCount;
    s->Gl = p->group_count;
    s->Np = (N + 7) & ~7;
-   if (const char *te = getenv("RT_CUDA_SWEEP_THREADS"))
+   // RT_CUDA_SWEEP_THREADS / _CPT / _RING: one value for all stage kinds or "be,cn,bdf"
+   auto env3 = [](const char *name, int out[3]) {
+      const char *e = getenv(name);
+      if (!e) return;
+      int v[3];
+      const int got = sscanf(e, "%d,%d,%d", &v[0], &v[1], &v[2]);
+      if (got == 1) v[1] = v[2] = v[0];
+      if (got == 1 || got == 3) for (int k = 0; k < 3; ++k) out[k] = v[k];
+   };
+   int want_t[3] = {s->threads[0], s->threads[1], s->threads[2]}, want_c[3] = {s->cpt[0], s->cpt[1], s->cpt[2]};
+   env3("RT_CUDA_SWEEP_THREADS", want_t);
+   env3("RT_CUDA_SWEEP_CPT", want_c);
+   env3("RT_CUDA_SWEEP_RING", s->ring);
+   for (int k = 0; k < 3; ++k)
    {
-      const int t = atoi(te);
-      if (sweep_shape_supported(t, s->cpt)) s->threads = t;
+      if (sweep_shape_supported(want_t[k], want_c[k])) { s->threads[k] = want_t[k]; s->cpt[k] = want_c[k]; }
+      if (s->ring[k] != 2 && s->ring[k] != 3) s->ring[k] = 0;
+      s->tile_cells[k] = s->threads[k] * s->cpt[k];
+      s->tiles_per_row[k] = (N + s->tile_cells[k] - 1) / s->tile_cells[k];
+      s->max_tiles_per_row = std::max(s->max_tiles_per_row, s->tiles_per_row[k]);
    }
-   if (const char *ce = getenv("RT_CUDA_SWEEP_CPT"))
-   {
-      const int c = atoi(ce);
-      if (sweep_shape_supported(s->threads, c)) s->cpt = c;
-   }
-   s->tile_cells = s->threads * s->cpt;
-   s->tiles_per_row = (N + s->tile_cells - 1) / s->tile_cells;
    const char *tenv = getenv("RT_CUDA_TIMING");
    s->timing_on = !(tenv && tenv[0] == '0');
    if (const char *be = getenv("RT_CUDA_TICKET_BATCH"))
@@ -383,7 +396,7 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
    // ---- memory plan: 4 time-level buffers of (u,v) per unknown + look-back state
    size_t free_b = 0, total_b = 0;
    CKC(cudaMemGetInfo(&free_b, &total_b));
-   const size_t per_group = (size_t)4 * M * s->Np * sizeof(double2) + (size_t)M * s->tiles_per_row * 20;
+   const size_t per_group = (size_t)4 * M * s->Np * sizeof(double2) + (size_t)M * s->max_tiles_per_row * 20;
    const size_t reserve = (size_t)1 << 30; // results staging, allocator slack
    int gb = p->groups_per_batch;
    if (gb <= 0)
@@ -406,8 +419,12 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
    s->Gb = gb;
    s->n_batches = (s->Gl + gb - 1) / gb;
    s->buf_elems = (size_t)gb * M * s->Np;
-   for (int k = 0; k < 4; ++k) CKD(dalloc(&s->E[k], s->buf_elems));
-   const size_t ntiles = (size_t)gb * M * s->tiles_per_row;
+   for (int k = 0; k < 4; ++k)
+   {
+      CKD(dalloc(&s->E[k], s->buf_elems));
+      for (int kind = 0; kind < 3; ++kind) CKC(make_tile_map(&s->maps[kind].m[k], s->E[k], gb * M, s->Np, s->tile_cells[kind]));
+   }
+   const size_t ntiles = (size_t)gb * M * s->max_tiles_per_row;
    CKD(dalloc(&s->d_tile_status, ntiles));
    CKC(cudaMemsetAsync(s->d_tile_status, 0, ntiles * sizeof(double2), s->st));
    if (s->n_batches > 1)
@@ -429,10 +446,10 @@ extern "C" int rt_get_plan(const rt_solver *s, rt_plan *plan)
    plan->groups_per_batch = s->Gb;
    plan->n_batches = s->n_batches;
    plan->resident = s->n_batches == 1;
-   plan->tile_cells = s->tile_cells;
-   plan->tiles_per_row = s->tiles_per_row;
+   plan->tile_cells = s->tile_cells[KIND_BE];
+   plan->tiles_per_row = s->tiles_per_row[KIND_BE];
    plan->sweep_grid = s->last_grid;
-   plan->sweep_block = s->threads;
+   plan->sweep_block = s->threads[KIND_BE];
    plan->bytes_per_group = (size_t)4 * s->p.M * s->Np * sizeof(double2);
    plan->state_bytes = 4 * s->buf_elems * sizeof(double2);
    cudaSetDevice(s->p.device);
@@ -457,81 +474,79 @@ static int run_one_stage(rt_solver *s)
    const rt_params &p = s->p;
    const int it = s->stages_done;
    int kind, out;
-   double tau;
-   const double2 *x1n, *x1p, *x2 = nullptr, *xc = nullptr;
+   int i1n, i1p, i2 = -1, ic = -1; // buffer indices: X1 for mu<0 / mu>0 rows, X2, XC
    const bool corr = p.use_correction && p.V != 0.0; // V == 0 makes total_correction exactly zero
    if (p.ts_method == 1)
    {
-      kind = KIND_BE; tau = p.dt;
+      kind = KIND_BE;
       out = pick_free(s->i_ends, -1, -1, -1);
-      x1n = x1p = s->E[s->i_ends];
+      i1n = i1p = s->i_ends;
       s->i_prev = s->i_ends; // prev_ends = ends (solver.cpp:624), by aliasing instead of copying
    }
    else if (p.ts_method == 2)
    {
-      kind = KIND_CN; tau = p.dt;
+      kind = KIND_CN;
       out = pick_free(s->i_ends, -1, -1, -1);
-      x1n = x1p = x2 = s->E[s->i_ends];
+      i1n = i1p = i2 = s->i_ends;
       s->i_prev = s->i_ends;
    }
    else
    {
-      tau = p.dt / 2.;
       switch (it % 4)
       {
       case 0: // BE predictor; prev_ends = ends
          kind = KIND_BE;
          out = pick_free(s->i_ends, s->i_half_neg, s->i_half_pos, -1);
-         x1n = x1p = s->E[s->i_ends];
+         i1n = i1p = s->i_ends;
          s->i_prev = s->i_ends;
          break;
       case 1: // CN corrector; afterwards half_ends = CN result for mu<0 rows, stage-0 result for mu>0 rows
          kind = KIND_CN;
          out = pick_free(s->i_ends, s->i_prev, -1, -1);
-         x1n = x1p = s->E[s->i_ends];
-         x2 = s->E[s->i_prev];
+         i1n = i1p = s->i_ends;
+         i2 = s->i_prev;
          s->i_half_pos = s->i_ends;
          s->i_half_neg = out;
          break;
       case 2: // second BE predictor
          kind = KIND_BE;
          out = pick_free(s->i_ends, s->i_prev, s->i_half_neg, s->i_half_pos);
-         x1n = x1p = s->E[s->i_ends];
+         i1n = i1p = s->i_ends;
          break;
       default: // BDF corrector, written in place over the stage-2 result (only read for the correction source, same cell)
          kind = KIND_BDF;
          out = s->i_ends;
-         x1n = s->E[s->i_half_neg];
-         x1p = s->E[s->i_half_pos];
-         x2 = s->E[s->i_prev];
-         xc = s->E[s->i_ends];
+         i1n = s->i_half_neg;
+         i1p = s->i_half_pos;
+         i2 = s->i_prev;
+         ic = s->i_ends;
          break;
       }
    }
    if (out < 0) return fail("internal: no free time-level buffer");
 
    SweepArgs a;
-   a.x1[0] = x1n; a.x1[1] = x1p;
-   a.x2[0] = a.x2[1] = x2;
-   a.xc[0] = a.xc[1] = xc;
-   a.out[0] = a.out[1] = s->E[out];
+   a.x1[0] = s->E[i1n]; a.x1[1] = s->E[i1p];
+   a.x2 = i2 >= 0 ? s->E[i2] : nullptr;
+   a.xc = ic >= 0 ? s->E[ic] : nullptr;
+   a.ix1[0] = i1n; a.ix1[1] = i1p; a.ix2 = i2 >= 0 ? i2 : 0; a.ixc = ic >= 0 ? ic : 0; a.iout = out;
    a.coef = reinterpret_cast<const double2 *>(s->d_coef[kind] + (size_t)s->batch_start * p.M * COEF_ENTRY_DOUBLES);
    a.tile_status = s->d_tile_status;
    a.ticket = s->d_ticket; a.ticket_base = s->ticket_base; a.ticket_batch = s->ticket_batch;
    a.epoch = ++s->epoch;
    a.M = p.M; a.N = p.N; a.Np = s->Np;
    a.rows = s->batch_groups * p.M;
-   a.tiles_per_row = s->tiles_per_row;
+   a.tiles_per_row = s->tiles_per_row[kind];
    a.reflective_left = (p.bc_left == 2) ? 1 : 0;
    a.n_chains = a.reflective_left ? a.rows / 2 : a.rows;
-   a.tiles_per_chain = a.reflective_left ? 2 * s->tiles_per_row : s->tiles_per_row;
+   a.tiles_per_chain = a.reflective_left ? 2 * a.tiles_per_row : a.tiles_per_row;
    a.lookback_walk = s->lookback_walk ? 1 : 0;
    a.l2_prefetch = s->l2_prefetch ? 1 : 0;
 
    EventPair *ep;
    if (event_begin(s, kind, &ep)) return 1;
    int grid = 0;
-   CK(launch_sweep(kind, corr, s->threads, s->cpt, a, s->num_sms, s->st, &grid));
+   CK(launch_sweep(kind, corr, s->threads[kind], s->cpt[kind], s->ring[kind], s->maps[kind], a, s->num_sms, s->st, &grid));
    if (event_end(s, ep)) return 1;
    const unsigned long long total_tiles = (unsigned long long)a.n_chains * a.tiles_per_chain;
    s->ticket_base += (total_tiles + s->ticket_batch - 1) / s->ticket_batch + (unsigned long long)grid;

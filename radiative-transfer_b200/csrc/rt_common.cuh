@@ -1,5 +1,6 @@
 // rt_common.cuh -- shared definitions for the sm_100a kernels of librt_cuda.
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -28,8 +29,6 @@ constexpr double VALIDATION_TOL = 1.e-6;
 //   The cell average psi = (u+v)/2 is never stored (solver.cpp:352: psi is exactly 0.5*(L+R)).
 // ---------------------------------------------------------------------------------------------
 
-constexpr int SWEEP_THREADS_DEFAULT = 64;     // CTA size of the sweep kernel (64/128/256 selectable, RT_CUDA_SWEEP_THREADS)
-constexpr int CELLS_PER_THREAD_DEFAULT = 8;   // cells per thread (4/8, RT_CUDA_SWEEP_CPT); tile = threads * cpt cells
 
 enum StageKind : int { KIND_BE = 0, KIND_CN = 1, KIND_BDF = 2 };
 
@@ -47,15 +46,23 @@ struct CoefArgs
    double dx, tau, dt, beta;
 };
 
+// Tensor maps of the four rotating time-level buffers (SWIZZLE_128B tile boxes), passed as a __grid_constant__ kernel
+// parameter; SweepArgs::ix1/ix2/ixc/iout index into it.
+struct alignas(64) SweepMaps
+{
+   CUtensorMap m[4];
+};
+
 // Arguments of one stage-sweep launch.
 struct SweepArgs
 {
-   // time levels, per direction sign s (0: mu<0 rows, 1: mu>0 rows) because the BDF stage reads a
-   // different `half` buffer for the two signs.  All are row-indexed with pitch Np.
+   // time levels; X1 per direction sign s (0: mu<0 rows, 1: mu>0 rows) because the BDF stage reads a different `half`
+   // buffer for the two signs.  Raw pointers (row-indexed with pitch Np) for the L2 prefetch and the
+   // one-cell halo copies; the tiles themselves move through the tensor maps.
    const double2 *x1[2]; // BE/CN: ends before the stage ; BDF: half_ends
-   const double2 *x2[2]; // CN/BDF: prev_ends             ; BE: unused
-   const double2 *xc[2]; // BDF with live correction: ends before the stage (psi for the source)
-   double2 *out[2];      // ends after the stage
+   const double2 *x2;    // CN/BDF: prev_ends             ; BE: unused
+   const double2 *xc;    // BDF with live correction: ends before the stage (psi for the source)
+   int ix1[2], ix2, ixc, iout; // the same buffers (and the output buffer) as indices into SweepMaps::m
    const double2 *coef;  // stepper constants of this stage kind, entry `row` of the batch at coef + row*9 (144-byte entries)
    // look-back state
    double2 *tile_status;          // [chains*tiles_per_chain] {value, flag}: flag = epoch*2+1 -> value is the tile's zero-inflow

@@ -1,4 +1,4 @@
-// sweep_kernel.cu -- the stage sweep (BE / CN / BDF) as a single-pass affine-recurrence scan.
+// sweep_kernel.cu -- the stage sweep (BE / CN / BDF) as a single-pass affine-recurrence scan, fed by TMA.
 //
 // What the reference does (src/solver.cpp:628-811 with the steppers at 319-587): for every
 // direction i and group g it walks the N cells in upwind order and solves a 2x2 system per cell;
@@ -12,20 +12,30 @@
 //
 // where beta_j, U_j depend only on old time levels of cell j (and, for CN/BDF, on old-time-level
 // outflow nodes of cell j-1).  alpha is constant along a row (uniform rho, kappa_g, dx).  Rows are
-// cut into tiles of TILE cells; a tile is scanned by one CTA (thread-serial chunks of 8 cells,
+// cut into tiles of TILE cells; a tile is scanned by one CTA (thread-serial chunks of CPT cells,
 // warp-shuffle scan of the chunk aggregates, cross-warp combine) and tiles of a row are chained
 // with a decoupled look-back through global memory, so every cell is read once and written once.
 //
-// Work distribution: persistent CTAs draw tickets from a global counter; ticket t maps to
-// (tile position p = t / n_chains, chain = t % n_chains), i.e. all chains advance together and the
-// predecessor tile of a chain has normally been finished long before its successor starts -- the
-// look-back then costs one 16-byte status read, issued before the local scan so its latency is hidden.  With few chains (small problems) the same code degrades
-// gracefully to the classic aggregate walk-back.  Tickets are handed out in dependency order, so a
-// CTA only ever waits on a CTA that is already running: no deadlock, no cooperative launch.
+// Data movement (the kernel is HBM-bound and, sustained, POWER-bound: on a 1 kW B200 every instruction
+// that is not needed costs bandwidth, so the copies are done by the TMA engine, not by the threads):
+//   * every time-level buffer is described by a 3-D tensor map (16 doubles = 8 cells = 128 bytes, Np/8 chunks,
+//     rows) with SWIZZLE_128B.  ONE thread issues one cp.async.bulk.tensor load per time level and tile; the
+//     bytes land in dense shared memory, XOR-swizzled by the hardware so that the blocked access of the scan
+//     (thread t owns cells CPT*t .. CPT*t+CPT-1) is bank-conflict free without padding; completion is signalled
+//     on an mbarrier that all threads wait on.  Rows that end inside a tile are clipped / zero-filled by TMA.
+//   * the row's stepper constants (144 bytes) and the old-time-level outflow nodes of the cell upstream of the
+//     tile travel with the tile as plain bulk copies on the same mbarrier.
+//   * results are written back into the staged tile and leave with ONE cp.async.bulk.tensor store per tile.
+//   * the tile two tickets ahead is pulled from HBM into L2 with cp.async.bulk.prefetch.L2.
+//   Shared memory: a 3-slot ring for the X1/result tile (a slot is reloaded one full iteration after its store was
+//   issued, so the store never has to be waited for), 2 slots for the X2 / XC tiles.
 //
-// Pipeline: each CTA double-buffers its tiles in shared memory -- the cp.async copies of the NEXT ticket's tile are
-// in flight while the current tile is scanned, and the ticket after that is being drawn -- so HBM reads never wait
-// for the scan, the look-back or the barriers of the tile in progress.
+// Work distribution: persistent CTAs draw tickets from a global counter (several tickets per atomic); ticket t maps
+// to (tile position p = t / n_chains, chain = t % n_chains), i.e. all chains advance together and the predecessor
+// tile of a chain has normally been finished long before its successor starts -- the look-back then costs one
+// 16-byte status read, issued before the local scan so its latency is hidden.  Tickets are handed out and consumed
+// in dependency order, so a CTA only ever waits on a CTA that is already running: no deadlock, no cooperative
+// launch.  One thread decodes tickets (incrementally -- consecutive tickets need no division).
 //
 // Reflective left boundary (solver.cpp:677-685): the mu>0 row takes its inflow from the SAME
 // stage's result of the mirrored mu<0 row at cell 0, i.e. from the end of that row's sweep.  The two
@@ -34,29 +44,89 @@
 // Boundary rule common to all BCs (solver.cpp:695-697): at the first cell of a row the three inflow
 // carries (n+1, n+1/2, n) all equal bdry_cond.  In scan form: effective inflow = kbc * bdry with
 // kbc = 1 (BE), 2 (CN), 6 (BDF), and no old-time-level upstream terms for that cell.
+#include <cstdlib>
+
 #include "rt_common.cuh"
 #include "sweep_kernel.cuh"
 
 namespace rtk
 {
-__device__ __forceinline__ void cp_async16(void *smem, const void *gmem)
-{
-   const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
-}
+// ------------------------------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 
-// padded shared-memory slot of cell j of the tile: one 16-byte pad slot per 8 cells makes both the
-// striped (coalesced) and the blocked (8 consecutive cells per thread) access patterns conflict-free
-__device__ __forceinline__ int slot(int j) { return j + (j >> 3); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count)
+{
+   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes)
+{
+   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(unsigned long long *bar, unsigned parity)
+{
+   unsigned ok;
+   asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+   return ok != 0;
+}
+// Every spin in this kernel is bounded: a wait that does not end within seconds of polling is a bug (or a dead
+// predecessor) and traps -- the launch fails loudly instead of hanging the device.
+constexpr long long SPIN_LIMIT = 1ll << 22;
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity)
+{
+   long long spins = 0;
+   while (!mbar_try_wait(bar, parity))
+      if (++spins > SPIN_LIMIT) __trap();
+}
+// 3-D tiled tensor load: coordinates (element in chunk, chunk in row, row)
+__device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *map, int c0, int c1, int c2, unsigned long long *bar)
+{
+   asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
+                : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap *map, int c0, int c1, int c2, const void *src)
+{
+   asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%1, %2, %3}], [%4];"
+                ::"l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(src))
+                : "memory");
+}
+// plain bulk copy global -> shared (16-byte granules), completing on an mbarrier
+__device__ __forceinline__ void bulk_load(void *dst, const void *src, unsigned bytes, unsigned long long *bar)
+{
+   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+// HBM -> L2 only (no shared-memory landing zone needed): used two tiles ahead of the tile being scanned
+__device__ __forceinline__ void prefetch_l2_bulk(const void *gmem, unsigned bytes)
+{
+   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gmem), "r"(bytes) : "memory");
+}
 
 template <int THREADS, int CPT_>
 struct TileShape
 {
-   static constexpr int CPT = CPT_; // cells per thread: 8 or 4 (4 doubles the warps per shared-memory byte)
+   static constexpr int CPT = CPT_; // cells per thread: 8 or 4
    static constexpr int TILE = THREADS * CPT;
-   static constexpr int SLOTS = TILE + TILE / 8;
+   static constexpr int TILE_BYTES = TILE * 16;
    static constexpr int WARPS = THREADS / 32;
 };
+
+// Byte offset of cell j of a tile in its SWIZZLE_128B shared-memory image (tile base 1024-byte aligned):
+// 128-byte line r = j/8 holds 8 cells; the 16-byte chunk index is XORed with (r mod 8).
+__device__ __forceinline__ int swz(int j) { return ((j >> 3) << 7) | ((((j & 7) ^ ((j >> 3) & 7))) << 4); }
 
 // Per-row stepper constants (identical formulas for both signs of mu, see rt_common.cuh).  They depend on
 // (stage kind, group, direction) only, so they are evaluated ONCE per solver by coef_table_kernel into a table of
@@ -165,191 +235,210 @@ __device__ __forceinline__ void st_status(double2 *p, double value, unsigned fla
 }
 __device__ __forceinline__ unsigned status_flag(const double2 &v) { return (unsigned)__double_as_longlong(v.y); }
 
-__device__ __forceinline__ void cp_async8(void *smem, const void *gmem)
-{
-   const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gmem) : "memory");
-}
-// HBM -> L2 only (no shared-memory landing zone needed): used two tiles ahead of the tile being scanned
-__device__ __forceinline__ void prefetch_l2_bulk(const void *gmem, unsigned bytes)
-{
-   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gmem), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
-// Everything the CTA needs to know about one ticket; decoded by ONE thread (the 64-bit divisions are not cheap) and
-// handed to the others through shared memory.
+// Everything the CTA needs to know about one ticket; decoded by ONE thread and handed to the others through
+// shared memory.
 struct TileDesc
 {
    long long row_off;    // element offset of the tile's first cell in a time-level buffer
    long long status_idx; // index of the tile's look-back word
-   int row, p, t, sgn, tile_start, valid;
+   int row, p, sgn, tile_start, valid, junction;
 };
 
-// ticket -> (tile position p, chain) -> (row, tile in row); p-major so that all chains advance together
-__device__ __forceinline__ TileDesc decode_ticket(const SweepArgs &a, long long ticket, int tile_cells)
+// ticket -> (tile position p, chain) -> (row, tile in row); p-major so that all chains advance together.
+// Consecutive tickets are decoded by increments; the divisions only run after a jump (new batch of tickets).
+struct TicketCursor
 {
+   long long ticket;
+   int chain, p, gl, pp; // gl = chain / dm, pp = chain % dm with dm = M/2 (reflective left) or M
+};
+
+__device__ __forceinline__ TileDesc decode_ticket(const SweepArgs &a, TicketCursor &cu, long long ticket, int tile_cells)
+{
+   const int half_m = a.M >> 1, dm = a.reflective_left ? half_m : a.M;
+   if (ticket == cu.ticket + 1)
+   {
+      ++cu.chain;
+      if (++cu.pp == dm) { cu.pp = 0; ++cu.gl; }
+      if (cu.chain == a.n_chains) { cu.chain = 0; cu.gl = 0; cu.pp = 0; ++cu.p; }
+   }
+   else
+   {
+      cu.p = (int)(ticket / a.n_chains);
+      cu.chain = (int)(ticket - (long long)cu.p * a.n_chains);
+      cu.gl = cu.chain / dm;
+      cu.pp = cu.chain - cu.gl * dm;
+   }
+   cu.ticket = ticket;
    TileDesc ti;
-   ti.p = (int)(ticket / a.n_chains);
-   const int chain = (int)(ticket % a.n_chains);
+   int t;
+   ti.p = cu.p;
    if (a.reflective_left)
    {
-      const int half_m = a.M >> 1, gl = chain / half_m, pp = chain % half_m;
-      if (ti.p < a.tiles_per_row) { ti.row = gl * a.M + (half_m - 1 - pp); ti.t = ti.p; }
-      else { ti.row = gl * a.M + (half_m + pp); ti.t = ti.p - a.tiles_per_row; }
+      ti.sgn = (cu.p >= a.tiles_per_row) ? 1 : 0;
+      ti.row = cu.gl * a.M + (ti.sgn ? half_m + cu.pp : half_m - 1 - cu.pp);
+      t = ti.sgn ? cu.p - a.tiles_per_row : cu.p;
    }
-   else { ti.row = chain; ti.t = ti.p; }
-   ti.sgn = ((ti.row % a.M) >= (a.M >> 1)) ? 1 : 0;
-   ti.tile_start = ti.t * tile_cells;
+   else
+   {
+      ti.sgn = (cu.pp >= half_m) ? 1 : 0;
+      ti.row = cu.chain;
+      t = cu.p;
+   }
+   ti.junction = (t == 0 && cu.p > 0) ? 1 : 0; // reflective: first tile of the mu>0 row, fed by the mirrored mu<0 row
+   ti.tile_start = t * tile_cells;
    ti.valid = min(tile_cells, a.N - ti.tile_start);
    ti.row_off = (long long)ti.row * a.Np + ti.tile_start;
-   ti.status_idx = (long long)chain * a.tiles_per_chain + ti.p;
+   ti.status_idx = (long long)cu.chain * a.tiles_per_chain + cu.p;
    return ti;
 }
 
-// (A single-buffered variant that relied on the L2 prefetch alone and doubled the resident CTAs was measured
-// 7 % slower on C4 -- gpurun_out exp2 -- and removed.)
-template <int KIND, bool CORR, int THREADS, int CPT>
-__global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
+// RING = number of shared-memory slots for the X1 / result tile:
+//   3: a slot is reloaded one full iteration after its store was issued -> the store is never waited for;
+//   2: (when 3 would cost a resident CTA) the reload is issued after this tile's look-back, by which time the
+//      store of the previous tile has long finished reading its slot.
+template <int KIND, bool CORR, int THREADS, int CPT, int RING>
+__global__ void __launch_bounds__(THREADS) sweep_kernel(const __grid_constant__ SweepMaps maps, const SweepArgs a)
 {
    using TS = TileShape<THREADS, CPT>;
-   constexpr int TILE = TS::TILE, SLOTS = TS::SLOTS, WARPS = TS::WARPS;
+   constexpr int TILE = TS::TILE, TILE_BYTES = TS::TILE_BYTES, WARPS = TS::WARPS;
    constexpr bool NEED_X2 = (KIND != KIND_BE);
    constexpr bool NEED_XC = (KIND == KIND_BDF) && CORR;
    constexpr int NARR = 1 + (NEED_X2 ? 1 : 0) + (NEED_XC ? 1 : 0);
-   static_assert(CPT == 8 || CPT == 4, "the padded shared-memory layout is conflict-free for 4 or 8 cells per thread");
+   static_assert(CPT == 8 || CPT == 4, "the swizzled tile image is conflict-free for 4 or 8 cells per thread");
    static_assert((WARPS & (WARPS - 1)) == 0, "WARPS must be a power of two");
+   static_assert(TILE_BYTES % 1024 == 0, "SWIZZLE_128B images must be 1024-byte aligned");
 
-   extern __shared__ double2 smem[]; // [2 pipeline buffers][NARR arrays][SLOTS]
-   __shared__ double s_warp_tot[WARPS];
-   __shared__ double s_halo[2][2];
-   __shared__ double s_agg, s_alast, s_ctile;
-   __shared__ long long s_ticket[2];
-   __shared__ TileDesc s_desc[3]; // [0],[1]: the tiles in the two pipeline buffers ; [2]: the tile two tickets ahead
+   static_assert(RING == 2 || RING == 3, "X1 ring depth");
+   // dynamic shared memory, 1024-byte aligned by hand: [RING x X1/result][2 x X2][2 x XC]
+   extern __shared__ unsigned char smem_raw[];
+   unsigned char *const tiles = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+   auto x1_slot = [&](int r) { return tiles + r * TILE_BYTES; };
+   auto x2_slot = [&](int b) { return tiles + (RING + b) * TILE_BYTES; };
+   auto xc_slot = [&](int b) { return tiles + (RING + (NEED_X2 ? 2 : 0) + b) * TILE_BYTES; };
+
    __shared__ __align__(16) RowCoef s_coef[2];
+   __shared__ __align__(16) double2 s_halo[2][2]; // [buffer][0: X1, 1: X2]: the cell upstream of the tile
+   __shared__ __align__(8) unsigned long long s_full[2];
+   // tickets and their decoded descriptors rotate through 3 slots: iteration k scans slot k%3, loads slot (k+1)%3 and
+   // thread 0 publishes the ticket two ahead into slot (k+2)%3 -- last read two barriers ago, first read after the next
+   __shared__ TileDesc s_desc[3];
+   __shared__ long long s_ticket[3];
+   __shared__ double s_warp_tot[WARPS];
+   __shared__ double s_agg, s_alast, s_ctile;
 
    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
    const unsigned flag_agg = a.epoch * 2u + 1u, flag_incl = a.epoch * 2u + 2u;
    const long long total_tiles = (long long)a.n_chains * a.tiles_per_chain;
 
-   // coalesced 16-byte async copies of one tile's time levels into pipeline buffer b
-   auto issue_loads = [&](const TileDesc &ti, int b) {
-      double2 *d1 = smem + (size_t)b * NARR * SLOTS;
-      double2 *d2 = d1 + SLOTS;
-      double2 *dc = d1 + (NEED_X2 ? 2 : 1) * SLOTS;
-      const double2 *g1 = a.x1[ti.sgn] + ti.row_off;
-      const double2 *g2 = NEED_X2 ? a.x2[ti.sgn] + ti.row_off : nullptr;
-      const double2 *gc = NEED_XC ? a.xc[ti.sgn] + ti.row_off : nullptr;
-#pragma unroll
-      for (int k = 0; k < CPT; ++k)
-      {
-         const int j = k * THREADS + tid, s = slot(j);
-         if (j < ti.valid)
-         {
-            cp_async16(&d1[s], g1 + j);
-            if (NEED_X2) cp_async16(&d2[s], g2 + j);
-            if (NEED_XC) cp_async16(&dc[s], gc + j);
-         }
-         else
-         {
-            d1[s] = make_double2(0.0, 0.0);
-            if (NEED_X2) d2[s] = make_double2(0.0, 0.0);
-            if (NEED_XC) dc[s] = make_double2(0.0, 0.0);
-         }
-      }
-      // the row's stepper constants travel with the tile (9 x 16 bytes)
-      if (tid < (int)(sizeof(RowCoef) / 16))
-         cp_async16(reinterpret_cast<double2 *>(&s_coef[b]) + tid, a.coef + (size_t)ti.row * (sizeof(RowCoef) / 16) + tid);
-      if (NEED_X2 && tid == 0)
+   // ---- thread 0 only: TMA / bulk loads of one tile into pipeline buffer b (X1 into ring slot r)
+   auto issue_loads = [&](const TileDesc &ti, int b, int r) {
+      const bool halo = NEED_X2 && ti.tile_start > 0;
+      const unsigned bytes = (unsigned)(NARR * TILE_BYTES + sizeof(RowCoef)) + (halo ? (KIND == KIND_BDF ? 32u : 16u) : 0u);
+      mbar_expect_tx(&s_full[b], bytes);
+      const int chunk0 = ti.tile_start >> 3;
+      tma_load_3d(x1_slot(r), &maps.m[a.ix1[ti.sgn]], 0, chunk0, ti.row, &s_full[b]);
+      if (NEED_X2) tma_load_3d(x2_slot(b), &maps.m[a.ix2], 0, chunk0, ti.row, &s_full[b]);
+      if (NEED_XC) tma_load_3d(xc_slot(b), &maps.m[a.ixc], 0, chunk0, ti.row, &s_full[b]);
+      bulk_load(&s_coef[b], a.coef + (size_t)ti.row * (sizeof(RowCoef) / 16), (unsigned)sizeof(RowCoef), &s_full[b]);
+      if (halo)
       {
          // old-time-level outflow nodes of the cell upstream of the tile (CN: prev ; BDF: half and prev)
-         if (ti.tile_start > 0)
-         {
-            cp_async8(&s_halo[b][1], &(g2 - 1)->y);
-            if (KIND == KIND_BDF) cp_async8(&s_halo[b][0], &(g1 - 1)->y);
-            else s_halo[b][0] = 0.0;
-         }
-         else { s_halo[b][0] = 0.0; s_halo[b][1] = 0.0; }
+         bulk_load(&s_halo[b][1], a.x2 + ti.row_off - 1, 16u, &s_full[b]);
+         if (KIND == KIND_BDF) bulk_load(&s_halo[b][0], a.x1[ti.sgn] + ti.row_off - 1, 16u, &s_full[b]);
       }
    };
 
-   // one thread: pull the time levels of a tile two tickets ahead from HBM into L2 (bulk prefetch, 16-byte granules)
+   // thread 0: pull the time levels of a tile two tickets ahead from HBM into L2 (bulk prefetch, 16-byte granules)
    auto prefetch_tile = [&](const TileDesc &ti) {
       if (!a.l2_prefetch) return;
       const unsigned bytes = (unsigned)ti.valid * (unsigned)sizeof(double2);
       prefetch_l2_bulk(a.x1[ti.sgn] + ti.row_off, bytes);
-      if (NEED_X2) prefetch_l2_bulk(a.x2[ti.sgn] + ti.row_off, bytes);
-      if (NEED_XC) prefetch_l2_bulk(a.xc[ti.sgn] + ti.row_off, bytes);
+      if (NEED_X2) prefetch_l2_bulk(a.x2 + ti.row_off, bytes);
+      if (NEED_XC) prefetch_l2_bulk(a.xc + ti.row_off, bytes);
    };
 
-   // every CTA draws tickets until it has seen ONE that is past the end (the host's ticket accounting relies on it)
    // Tickets are drawn in batches of a.ticket_batch consecutive tickets per atomic (one atomic per tile on a single
    // address would be ~4e8 atomics/s at 6 TB/s with 8 KB tiles).  A batch is consumed in increasing order, so the
    // dependency-order argument above still holds.  Host accounting: the counter advances by one per draw; every CTA
    // makes exactly ONE draw that lies past the end (at the latest when it exits).
-   long long last_taken = 0, q_next = 0, q_end = 0;
-   bool drew_past_end = false;
+   // (no branch depends on a freshly drawn value, so the atomic's latency is only paid where the ticket is used)
+   long long last_taken = 0, q_next = 0, q_end = 0, q_start = -1;
    auto take_ticket = [&]() -> long long {
       if (last_taken >= total_tiles) return last_taken;
       if (q_next == q_end)
       {
-         q_next = (long long)(atomicAdd(a.ticket, 1ull) - a.ticket_base) * a.ticket_batch;
-         q_end = q_next + a.ticket_batch;
-         if (q_next >= total_tiles) drew_past_end = true;
+         q_start = (long long)(atomicAdd(a.ticket, 1ull) - a.ticket_base) * a.ticket_batch;
+         q_next = q_start;
+         q_end = q_start + a.ticket_batch;
       }
       last_taken = q_next++;
       return last_taken;
    };
 
-   // ---- prologue: two tickets drawn and decoded, the first tile in flight, a third ticket drawn
+   // ---- prologue: barriers armed, two tickets drawn and decoded, the first tile in flight, a third ticket drawn
+   TicketCursor cursor;
+   cursor.ticket = -2;
    long long ahead = 0; // thread 0: the ticket two tiles ahead (already drawn, value known)
    if (tid == 0)
    {
+      mbar_init(&s_full[0], 1);
+      mbar_init(&s_full[1], 1);
+      fence_proxy_async();
       const long long t0 = take_ticket(), t1 = take_ticket();
       s_ticket[0] = t0;
       s_ticket[1] = t1;
-      if (t0 < total_tiles) s_desc[0] = decode_ticket(a, t0, TILE);
-      if (t1 < total_tiles) s_desc[1] = decode_ticket(a, t1, TILE);
+      if (t0 < total_tiles)
+      {
+         s_desc[0] = decode_ticket(a, cursor, t0, TILE);
+         issue_loads(s_desc[0], 0, 0);
+      }
+      if (t1 < total_tiles) s_desc[1] = decode_ticket(a, cursor, t1, TILE);
       ahead = take_ticket();
    }
    __syncthreads();
    long long cur = s_ticket[0];
-   int buf = 0;
-   if (cur < total_tiles) issue_loads(s_desc[0], 0);
-   cp_async_commit();
+   int buf = 0, ring = 0, slot = 0;
+   unsigned phase = 0; // bit b: parity the next wait on s_full[b] uses
 
    while (cur < total_tiles)
    {
-      __syncthreads(); // (A) next ticket visible ; everybody is done with the other pipeline buffer
-      const long long nxt = s_ticket[buf ^ 1];
-      if (nxt < total_tiles) issue_loads(s_desc[buf ^ 1], buf ^ 1);
-      cp_async_commit();
-      long long newer = 0;
+      const int ring_next = (ring == RING - 1) ? 0 : ring + 1;
+      const int slot_next = (slot == 2) ? 0 : slot + 1, slot_ahead = (slot_next == 2) ? 0 : slot_next + 1;
+      const long long nxt = s_ticket[slot_next];
+      // thread 0: next tile's loads.  The target X1 slot must no longer be read by the store that last used it.
+      auto issue_next = [&]() {
+         if (nxt >= total_tiles) return;
+         if (RING == 3) bulk_wait_read<1>(); // that store was issued a full iteration ago; the newest may still fly
+         else bulk_wait_read<0>();
+         const TileDesc dn = s_desc[slot_next];
+         issue_loads(dn, buf ^ 1, ring_next);
+      };
       if (tid == 0)
       {
+         if (RING == 3) issue_next();
+         s_ticket[slot_ahead] = ahead;
          if (ahead < total_tiles)
          {
-            const TileDesc d_ahead = decode_ticket(a, ahead, TILE);
+            const TileDesc d_ahead = decode_ticket(a, cursor, ahead, TILE);
             prefetch_tile(d_ahead); // HBM -> L2 for the tile after next
-            s_desc[2] = d_ahead;
+            s_desc[slot_ahead] = d_ahead;
          }
-         newer = take_ticket(); // three ahead; latency hidden behind this tile's work, consumed at the loop end
+         ahead = take_ticket(); // three ahead; the atomic's latency hides behind this tile's work
       }
 
-      const TileDesc ti = s_desc[buf];
-      double2 *s1 = smem + (size_t)buf * NARR * SLOTS; // X1 tile, later the result tile
-      double2 *s2 = s1 + SLOTS;                          // X2 tile
-      double2 *sc = s1 + (NEED_X2 ? 2 : 1) * SLOTS;      // ends-before-stage tile for the BDF correction source
+      const TileDesc ti = s_desc[slot];
+      unsigned char *const s1 = x1_slot(ring); // X1 tile, later the result tile
+      unsigned char *const s2 = x2_slot(buf);  // X2 tile
+      unsigned char *const sc = xc_slot(buf);  // ends-before-stage tile for the BDF correction source
       double2 *status = a.tile_status + ti.status_idx;
 
       // early look-back probe: by the time the local scan is done the predecessor's word has arrived
       double2 early = make_double2(0.0, 0.0);
       if (tid == 0 && ti.p > 0) early = ld_status(status - 1);
 
-      cp_async_wait<1>(); // this tile's copies (the group before the prefetch) have landed
-      __syncthreads();    // (B)
+      mbar_wait(&s_full[buf], (phase >> buf) & 1u); // this tile's bytes have landed
+      phase ^= 1u << buf;
+
       // the row's constants from shared memory; entries that are structurally fixed for this stage kind are folded
       // at compile time (BE: no cross terms, no X2 ; CN: no X2 cell terms ; symmetric / antisymmetric pairs)
       RowCoef c;
@@ -372,36 +461,52 @@ __global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
       double wl[CPT], U[CPT];
       {
          const int j0 = tid * CPT;
-         double up1, up2; // X1(j-1).v and X2(j-1).v
-         if (tid == 0) { up1 = s_halo[buf][0]; up2 = s_halo[buf][1]; }
+         double up1 = 0.0, up2 = 0.0; // X1(j-1).v and X2(j-1).v
+         if (tid == 0)
+         {
+            if (NEED_X2 && ti.tile_start > 0) { up1 = s_halo[buf][0].y; up2 = s_halo[buf][1].y; }
+         }
          else
          {
-            up1 = (KIND == KIND_BDF) ? s1[slot(j0 - 1)].y : 0.0;
-            up2 = NEED_X2 ? s2[slot(j0 - 1)].y : 0.0;
+            if (KIND == KIND_BDF) up1 = reinterpret_cast<const double2 *>(s1 + swz(j0 - 1))->y;
+            if (NEED_X2) up2 = reinterpret_cast<const double2 *>(s2 + swz(j0 - 1))->y;
          }
          const bool row_first = (ti.tile_start == 0) && (tid == 0);
          double w = 0.0;
 #pragma unroll
          for (int jj = 0; jj < CPT; ++jj)
          {
-            const int s = slot(j0 + jj);
-            const double2 x1 = s1[s];
+            const int o = swz(j0 + jj);
+            const double2 x1 = *reinterpret_cast<const double2 *>(s1 + o);
             double2 x2 = make_double2(0.0, 0.0);
-            if (NEED_X2) x2 = s2[s];
+            if (NEED_X2) x2 = *reinterpret_cast<const double2 *>(s2 + o);
             double q = c.qa;
             if (CORR)
             {
-               const double2 xs = NEED_XC ? sc[s] : x1;
+               const double2 xs = NEED_XC ? *reinterpret_cast<const double2 *>(sc + o) : x1;
                q = fma(c.qb, xs.x + xs.y, c.qa);
             }
-            double ru = q + c.c_uu * x1.x + c.c_uv * x1.y;
-            double rv = q + c.c_vu * x1.x + c.c_vv * x1.y;
+            double ru, rv;
+            if (KIND == KIND_BE)
+            {
+               ru = fma(c.c_uu, x1.x, q);
+               rv = fma(c.c_uu, x1.y, q);
+            }
+            else
+            {
+               ru = q + c.c_uu * x1.x + c.c_uv * x1.y;
+               rv = q + c.c_vu * x1.x + c.c_vv * x1.y;
+            }
             if (KIND == KIND_BDF)
             {
                ru += c.p_uu * x2.x + c.p_uv * x2.y;
                rv += c.p_vu * x2.x + c.p_vv * x2.y;
             }
-            if (NEED_X2 && !(row_first && jj == 0)) ru += c.up1 * up1 + c.up2 * up2;
+            if (NEED_X2 && !(row_first && jj == 0))
+            {
+               if (KIND == KIND_BDF) ru += c.up1 * up1 + c.up2 * up2;
+               else ru += c.up2 * up2;
+            }
             const double beta = c.io * ru + c.id * rv;
             U[jj] = c.id * ru - c.io * rv;
             w = fma(c.alpha, w, beta);
@@ -430,30 +535,14 @@ __global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
 #pragma unroll
       for (int s = 0; s < 5; ++s)
          if ((lane >> s) & 1) lane_pow *= pw[s];
-      double warp_carry = 0.0, warp_pow = 1.0; // inflow of this warp for zero tile inflow ; alpha^(32*CPT*warp)
-      if (WARPS > 1)
-      {
-         if (lane == 31) s_warp_tot[warp] = incl;
-         __syncthreads(); // (C)
-         for (int w2 = 0; w2 < warp; ++w2)
-         {
-            warp_carry = fma(warp_factor, warp_carry, s_warp_tot[w2]);
-            warp_pow *= warp_factor;
-         }
-      }
-      const double E_t = fma(lane_pow, warp_carry, excl); // inflow of this thread's chunk for zero tile inflow
-      const double tpow = lane_pow * warp_pow;            // alpha^(CPT*tid)
-      double afull = warp_factor;                         // alpha^TILE
+      double afull = warp_factor; // alpha^TILE
 #pragma unroll
       for (int w2 = 1; w2 < WARPS; w2 <<= 1) afull *= afull;
-
-      // ---- tile aggregate (zero-inflow value and inflow factor at the tile's last valid cell)
-      if (ti.valid == TILE)
+      if (lane == 31) s_warp_tot[warp] = incl;
+      if (ti.valid != TILE)
       {
-         if (tid == THREADS - 1) { s_agg = fma(achunk, E_t, wl[CPT - 1]); s_alast = afull; }
-      }
-      else
-      {
+         // row ends inside the tile: zero-inflow value and inflow factor at the last valid cell need the warp carry,
+         // so the owning thread publishes its pieces and thread 0 finishes the job after the barrier
          const int last = ti.valid - 1;
          if (tid == last / CPT)
          {
@@ -462,61 +551,90 @@ __global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
 #pragma unroll
             for (int jj = 1; jj < CPT; ++jj)
                if (jj <= jo) { wsel = wl[jj]; apow *= c.alpha; }
-            s_agg = fma(apow, E_t, wsel);
-            s_alast = apow * tpow;
+            // value(last) = apow * (lane_pow * warp_carry + excl) + wsel ; factor(last) = apow * lane_pow * warp_pow
+            s_agg = fma(apow, excl, wsel);
+            s_alast = apow * lane_pow;
          }
       }
-      __syncthreads(); // (D)
+      __syncthreads(); // (C) warp totals (and the partial-tile pieces) visible
+      double warp_carry = 0.0, warp_pow = 1.0; // inflow of this warp for zero tile inflow ; alpha^(32*CPT*warp)
+      for (int w2 = 0; w2 < warp; ++w2)
+      {
+         warp_carry = fma(warp_factor, warp_carry, s_warp_tot[w2]);
+         warp_pow *= warp_factor;
+      }
+      const double E_t = fma(lane_pow, warp_carry, excl); // inflow of this thread's chunk for zero tile inflow
+      const double tpow = lane_pow * warp_pow;            // alpha^(CPT*tid)
 
       // ---- decoupled look-back (one thread)
       if (tid == 0)
       {
+         // tile aggregate: zero-inflow value and inflow factor at the tile's last valid cell
+         double agg, alast;
+         if (ti.valid == TILE)
+         {
+            agg = 0.0;
+            for (int w2 = 0; w2 < WARPS; ++w2) agg = fma(warp_factor, agg, s_warp_tot[w2]);
+            alast = afull;
+         }
+         else
+         {
+            const int wl_ = ((ti.valid - 1) / CPT) >> 5; // warp that owns the last valid cell
+            double wc = 0.0, wp = 1.0;
+            for (int w2 = 0; w2 < wl_; ++w2) { wc = fma(warp_factor, wc, s_warp_tot[w2]); wp *= warp_factor; }
+            agg = fma(s_alast, wc, s_agg);
+            alast = s_alast * wp;
+         }
          double ctile;
          if (ti.p == 0) ctile = c.inflow0;
          else
          {
-            const bool junction = (ti.t == 0); // reflective: first tile of the mu>0 row, fed by the mirrored mu<0 row
             double2 w = early;
-            if (junction || !a.lookback_walk)
+            if (ti.junction || !a.lookback_walk)
             {
                // deterministic: always the predecessor's inclusive value (bitwise run-to-run reproducible)
-               while ((int)(status_flag(w) - flag_incl) < 0) { __nanosleep(32); w = ld_status(status - 1); }
-               ctile = junction ? c.kbc * w.x : w.x;
+               long long spins = 0;
+               while ((int)(status_flag(w) - flag_incl) < 0)
+               {
+                  __nanosleep(32);
+                  w = ld_status(status - 1);
+                  if (++spins > SPIN_LIMIT) __trap();
+               }
+               ctile = ti.junction ? c.kbc * w.x : w.x;
             }
             else if ((int)(status_flag(w) - flag_incl) >= 0) ctile = w.x;
             else
             {
                // classic walk-back over aggregates (not bitwise reproducible; for very few chains)
-               st_status(status, s_agg, flag_agg);
+               st_status(status, agg, flag_agg);
                double carry = 0.0, fac = 1.0;
-               int q = ti.t - 1;
                const double2 *qp = status - 1;
                while (true)
                {
                   w = ld_status(qp);
-                  while ((int)(status_flag(w) - flag_agg) < 0) { __nanosleep(32); w = ld_status(qp); }
-                  if ((int)(status_flag(w) - flag_incl) >= 0) { carry = fma(fac, w.x, carry); break; }
-                  if (q == 0)
+                  long long spins = 0;
+                  while ((int)(status_flag(w) - flag_agg) < 0)
                   {
-                     while ((int)(status_flag(w) - flag_incl) < 0) { __nanosleep(32); w = ld_status(qp); }
-                     carry = fma(fac, w.x, carry);
-                     break;
+                     __nanosleep(32);
+                     w = ld_status(qp);
+                     if (++spins > SPIN_LIMIT) __trap();
                   }
+                  if ((int)(status_flag(w) - flag_incl) >= 0) { carry = fma(fac, w.x, carry); break; }
                   carry = fma(fac, w.x, carry);
                   fac *= afull;
                   if (fac == 0.0) break; // everything further upstream has underflowed out of fp64 range
-                  --q;
-                  --qp;
+                  --qp; // never runs past the junction / chain head: those tiles always publish inclusive values
                }
                ctile = carry;
             }
          }
-         st_status(status, fma(s_alast, ctile, s_agg), flag_incl);
+         st_status(status, fma(alast, ctile, agg), flag_incl);
          s_ctile = ctile;
+         if (RING == 2) issue_next();
       }
       __syncthreads(); // (E)
 
-      // ---- pass 2: true nodes, written back into the X1 tile (blocked, conflict-free)
+      // ---- pass 2: true nodes, written back into the X1 tile image
       {
          const double cin = fma(tpow, s_ctile, E_t); // true inflow of this thread's chunk
          const int j0 = tid * CPT;
@@ -526,79 +644,113 @@ __global__ void __launch_bounds__(THREADS) sweep_kernel(const SweepArgs a)
          {
             const double v = fma(ap, cin, wl[jj]);
             const double u = fma(c.gamma, vin, U[jj]);
-            s1[slot(j0 + jj)] = make_double2(u, v);
+            *reinterpret_cast<double2 *>(s1 + swz(j0 + jj)) = make_double2(u, v);
             vin = v;
             ap *= c.alpha;
          }
       }
-      __syncthreads(); // (F)
+      fence_proxy_async(); // generic-proxy writes -> visible to the TMA store
+      __syncthreads();     // (F)
 
-      // ---- coalesced store
-      {
-         double2 *go = a.out[ti.sgn] + ti.row_off;
-#pragma unroll
-         for (int k = 0; k < CPT; ++k)
-         {
-            const int j = k * THREADS + tid;
-            if (j < ti.valid) __stcs(go + j, s1[slot(j)]);
-         }
-      }
       if (tid == 0)
       {
-         s_ticket[buf] = ahead;
-         if (ahead < total_tiles) s_desc[buf] = s_desc[2];
-         ahead = newer;
+         tma_store_3d(&maps.m[a.iout], 0, ti.tile_start >> 3, ti.row, s1); // rows that end inside the tile are clipped
+         bulk_commit();
       }
       cur = nxt;
       buf ^= 1;
+      ring = ring_next;
+      slot = slot_next;
    }
-   cp_async_wait<0>();
-   if (tid == 0 && !drew_past_end) atomicAdd(a.ticket, 1ull);
+   if (tid == 0)
+   {
+      bulk_wait_read<0>(); // the last stores must have read their tiles before the CTA's shared memory goes away
+      if (q_start < total_tiles) atomicAdd(a.ticket, 1ull); // no draw of this CTA lay past the end yet (q_start = -1: none at all)
+   }
 }
 
 // ------------------------------------------------------------------------------------------ host side
-template <int KIND, bool CORR, int THREADS, int CPT>
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// 3-D view of one time-level buffer [rows][Np] of double2: (16 doubles = 8 cells, Np/8 chunks, rows), box = one tile
+cudaError_t make_tile_map(CUtensorMap *map, void *base, int rows, int Np, int tile_cells)
+{
+   static EncodeTiledFn encode = nullptr;
+   if (!encode)
+   {
+      void *fn = nullptr;
+      cudaDriverEntryPointQueryResult q;
+      cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+      if (e != cudaSuccess) return e;
+      if (q != cudaDriverEntryPointSuccess || !fn) return cudaErrorNotSupported;
+      encode = (EncodeTiledFn)fn;
+   }
+   const cuuint64_t dims[3] = {16, (cuuint64_t)(Np / 8), (cuuint64_t)rows};
+   const cuuint64_t strides[2] = {128, (cuuint64_t)Np * 16}; // bytes, dims 1 and 2
+   const cuuint32_t box[3] = {16, (cuuint32_t)(tile_cells / 8), 1};
+   const cuuint32_t estr[3] = {1, 1, 1};
+   const CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+   return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
+}
+
+template <int KIND, bool CORR, int THREADS, int CPT, int RING>
 static size_t smem_bytes()
 {
    const int narr = 1 + (KIND != KIND_BE ? 1 : 0) + ((KIND == KIND_BDF && CORR) ? 1 : 0);
-   return (size_t)2 * narr * TileShape<THREADS, CPT>::SLOTS * sizeof(double2); // two pipeline buffers
+   return (size_t)(RING + 2 * (narr - 1)) * TileShape<THREADS, CPT>::TILE_BYTES + 1024; // + alignment slack
 }
 
 template <int KIND, bool CORR, int THREADS, int CPT>
-static cudaError_t launch_one(const SweepArgs &a, int num_sms, cudaStream_t st, int *grid_out)
+static cudaError_t launch_one(int ring_pref, const SweepMaps &maps, const SweepArgs &a, int num_sms, cudaStream_t st, int *grid_out)
 {
-   static int ctas_per_sm = -1;
-   const size_t smem = smem_bytes<KIND, CORR, THREADS, CPT>();
-   auto kern = sweep_kernel<KIND, CORR, THREADS, CPT>;
+   // plan once per instantiation: X1 ring depth and resident CTAs per SM
+   static int ctas_per_sm = -1, ring = 3;
+   auto k3 = sweep_kernel<KIND, CORR, THREADS, CPT, 3>;
+   auto k2 = sweep_kernel<KIND, CORR, THREADS, CPT, 2>;
+   const size_t s3 = smem_bytes<KIND, CORR, THREADS, CPT, 3>(), s2 = smem_bytes<KIND, CORR, THREADS, CPT, 2>();
    if (ctas_per_sm < 0)
    {
-      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaError_t e = cudaFuncSetAttribute(k3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s3);
       if (e != cudaSuccess) return e;
-      int occ = 0;
-      e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, THREADS, smem);
+      e = cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s2);
       if (e != cudaSuccess) return e;
-      ctas_per_sm = occ > 0 ? occ : 1;
+      int o3 = 0, o2 = 0;
+      e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o3, k3, THREADS, s3);
+      if (e != cudaSuccess) return e;
+      e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, k2, THREADS, s2);
+      if (e != cudaSuccess) return e;
+      // measured (exp9): with >= 4 resident CTAs the never-wait 3-slot ring wins (CN: 5 CTAs x ring 3 beats 6 x ring 2);
+      // below that the extra CTA is worth more (BDF: 4 CTAs x ring 2 beats 3 x ring 3)
+      ring = (o3 < 4 && o2 > o3) ? 2 : 3;
+      if (ring_pref == 2 || ring_pref == 3) ring = ring_pref;
+      ctas_per_sm = (ring == 2) ? o2 : o3;
+      if (ctas_per_sm < 1) ctas_per_sm = 1;
    }
    const long long total = (long long)a.n_chains * a.tiles_per_chain;
    long long grid = (long long)num_sms * ctas_per_sm;
    if (grid > total) grid = total;
    if (grid < 1) grid = 1;
    if (grid_out) *grid_out = (int)grid;
-   kern<<<(unsigned)grid, THREADS, smem, st>>>(a);
+   if (ring == 3) k3<<<(unsigned)grid, THREADS, s3, st>>>(maps, a);
+   else k2<<<(unsigned)grid, THREADS, s2, st>>>(maps, a);
    return cudaGetLastError();
 }
 
 template <int T, int CPT>
-static cudaError_t launch_shape(int kind, bool corr, const SweepArgs &a, int num_sms, cudaStream_t st, int *grid_out)
+static cudaError_t launch_shape(int kind, bool corr, int ring, const SweepMaps &maps, const SweepArgs &a, int num_sms,
+                                cudaStream_t st, int *grid_out)
 {
    switch (kind * 2 + (corr ? 1 : 0))
    {
-   case 0: return launch_one<KIND_BE, false, T, CPT>(a, num_sms, st, grid_out);
-   case 1: return launch_one<KIND_BE, true, T, CPT>(a, num_sms, st, grid_out);
-   case 2: return launch_one<KIND_CN, false, T, CPT>(a, num_sms, st, grid_out);
-   case 3: return launch_one<KIND_CN, true, T, CPT>(a, num_sms, st, grid_out);
-   case 4: return launch_one<KIND_BDF, false, T, CPT>(a, num_sms, st, grid_out);
-   case 5: return launch_one<KIND_BDF, true, T, CPT>(a, num_sms, st, grid_out);
+   case 0: return launch_one<KIND_BE, false, T, CPT>(ring, maps, a, num_sms, st, grid_out);
+   case 1: return launch_one<KIND_BE, true, T, CPT>(ring, maps, a, num_sms, st, grid_out);
+   case 2: return launch_one<KIND_CN, false, T, CPT>(ring, maps, a, num_sms, st, grid_out);
+   case 3: return launch_one<KIND_CN, true, T, CPT>(ring, maps, a, num_sms, st, grid_out);
+   case 4: return launch_one<KIND_BDF, false, T, CPT>(ring, maps, a, num_sms, st, grid_out);
+   case 5: return launch_one<KIND_BDF, true, T, CPT>(ring, maps, a, num_sms, st, grid_out);
    }
    return cudaErrorInvalidValue;
 }
@@ -608,17 +760,17 @@ bool sweep_shape_supported(int threads, int cpt)
    return (threads == 64 || threads == 128 || threads == 256) && (cpt == 4 || cpt == 8);
 }
 
-cudaError_t launch_sweep(int kind, bool corr, int threads, int cpt, const SweepArgs &a, int num_sms, cudaStream_t st,
-                         int *grid_out)
+cudaError_t launch_sweep(int kind, bool corr, int threads, int cpt, int ring, const SweepMaps &maps, const SweepArgs &a,
+                         int num_sms, cudaStream_t st, int *grid_out)
 {
    switch (threads * 16 + cpt)
    {
-   case 64 * 16 + 8: return launch_shape<64, 8>(kind, corr, a, num_sms, st, grid_out);
-   case 64 * 16 + 4: return launch_shape<64, 4>(kind, corr, a, num_sms, st, grid_out);
-   case 128 * 16 + 8: return launch_shape<128, 8>(kind, corr, a, num_sms, st, grid_out);
-   case 128 * 16 + 4: return launch_shape<128, 4>(kind, corr, a, num_sms, st, grid_out);
-   case 256 * 16 + 8: return launch_shape<256, 8>(kind, corr, a, num_sms, st, grid_out);
-   case 256 * 16 + 4: return launch_shape<256, 4>(kind, corr, a, num_sms, st, grid_out);
+   case 64 * 16 + 8: return launch_shape<64, 8>(kind, corr, ring, maps, a, num_sms, st, grid_out);
+   case 64 * 16 + 4: return launch_shape<64, 4>(kind, corr, ring, maps, a, num_sms, st, grid_out);
+   case 128 * 16 + 8: return launch_shape<128, 8>(kind, corr, ring, maps, a, num_sms, st, grid_out);
+   case 128 * 16 + 4: return launch_shape<128, 4>(kind, corr, ring, maps, a, num_sms, st, grid_out);
+   case 256 * 16 + 8: return launch_shape<256, 8>(kind, corr, ring, maps, a, num_sms, st, grid_out);
+   case 256 * 16 + 4: return launch_shape<256, 4>(kind, corr, ring, maps, a, num_sms, st, grid_out);
    }
    return cudaErrorInvalidValue;
 }

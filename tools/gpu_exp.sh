@@ -4,12 +4,12 @@
 TAG=$1; shift
 OUT=gpurun_out/$TAG
 mkdir -p $OUT
-timeout 600 python -m pytest tests/test_gpu_parity.py -x -q -k "synthetic or golden_final" > $OUT/pytest.log 2>&1; echo "pytest exit $?"; tail -3 $OUT/pytest.log
+timeout 240 python -m pytest tests/test_gpu_parity.py -x -q -k "synthetic or golden_final" > $OUT/pytest.log 2>&1; echo "pytest exit $?"; tail -3 $OUT/pytest.log
 i=0
 for cfg in "$@"; do
   i=$((i+1))
   echo "== [$i] $cfg"
-  env $cfg timeout 600 python bench.py --steps 3 --warmup 2 --no-e2e --no-cpu-baseline > $OUT/bench_$i.json 2> $OUT/bench_$i.err || tail -5 $OUT/bench_$i.err
+  env $cfg timeout 180 python bench.py --steps 3 --warmup 2 --no-e2e --no-cpu-baseline > $OUT/bench_$i.json 2> $OUT/bench_$i.err || tail -5 $OUT/bench_$i.err
   python - "$OUT/bench_$i.json" "$cfg" <<'PY'
 import json,sys
 try:
