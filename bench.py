@@ -202,10 +202,33 @@ def run_reference_arm(args, rt, M, G, N, bcl, bcr, workload):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_JSON_FD = None
+
+
+def _reserve_stdout():
+    """Rank 0 must print ONE JSON line on stdout, but libraries write there too (NCCL prints its version banner on the
+    first communicator): keep the real stdout for the JSON line and point fd 1 at stderr for everything else."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
 
 
 def main():
+    _reserve_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -308,6 +331,7 @@ def main():
             t0 = time.perf_counter()
             s2 = rt.Solver(p, device=local_rank, group_begin=g0, group_count=gn, groups_per_batch=args.groups_per_batch, fetch_psi=False)
             s2.set_step_output(pin, True)
+            t_setup = time.perf_counter() - t0
             s2.solve()
             tm2 = s2.timing()
             wall = time.perf_counter() - t0
@@ -317,6 +341,7 @@ def main():
         wall_max = sharding.reduce_scalar(wall, "max", dist)
         e2e = {"value": unknown_stages / wall_max, "unit": UNIT, "h2d_bytes_per_step": int(tm2.h2d_bytes // K),
                "d2h_bytes_per_step": int(tm2.d2h_bytes // K), "wall_s": wall_max,
+               "setup_s": t_setup, "moments_ms_per_step": tm2.moments_ms / K,
                "what": "Solver(params) [tables H2D, Planck+correction terms, state init] + solve() of K steps with phi of every "
                        "step copied to pinned host memory; wall clock incl. allocation"}
 
@@ -335,7 +360,7 @@ def main():
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": gpu_launches,
                 "clocks": clk.summary(), "s_per_bdf2_step": ms_max / K * 1e-3,
                 "sweep_grid": plan.sweep_grid, "sweep_block": plan.sweep_block}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()

@@ -25,20 +25,41 @@ __global__ void init_state_kernel(double2 *__restrict__ buf, const double *__res
 
 // phi, phi_plus, F for one batch, group-major output [gl][c].  One thread per (gl, c); the sum over
 // directions runs in ascending m like the reference.  For a fixed m a warp reads 32 consecutive
-// cells of one row (512 contiguous bytes, reversed for mu<0 rows).
-__global__ void moments_kernel(const double2 *__restrict__ ends, const double *__restrict__ mu,
-                               const double *__restrict__ wt, int M, int N, int Np, int groups,
-                               double *__restrict__ phi, double *__restrict__ phi_plus, double *__restrict__ F)
+// cells of one row (512 contiguous bytes, reversed for mu<0 rows).  The direction loop is blocked by
+// UNR (8 when M is a multiple of 8, else 4) with the loads issued first, so every thread keeps UNR
+// independent 16-byte loads in flight (the plain loop serialised them and reached only 2.7 TB/s).
+template <int UNR>
+__global__ void __launch_bounds__(256) moments_kernel(const double2 *__restrict__ ends, const double *__restrict__ mu,
+                                                      const double *__restrict__ wt, int M, int N, int Np, int groups,
+                                                      double *__restrict__ phi, double *__restrict__ phi_plus,
+                                                      double *__restrict__ F)
 {
    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
    if (idx >= (long long)groups * N) return;
    const int c = (int)(idx % N), gl = (int)(idx / N);
    const int half_m = M >> 1;
+   const double2 *base = ends + (size_t)gl * M * Np;
+   const int jneg = N - 1 - c;
    double a = 0.0, b = 0.0, f = 0.0;
-   for (int m = 0; m < M; ++m)
+   int m = 0;
+   for (; m + UNR <= M; m += UNR)
    {
-      const int j = (m < half_m) ? (N - 1 - c) : c;
-      const double2 e = __ldcs(ends + ((size_t)(gl * M + m) * Np + j));
+      double2 e[UNR];
+#pragma unroll
+      for (int k = 0; k < UNR; ++k) e[k] = __ldcs(base + (size_t)(m + k) * Np + ((m + k) < half_m ? jneg : c));
+#pragma unroll
+      for (int k = 0; k < UNR; ++k)
+      {
+         const double psi = 0.5 * (e[k].x + e[k].y);
+         const double w = wt[m + k];
+         a += w * psi;
+         if (m + k >= half_m) b += w * psi;
+         f += mu[m + k] * w * psi;
+      }
+   }
+   for (; m < M; ++m)
+   {
+      const double2 e = __ldcs(base + (size_t)m * Np + (m < half_m ? jneg : c));
       const double psi = 0.5 * (e.x + e.y);
       const double w = wt[m];
       a += w * psi;
@@ -120,7 +141,7 @@ __device__ __forceinline__ double block_sum(double v, double *red)
 // One block per local group: balance (solver.cpp:240-284) and group-end spectra (solver.cpp:826-850).
 // The sum over cells of sigma*phi*dx is a warp-shuffle block reduction; the sum over directions of the
 // boundary currents runs in ascending m in one thread.
-__global__ void diagnostics_kernel(const double2 *__restrict__ ends, const double *__restrict__ mu,
+__global__ void diagnostics_kernel(const double2 *__restrict__ ends, const double *__restrict__ phi, const double *__restrict__ mu,
                                    const double *__restrict__ wt, const double *__restrict__ sigma,
                                    const double *__restrict__ de_ave, int M, int N, int Np, int G0, double dx, double T,
                                    double *__restrict__ balance, double *__restrict__ left_ends,
@@ -129,18 +150,10 @@ __global__ void diagnostics_kernel(const double2 *__restrict__ ends, const doubl
    __shared__ double red[32];
    const int gl = blockIdx.x, g = G0 + gl, half_m = M >> 1;
    const double sig = sigma[g];
+   // sum_c sigma*phi(g,c)*dx from the scalar intensity the moments kernel has just written (1/(2M) of the bytes of `ends`)
    double part = 0.0;
-   for (int c = threadIdx.x; c < N; c += blockDim.x)
-   {
-      double a = 0.0;
-      for (int m = 0; m < M; ++m)
-      {
-         const int j = (m < half_m) ? (N - 1 - c) : c;
-         const double2 e = ends[(size_t)(gl * M + m) * Np + j];
-         a += wt[m] * (0.5 * (e.x + e.y));
-      }
-      part += sig * a * dx;
-   }
+   const double *prow = phi + (size_t)gl * N;
+   for (int c = threadIdx.x; c < N; c += blockDim.x) part += sig * prow[c] * dx;
    const double absorbed = block_sum(part, red);
    if (threadIdx.x == 0)
    {
@@ -186,7 +199,8 @@ void launch_moments(const double2 *ends, const double *mu, const double *wt, int
                     double *phi, double *phi_plus, double *F, cudaStream_t st)
 {
    const long long total = (long long)groups * N;
-   moments_kernel<<<blocks_for(total, 256), 256, 0, st>>>(ends, mu, wt, M, N, Np, groups, phi, phi_plus, F);
+   if (M % 8 == 0) moments_kernel<8><<<blocks_for(total, 256), 256, 0, st>>>(ends, mu, wt, M, N, Np, groups, phi, phi_plus, F);
+   else moments_kernel<4><<<blocks_for(total, 256), 256, 0, st>>>(ends, mu, wt, M, N, Np, groups, phi, phi_plus, F);
 }
 
 void launch_transpose_gn(const double *in, double *out, int groups, int N, int c0, int nc, cudaStream_t st)
@@ -208,11 +222,11 @@ void launch_export_ends(const double2 *neg, const double2 *pos, double *out, int
    export_ends_kernel<<<blocks_for(total, 256), 256, 0, st>>>(neg, pos, out, M, N, Np, groups);
 }
 
-void launch_diagnostics(const double2 *ends, const double *mu, const double *wt, const double *sigma,
+void launch_diagnostics(const double2 *ends, const double *phi, const double *mu, const double *wt, const double *sigma,
                         const double *de_ave, int M, int N, int Np, int G0, int groups, double dx, double T,
                         double *balance, double *left_ends, double *right_ends, cudaStream_t st)
 {
-   diagnostics_kernel<<<groups, 256, 0, st>>>(ends, mu, wt, sigma, de_ave, M, N, Np, G0, dx, T, balance, left_ends,
+   diagnostics_kernel<<<groups, 1024, 0, st>>>(ends, phi, mu, wt, sigma, de_ave, M, N, Np, G0, dx, T, balance, left_ends,
                                               right_ends);
 }
 } // namespace rtk

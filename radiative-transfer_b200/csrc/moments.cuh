@@ -13,7 +13,8 @@ void launch_transpose_gn(const double *in, double *out, int groups, int N, int c
 void launch_export_psi(const double2 *ends, double *psi, int M, int N, int Np, int groups, cudaStream_t st);
 void launch_export_ends(const double2 *neg, const double2 *pos, double *out, int M, int N, int Np, int groups,
                         cudaStream_t st);
-void launch_diagnostics(const double2 *ends, const double *mu, const double *wt, const double *sigma,
+// phi: the batch's scalar intensity [groups][N] (group-major), as written by launch_moments for the same state
+void launch_diagnostics(const double2 *ends, const double *phi, const double *mu, const double *wt, const double *sigma,
                         const double *de_ave, int M, int N, int Np, int G0, int groups, double dx, double T,
                         double *balance, double *left_ends, double *right_ends, cudaStream_t st);
 } // namespace rtk
