@@ -136,6 +136,12 @@ int rt_reset_timing(rt_solver *s);
 int rt_planck_groups(int device, int G, const double *e_edge, int ncell, const double *T, double *B, double *dBdT,
                      double *kernel_ms);
 
+/* Correction::generate_multigroup_opacities (correction.cpp:66-97; kept by the reference but never called -- second
+ * statement tests/test_planckian.cpp:267-349): Planck-weighted group opacities at temperature T normalised so that
+ * sum_g kappa_g B_g = kappa_grey a c T^4.  Outputs are G long, any may be NULL. */
+int rt_multigroup_opacities(int device, int G, const double *e_edge, double T, double kappa_grey, double *kappa,
+                            double *emis_spec, double *ukappa, double *ckappa);
+
 #ifdef __cplusplus
 }
 #endif

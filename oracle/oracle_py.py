@@ -69,6 +69,7 @@ def lib():
         L.rto_glquad.argtypes = [C.c_int, C.c_double, _dp, _dp]
         L.rto_group_edges.argtypes = [C.c_int, C.c_double, C.c_double, _dp]
         L.rto_planck.argtypes = [C.c_double, C.c_int, _dp, _dp, _dp]
+        L.rto_multigroup_opacities.argtypes = [C.c_double, C.c_double, C.c_int, _dp, _dp, _dp, _dp, _dp, _dp]
         _lib = L
     return _lib
 
@@ -95,6 +96,49 @@ def planck(T: float, e_edge: np.ndarray):
     B, dB = np.zeros(G), np.zeros(G)
     lib().rto_planck(T, G, _p(e_edge), _p(B), _p(dB))
     return B, dB
+
+
+def multigroup_opacities(T: float, kappa_grey: float, e_edge: np.ndarray, B: np.ndarray):
+    """correction.cpp:66-97: returns dict(kappa, emis_spec, ukappa, ckappa)"""
+    e_edge = np.ascontiguousarray(e_edge, dtype=np.float64)
+    B = np.ascontiguousarray(B, dtype=np.float64)
+    G = B.size
+    out = {k: np.zeros(G) for k in ("kappa", "emis_spec", "ukappa", "ckappa")}
+    lib().rto_multigroup_opacities(T, kappa_grey, G, _p(e_edge), _p(B), *[_p(out[k]) for k in ("kappa", "emis_spec", "ukappa", "ckappa")])
+    return out
+
+
+PLANCKIAN = os.path.join(HERE, "_ref", "test_planckian")
+
+
+def run_test_planckian(M, X, N, G, efirst, elast, T, kappa_grey):
+    """Drive the reference's interactive tests/test_planckian.cpp (compiled unmodified, oracle/_ref/test_planckian) through
+    stdin and parse the tables it prints (6 significant digits)."""
+    inp = "\n".join(str(v) for v in (M, X, N, G, efirst, elast, T, kappa_grey)) + "\n"
+    txt = subprocess.run([PLANCKIAN], input=inp, capture_output=True, text=True, timeout=120).stdout
+    lines = txt.splitlines()
+
+    def table(header_word, ncols, rows, first="Group"):
+        for i, ln in enumerate(lines):
+            f = ln.split()
+            if f and f[0] == first and header_word in ln:
+                out = []
+                for r in lines[i + 2:i + 2 + rows]:
+                    out.append([float(x) for x in r.split()[:ncols]])
+                return np.array(out)
+        raise KeyError(header_word)
+
+    t_planck = table("dBdT", 5, G)
+    t_uk = table("Planck-Averaged Opacity", 4, G)
+    t_fin = table("Final Opacity", 4, G)
+    t_deb = table("dEB", 3, G)
+    t_edge = table("Opacity", 3, G + 1, first="Edge")
+    t_dkde = table("dkapEdE", 3, G)
+    t_dkeb = table("dkapEB", 3, G)
+    t_cor = table("cor1", 5, G)
+    return {"B": t_planck[:, 3], "dBdT": t_planck[:, 4], "ukappa": t_uk[:, 2], "ckappa": t_uk[:, 3], "kappa": t_fin[:, 2],
+            "emis_spec": t_fin[:, 3], "dEB": t_deb[:, 2], "kappa_edge": t_edge[:, 2], "dkapEdE": t_dkde[:, 2],
+            "dkapEB": t_dkeb[:, 2], "cor1": t_cor[:, 2], "cor2": t_cor[:, 3], "cor3": t_cor[:, 4], "e_ave": t_uk[:, 1]}
 
 
 class Oracle:

@@ -91,6 +91,37 @@ void rto_planck(double T, int G, const double *e_edge, double *B, double *dBdT)
    rto::planck_groups(q, T, G, e_edge, B, dBdT);
 }
 
+// Correction::generate_multigroup_opacities, correction.cpp:66-97 (present in the reference but never called; second
+// statement in tests/test_planckian.cpp:267-349): Planck-weighted group opacities normalised so that
+// sum_g kappa_g B_g = kappa_grey a c T^4.  B is in jk units (after the unit change of correction.cpp:31-35).
+void rto_multigroup_opacities(double T, double kappa_grey, int G, const double *e_edge, const double *B, double *kappa,
+                              double *emis_spec, double *ukappa, double *ckappa)
+{
+   using namespace rto;
+   std::vector<double> uk(G), ck(G);
+   const double fourpi = 4.0 * PI_TRUNC;
+   for (int g = 0; g < G; g++)
+   {
+      const double tmp1 = 2.0 * fourpi * K_JPK * T / (std::pow(H_KEV_SH, 3) * std::pow(C_LIGHT, 2));
+      const double tmp2 = std::exp(-e_edge[g] / T) - std::exp(-e_edge[g + 1] / T);
+      const double e_ave = 0.5 * (e_edge[g] + e_edge[g + 1]);
+      uk[g] = tmp1 * tmp2 / B[g];
+      ck[g] = (1.0 - std::exp(-e_ave / T)) / std::pow(e_ave, 3);
+   }
+   double emis_tot = 0.0;
+   const double acT4 = RAD_A * C_LIGHT * std::pow(T, 4);
+   for (int g = 0; g < G; g++) emis_tot += uk[g] * B[g];
+   const double nfac = acT4 / emis_tot;
+   for (int g = 0; g < G; g++)
+   {
+      const double k = kappa_grey * nfac * uk[g];
+      if (kappa) kappa[g] = k;
+      if (emis_spec) emis_spec[g] = k * B[g];
+      if (ukappa) ukappa[g] = uk[g];
+      if (ckappa) ckappa[g] = ck[g];
+   }
+}
+
 rto_solver *rto_create(const rto_params *p)
 {
    rto_solver *s = new rto_solver();

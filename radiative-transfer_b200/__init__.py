@@ -14,6 +14,6 @@ Contents (only what the hot path needs):
 """
 from . import capi, grid, prm  # noqa: F401
 from .prm import Parameters  # noqa: F401
-from .solver import Solver, planck_groups  # noqa: F401
+from .solver import Solver, multigroup_opacities, planck_groups  # noqa: F401
 
-__all__ = ["capi", "grid", "prm", "Parameters", "Solver", "planck_groups"]
+__all__ = ["capi", "grid", "prm", "Parameters", "Solver", "planck_groups", "multigroup_opacities"]

@@ -23,7 +23,7 @@ EXPORTS = (
     "rt_stages_done", "rt_total_stages", "rt_reset", "rt_get_psi", "rt_get_ends", "rt_moments",
     "rt_moments_group_major", "rt_balance", "rt_group_ends", "rt_get_group_terms", "rt_get_psi_source",
     "rt_validate", "rt_set_step_output", "rt_get_timing", "rt_reset_timing", "rt_planck_groups", "rt_bench_steps",
-    "rt_host_alloc", "rt_host_free",
+    "rt_host_alloc", "rt_host_free", "rt_multigroup_opacities",
 )
 
 
@@ -102,6 +102,7 @@ def lib():
         L.rt_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
         L.rt_host_free.argtypes = [C.c_void_p]
         L.rt_planck_groups.argtypes = [C.c_int, C.c_int, _dp, C.c_int, _dp, _dp, _dp, _dp]
+        L.rt_multigroup_opacities.argtypes = [C.c_int, C.c_int, _dp, C.c_double, C.c_double, _dp, _dp, _dp, _dp]
         _lib = L
     return _lib
 

@@ -285,4 +285,46 @@ int launch_boundary_table(int M, int G, int bc_left, int bc_right, int use_mg_eq
                                                              psi_source, bdry);
    return 1;
 }
+// Planck-weighted multigroup opacities normalised to the grey emission, Correction::generate_multigroup_opacities
+// (correction.cpp:66-97; the reference keeps it but never calls it): ukappa_g = 2*4pi*k*T/(h^3 c^2) *
+// (e^{-E_g/T} - e^{-E_{g+1}/T}) / B_g, ckappa_g = (1 - e^{-Eave_g/T}) / Eave_g^3, kappa_g = kappa_grey * (a c T^4 /
+// sum ukappa*B) * ukappa_g, emis_g = kappa_g * B_g.  One block; the normalisation sum runs in ascending g in one thread
+// like the reference.
+__global__ void multigroup_opacities_kernel(int G, double T, double kappa_grey, const double *__restrict__ e_edge,
+                                            const double *__restrict__ B, double *__restrict__ kappa,
+                                            double *__restrict__ emis_spec, double *__restrict__ ukappa,
+                                            double *__restrict__ ckappa)
+{
+   __shared__ double s_nfac;
+   const double fourpi = 4.0 * PI_TRUNC;
+   const double tmp1 = 2.0 * fourpi * K_JPK * T / ((H_KEV_SH * H_KEV_SH * H_KEV_SH) * (C_LIGHT * C_LIGHT));
+   for (int g = threadIdx.x; g < G; g += blockDim.x)
+   {
+      const double tmp2 = exp(-e_edge[g] / T) - exp(-e_edge[g + 1] / T);
+      const double e_ave = 0.5 * (e_edge[g] + e_edge[g + 1]);
+      ukappa[g] = tmp1 * tmp2 / B[g];
+      ckappa[g] = (1.0 - exp(-e_ave / T)) / (e_ave * e_ave * e_ave);
+   }
+   __syncthreads();
+   if (threadIdx.x == 0)
+   {
+      double emis_tot = 0.0;
+      for (int g = 0; g < G; ++g) emis_tot += ukappa[g] * B[g];
+      s_nfac = RAD_A * C_LIGHT * (T * T) * (T * T) / emis_tot;
+   }
+   __syncthreads();
+   for (int g = threadIdx.x; g < G; g += blockDim.x)
+   {
+      const double k = kappa_grey * s_nfac * ukappa[g];
+      kappa[g] = k;
+      emis_spec[g] = k * B[g];
+   }
+}
+
+int launch_multigroup_opacities(int G, double T, double kappa_grey, const double *d_e_edge, const double *d_B, double *d_kappa,
+                                double *d_emis, double *d_ukappa, double *d_ckappa, cudaStream_t st)
+{
+   multigroup_opacities_kernel<<<1, 256, 0, st>>>(G, T, kappa_grey, d_e_edge, d_B, d_kappa, d_emis, d_ukappa, d_ckappa);
+   return 1;
+}
 } // namespace rtk

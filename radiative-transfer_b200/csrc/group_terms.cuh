@@ -23,6 +23,9 @@ void upload_gauss_rule(const double *pt, const double *w);
 // B,dBdT: [ncell][G]; returns the number of kernels launched
 int launch_planck(int G, int ncell, const double *d_e_edge, const double *d_T, double *d_B, double *d_dBdT, cudaStream_t st);
 int launch_group_terms(const GroupTermsArgs &a, cudaStream_t st);
+// correction.cpp:66-97; B in jk units (after launch_planck); all arrays G long
+int launch_multigroup_opacities(int G, double T, double kappa_grey, const double *d_e_edge, const double *d_B, double *d_kappa,
+                                double *d_emis, double *d_ukappa, double *d_ckappa, cudaStream_t st);
 int launch_boundary_table(int M, int G, int bc_left, int bc_right, int use_mg_equilib, double V, const double *mu,
                           const double *B, const double *dEB, double *psi_source, double *bdry, cudaStream_t st);
 } // namespace rtk

@@ -965,6 +965,45 @@ extern "C" int rt_planck_groups(int device, int G, const double *e_edge, int nce
 }
 
 // ---------------------------------------------------------------------------------------------
+// Correction::generate_multigroup_opacities (correction.cpp:66-97) on the device: Planck integrals at T, then the
+// Planck-weighted opacities normalised to kappa_grey * a c T^4.  Stand-alone like rt_planck_groups; its result is what a
+// caller would pass as rt_params::kappa.
+extern "C" int rt_multigroup_opacities(int device, int G, const double *e_edge, double T, double kappa_grey, double *kappa,
+                                       double *emis_spec, double *ukappa, double *ckappa)
+{
+   if (!e_edge || G < 1 || !(T > 0.0)) return fail("rt_multigroup_opacities: bad argument");
+   int ndev = 0;
+   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail("rt_multigroup_opacities: no CUDA device available");
+   CK(cudaSetDevice(device));
+   double *d = nullptr; // e_edge (G+1) | T (1) | B | dBdT | kappa | emis | ukappa | ckappa
+   const size_t n = (size_t)(G + 1) + 1 + 6 * (size_t)G;
+   if (dalloc(&d, n)) return 1;
+   double *d_e = d, *d_T = d + G + 1, *d_B = d_T + 1, *d_dB = d_B + G, *d_k = d_dB + G, *d_em = d_k + G, *d_uk = d_em + G,
+          *d_ck = d_uk + G;
+   int rc = 1;
+   do
+   {
+      if (cudaMemset(d, 0, n * sizeof(double)) != cudaSuccess) { fail("rt_multigroup_opacities: memset failed"); break; }
+      if (cudaMemcpy(d_e, e_edge, (G + 1) * sizeof(double), cudaMemcpyHostToDevice) != cudaSuccess ||
+          cudaMemcpy(d_T, &T, sizeof(double), cudaMemcpyHostToDevice) != cudaSuccess) { fail("rt_multigroup_opacities: H2D failed"); break; }
+      double pt[12], w[12];
+      gauss12_host(pt, w);
+      upload_gauss_rule(pt, w);
+      launch_planck(G, 1, d_e, d_T, d_B, d_dB, 0);
+      launch_multigroup_opacities(G, T, kappa_grey, d_e, d_B, d_k, d_em, d_uk, d_ck, 0);
+      if (cudaDeviceSynchronize() != cudaSuccess) { fail("rt_multigroup_opacities: kernel failed: %s", cudaGetErrorString(cudaGetLastError())); break; }
+      struct { double *h; const double *dv; } outs[] = {{kappa, d_k}, {emis_spec, d_em}, {ukappa, d_uk}, {ckappa, d_ck}};
+      bool ok = true;
+      for (auto &o : outs)
+         if (o.h && cudaMemcpy(o.h, o.dv, G * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) ok = false;
+      if (!ok) { fail("rt_multigroup_opacities: D2H failed"); break; }
+      rc = 0;
+   } while (0);
+   cudaFree(d);
+   return rc;
+}
+
+// ---------------------------------------------------------------------------------------------
 // measurement helpers
 // For every batch of owned groups: re-initialise, run `warmup_steps` untimed time steps, then time exactly
 // `timed_steps` time steps with CUDA events on the launching stream (all launches and the gaps between them).

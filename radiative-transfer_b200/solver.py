@@ -150,6 +150,39 @@ class Solver:
         assert side in ("left", "right"), "Invalid option for 'side'."
         return (self.left_ends if side == "left" else self.right_ends).copy()
 
+    # ------------------------------------------------------------------ output files (main.cc:117-133)
+    def write_outputs(self, directory: str = ".") -> None:
+        """The 8 files the reference's driver writes after solve() (src/main.cc:117-133: phi, phi_plus, psi, x, F, e_ave,
+        left_ends, right_ends `.csv`), same layout (one matrix row per line, blank-separated, ostream default precision
+        = 6 significant digits; psi as M rows x (G*N) columns, Eigen::Tensor's flattening) so that
+        scripts/plot_results.py reads them unchanged.  Calls the compute_* methods itself, like main.cc:105-129."""
+        import os
+
+        def fmt(v):
+            return "%g" % v
+
+        def dump(name, a2d):
+            with open(os.path.join(directory, name), "w") as fh:
+                fh.write("\n".join(" ".join(fmt(v) for v in row) for row in a2d) + "\n")
+
+        self.compute_angle_integrated_intensity()
+        self.compute_radiative_flux()
+        self.compute_balance()
+        self.compute_positive_angle_integrated_intensity()
+        self.compute_group_ends()
+        if self._fetch_psi and self.resident:
+            self._pull_psi()
+        col = lambda v: np.asarray(v, dtype=np.float64).reshape(-1, 1)
+        dump("phi.csv", self.phi_ref)
+        dump("phi_plus.csv", self.phi_plus)
+        if self.psi_mat_ref is not None and self.resident:
+            dump("psi.csv", self.psi_mat_ref.reshape(self.M, self.group_count * self.N, order="F"))
+        dump("x.csv", col((np.arange(self.N) + 0.5) * self.ph.dx))
+        dump("F.csv", self.F_ref)
+        dump("e_ave.csv", col(self.e_ave[self.group_begin:self.group_begin + self.group_count]))
+        dump("left_ends.csv", col(self.left_ends))
+        dump("right_ends.csv", col(self.right_ends))
+
     # ------------------------------------------------------------------ extras used by tests / bench
     def _pull_psi(self):
         capi.check(capi.lib().rt_get_psi(self._h, capi.ptr(self.psi_mat_ref)))
@@ -242,3 +275,14 @@ def planck_groups(e_edge, T, device: int = 0):
     capi.check(capi.lib().rt_planck_groups(device, G, capi.ptr(e_edge), T.size, capi.ptr(T), capi.ptr(B), capi.ptr(dB),
                                            C.cast(C.byref(ms), C.POINTER(C.c_double))))
     return B, dB, ms.value
+
+
+def multigroup_opacities(e_edge, T: float, kappa_grey: float, device: int = 0):
+    """Device version of Correction::generate_multigroup_opacities (correction.cpp:66-97): dict(kappa, emis_spec,
+    ukappa, ckappa), each G long."""
+    e_edge = np.ascontiguousarray(e_edge, dtype=np.float64)
+    G = e_edge.size - 1
+    out = {k: np.zeros(G) for k in ("kappa", "emis_spec", "ukappa", "ckappa")}
+    capi.check(capi.lib().rt_multigroup_opacities(device, G, capi.ptr(e_edge), float(T), float(kappa_grey),
+                                                  *[capi.ptr(out[k]) for k in ("kappa", "emis_spec", "ukappa", "ckappa")]))
+    return out

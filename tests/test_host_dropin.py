@@ -73,3 +73,31 @@ def test_gray_test_passes(tmp_path):
     assert "Gray test passed." in out.stdout
     F = _csv(tmp_path / "gray-test-F.csv")
     assert abs(F.max()) < 1e-6
+
+
+@pytest.mark.parametrize("name", ["multi_group_equilibrium", "llnl_slab_test"])
+def test_python_mirror_writes_the_same_files_as_the_cpp_driver(rt, name, tmp_path):
+    """Solver.write_outputs (Python mirror of main.cc:117-133) against the files transfer_b200 writes: same 8 files, same
+    numbers as printed (6 significant digits)"""
+    _need(TRANSFER)
+    from parity_util import load_case
+    run = tmp_path / "run"
+    run.mkdir()
+    shutil.copytree(PRM_DIR, tmp_path / "prm")
+    out = subprocess.run([TRANSFER, str(tmp_path / "prm" / (name + ".prm"))], cwd=run, capture_output=True, text=True,
+                         timeout=600)
+    assert out.returncode == 0
+    py = tmp_path / "py"
+    py.mkdir()
+    p = load_case(rt, name)
+    with rt.Solver(p) as s:
+        s.solve()
+        s.write_outputs(str(py))
+    names = ["phi", "phi_plus", "psi", "x", "F", "e_ave", "left_ends", "right_ends"]
+    for n in names:
+        a, b = _csv(run / (n + ".csv")), _csv(py / (n + ".csv"))
+        assert a.shape == b.shape, n
+        scale = float(np.max(np.abs(a))) or 1.0
+        # both print the SAME device results with 6 digits; F is a difference of O(phi) terms whose last bits may differ
+        tol = 2e-6 * scale if n != "F" else 1e-9 * float(np.max(np.abs(_csv(run / "phi.csv"))))
+        assert np.all(np.abs(a - b) <= tol + 1e-5 * np.abs(a)), n
