@@ -33,6 +33,7 @@ sys.path.insert(0, ROOT)
 METRIC = "sweep_unknown_stages_per_s"
 UNIT = "unknown-stages/s"
 BYTES_PER_UNKNOWN = {"BE": 32, "CN": 48, "BDF": 64}  # algorithmic fp64 traffic per (cell,angle,group), correction live
+STEP_BYTES_PER_UNKNOWN = 32  # fused BDF2 step: ends^n in (16 B), ends^(n+1) out (16 B) per (cell,angle,group)
 
 WORKLOADS = {
     # name: (M, G, N, bc_left, bc_right)
@@ -286,37 +287,54 @@ def main():
     unknown_stages = M * G * N * 4 * K
     value = unknown_stages / (ms_max * 1e-3)
 
-    # roofline of the dominant kernel (the stage sweep): algorithmic bytes / event time of the launches, this rank
+    # roofline of the dominant kernel: algorithmic bytes / event time of its launches, this rank
     kinds = ["BE", "CN", "BDF"]
-    per_unknown_launch = M * gn * N
-    alg_bytes = sum(BYTES_PER_UNKNOWN[k] * per_unknown_launch * K * (2 if k == "BE" else 1) for k in kinds)
-    sweep_ms = sum(tm.sweep_ms)
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
         peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-    achieved = alg_bytes / (sweep_ms * 1e-3) / 1e9 if sweep_ms > 0 else None
-    by_kind = {}
-    for i, k in enumerate(kinds):
-        if tm.sweep_ms[i] > 0:
-            nl = tm.sweep_launches[i]
-            by_kind[k] = {"launches": int(nl), "avg_ms": tm.sweep_ms[i] / nl,
-                          "GBps": BYTES_PER_UNKNOWN[k] * M * N * (tm.unknown_stages / tm.stages / (M * N)) * nl / (tm.sweep_ms[i] * 1e-3) / 1e9}
-    # measured DRAM traffic of the sweep launches (ncu --set full capture, per unknown and stage kind), scaled to the
-    # unknowns one launch of THIS run processes and averaged over the launches like `achieved`
-    traffic = None
+    unknowns_per_launch = M * min(plan.groups_per_batch, gn) * N
     tr_path = os.path.join(ROOT, "profiles", "sweep_traffic.json")
-    n_launches = int(sum(tm.sweep_launches))
-    if os.path.exists(tr_path) and n_launches:
-        per_unknown = json.load(open(tr_path)).get("dram_bytes_per_unknown") or {}
-        if all(k in per_unknown for k in kinds):
-            unknowns_per_launch = tm.unknown_stages / tm.stages
+    tr = json.load(open(tr_path)) if os.path.exists(tr_path) else {}
+    if tm.step_launches > 0:
+        # fused BDF2-step kernel: one pass over the state per time step -- reads ends^n (16 B), writes ends^(n+1) (16 B)
+        n_launches = int(tm.step_launches)
+        avg_ms = tm.step_ms / n_launches
+        alg = STEP_BYTES_PER_UNKNOWN * unknowns_per_launch
+        achieved = alg / (avg_ms * 1e-3) / 1e9
+        per_unknown = tr.get("step_dram_bytes_per_unknown")
+        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                    "traffic": per_unknown * unknowns_per_launch if per_unknown else None,
+                    "algorithmic_bytes_per_launch": alg, "avg_launch_ms": avg_ms, "peak_source": peak_src,
+                    "kernel": "rtk::step_kernel<CORR,T,CPT> (BE,CN,BE,BDF fused: one launch per BDF2 step and batch)",
+                    "algorithmic_bytes_per_unknown_step": STEP_BYTES_PER_UNKNOWN,
+                    "note": "the fused step is fp64-pipe bound, not HBM bound (profiles/: sm__pipe_fp64_cycles_active); run stage by "
+                            "stage the same step needs 176 B per unknown",
+                    "staged_equivalent_GBps": sum(BYTES_PER_UNKNOWN[k] * (2 if k == "BE" else 1) for k in kinds) * unknowns_per_launch / (avg_ms * 1e-3) / 1e9,
+                    "fp64_pipe_pct": tr.get("step_fp64_pipe_pct")}
+    else:
+        alg_bytes = sum(BYTES_PER_UNKNOWN[k] * unknowns_per_launch * tm.sweep_launches[i] for i, k in enumerate(kinds))
+        sweep_ms = sum(tm.sweep_ms)
+        n_launches = int(sum(tm.sweep_launches))
+        achieved = alg_bytes / (sweep_ms * 1e-3) / 1e9 if sweep_ms > 0 else None
+        by_kind = {}
+        for i, k in enumerate(kinds):
+            if tm.sweep_ms[i] > 0:
+                nl = tm.sweep_launches[i]
+                by_kind[k] = {"launches": int(nl), "avg_ms": tm.sweep_ms[i] / nl,
+                              "GBps": BYTES_PER_UNKNOWN[k] * unknowns_per_launch * nl / (tm.sweep_ms[i] * 1e-3) / 1e9}
+        # measured DRAM traffic of the sweep launches (ncu --set full capture, per unknown and stage kind), scaled to the
+        # unknowns one launch of THIS run processes and averaged over the launches like `achieved`
+        traffic = None
+        per_unknown = tr.get("dram_bytes_per_unknown") or {}
+        if n_launches and all(k in per_unknown for k in kinds):
             traffic = sum(per_unknown[k] * tm.sweep_launches[i] for i, k in enumerate(kinds)) * unknowns_per_launch / n_launches
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
-                "traffic": traffic, "algorithmic_bytes_per_launch": (alg_bytes / n_launches) if n_launches else None,
-                "avg_launch_ms": (sweep_ms / n_launches) if n_launches else None, "peak_source": peak_src, "kernel": "rtk::sweep_kernel<KIND,CORR,T> (BE,CN,BE,BDF per step)",
-                "algorithmic_bytes_per_unknown": BYTES_PER_UNKNOWN, "by_kind": by_kind}
+        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
+                    "traffic": traffic, "algorithmic_bytes_per_launch": (alg_bytes / n_launches) if n_launches else None,
+                    "avg_launch_ms": (sweep_ms / n_launches) if n_launches else None, "peak_source": peak_src,
+                    "kernel": "rtk::sweep_kernel<KIND,CORR,T,CPT,RING> (BE,CN,BE,BDF per step)",
+                    "algorithmic_bytes_per_unknown": BYTES_PER_UNKNOWN, "by_kind": by_kind}
     gpu_launches = int(tm.kernel_launches)
 
     # ------------------------------------------------------------- end to end through the public API (`e2e`)

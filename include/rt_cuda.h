@@ -68,6 +68,8 @@ typedef struct rt_timing
    long long unknown_stages;  /* M * groups * N summed over executed stage sweeps         */
    long long kernel_launches; /* all kernels launched by the library since rt_create      */
    long long h2d_bytes, d2h_bytes;
+   double step_ms;            /* device time spent in fused BDF2-step launches (4 stage sweeps each)  */
+   long long step_launches;
 } rt_timing;
 
 typedef struct rt_plan

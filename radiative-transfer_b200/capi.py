@@ -44,6 +44,7 @@ class RtTiming(C.Structure):
         ("sweep_ms", C.c_double * 3), ("sweep_launches", C.c_longlong * 3), ("moments_ms", C.c_double),
         ("stages", C.c_longlong), ("unknown_stages", C.c_longlong), ("kernel_launches", C.c_longlong),
         ("h2d_bytes", C.c_longlong), ("d2h_bytes", C.c_longlong),
+        ("step_ms", C.c_double), ("step_launches", C.c_longlong),
     ]
 
 

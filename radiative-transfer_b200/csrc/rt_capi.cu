@@ -16,6 +16,7 @@
 #include "group_terms.cuh"
 #include "moments.cuh"
 #include "rt_common.cuh"
+#include "step_kernel.cuh"
 #include "sweep_kernel.cuh"
 
 using namespace rtk;
@@ -43,7 +44,7 @@ static int fail(const char *fmt, ...)
 struct EventPair
 {
    cudaEvent_t a, b;
-   int kind; // 0..2 sweep kinds, 3 moments
+   int kind; // 0..2 sweep kinds, 3 moments, 4 fused BDF2 step
 };
 
 struct rt_solver
@@ -95,6 +96,10 @@ struct rt_solver
    std::vector<EventPair> ev_pool;
    size_t ev_used = 0;
    bool timing_on = true;
+   // fused BDF2-step kernel (step_kernel.cu): RT_CUDA_FUSED=0 runs every step stage by stage
+   bool fused = true, half_stale = false;
+   int step_threads = 64, step_cpt = 8, step_tile_cells = 512, step_tiles_per_row = 0;
+   SweepMaps maps_step;
    int ticket_batch = 8;       // tickets per atomic draw (RT_CUDA_TICKET_BATCH)
    bool l2_prefetch = true;    // RT_CUDA_L2_PREFETCH=0 switches the two-tiles-ahead L2 prefetch off
    bool lookback_walk = false; // RT_CUDA_LOOKBACK=walk: aggregate walk-back (faster with very few rows, not bitwise reproducible)
@@ -212,6 +217,7 @@ static int flush_events(rt_solver *s)
       float ms = 0.f;
       CK(cudaEventElapsedTime(&ms, s->ev_pool[k].a, s->ev_pool[k].b));
       if (s->ev_pool[k].kind < 3) s->tm.sweep_ms[s->ev_pool[k].kind] += ms;
+      else if (s->ev_pool[k].kind == 4) s->tm.step_ms += ms;
       else s->tm.moments_ms += ms;
    }
    s->ev_used = 0;
@@ -296,6 +302,7 @@ static int load_batch(rt_solver *s, int start)
    s->batch_groups = std::min(s->Gb, s->Gl - start);
    s->i_ends = 0;
    s->i_prev = s->i_half_neg = s->i_half_pos = -1;
+   s->half_stale = false;
    s->stages_done = 0;
    launch_init_state(s->E[0], s->d_B, s->p.M, s->p.N, s->Np, s->p.group_begin + start, s->batch_groups, s->st);
    s->tm.kernel_launches += 1;
@@ -399,6 +406,17 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       s->tiles_per_row[k] = (N + s->tile_cells[k] - 1) / s->tile_cells[k];
       s->max_tiles_per_row = std::max(s->max_tiles_per_row, s->tiles_per_row[k]);
    }
+   {
+      int st3[3] = {s->step_threads, 0, 0}, sc3[3] = {s->step_cpt, 0, 0};
+      env3("RT_CUDA_STEP_THREADS", st3);
+      env3("RT_CUDA_STEP_CPT", sc3);
+      if (step_shape_supported(st3[0], sc3[0])) { s->step_threads = st3[0]; s->step_cpt = sc3[0]; }
+      s->step_tile_cells = s->step_threads * s->step_cpt;
+      s->step_tiles_per_row = (N + s->step_tile_cells - 1) / s->step_tile_cells;
+      s->max_tiles_per_row = std::max(s->max_tiles_per_row, 4 * s->step_tiles_per_row); // 4 look-back words per tile
+      const char *fe = getenv("RT_CUDA_FUSED");
+      s->fused = !(fe && fe[0] == '0');
+   }
    const char *tenv = getenv("RT_CUDA_TIMING");
    s->timing_on = !(tenv && tenv[0] == '0');
    if (const char *be = getenv("RT_CUDA_TICKET_BATCH"))
@@ -468,6 +486,7 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
    {
       CKD(pool_alloc(s, &s->E[k], s->buf_elems));
       for (int kind = 0; kind < 3; ++kind) CKC(make_tile_map(&s->maps[kind].m[k], s->E[k], gb * M, s->Np, s->tile_cells[kind]));
+      CKC(make_tile_map(&s->maps_step.m[k], s->E[k], gb * M, s->Np, s->step_tile_cells));
    }
    const size_t ntiles = (size_t)gb * M * s->max_tiles_per_row;
    CKD(dalloc(&s->d_tile_status, ntiles));
@@ -513,6 +532,47 @@ static int pick_free(int a, int b, int c, int d)
 
 static int total_stages(const rt_solver *s) { return s->p.max_timesteps * (s->p.ts_method == 3 ? 4 : 1); }
 
+// launch the per-stage sweep kernel: X1 = E[i1n] / E[i1p] (mu<0 / mu>0 rows), X2 = E[i2], XC = E[ic] -> E[out]
+static int launch_stage(rt_solver *s, int kind, int i1n, int i1p, int i2, int ic, int out, bool counted)
+{
+   const rt_params &p = s->p;
+   const bool corr = p.use_correction && p.V != 0.0; // V == 0 makes total_correction exactly zero
+   SweepArgs a;
+   a.x1[0] = s->E[i1n]; a.x1[1] = s->E[i1p];
+   a.x2 = i2 >= 0 ? s->E[i2] : nullptr;
+   a.xc = ic >= 0 ? s->E[ic] : nullptr;
+   a.ix1[0] = i1n; a.ix1[1] = i1p; a.ix2 = i2 >= 0 ? i2 : 0; a.ixc = ic >= 0 ? ic : 0; a.iout = out;
+   a.coef = reinterpret_cast<const double2 *>(s->d_coef[kind] + (size_t)s->batch_start * p.M * COEF_ENTRY_DOUBLES);
+   a.tile_status = s->d_tile_status;
+   a.ticket = s->d_ticket; a.ticket_base = s->ticket_base; a.ticket_batch = s->ticket_batch;
+   a.epoch = ++s->epoch;
+   a.M = p.M; a.N = p.N; a.Np = s->Np;
+   a.rows = s->batch_groups * p.M;
+   a.tiles_per_row = s->tiles_per_row[kind];
+   a.reflective_left = (p.bc_left == 2) ? 1 : 0;
+   a.n_chains = a.reflective_left ? a.rows / 2 : a.rows;
+   a.tiles_per_chain = a.reflective_left ? 2 * a.tiles_per_row : a.tiles_per_row;
+   a.lookback_walk = s->lookback_walk ? 1 : 0;
+   a.l2_prefetch = s->l2_prefetch ? 1 : 0;
+
+   EventPair *ep = nullptr;
+   if (counted && event_begin(s, kind, &ep)) return 1;
+   int grid = 0;
+   CK(launch_sweep(kind, corr, s->threads[kind], s->cpt[kind], s->ring[kind], s->maps[kind], a, s->num_sms, s->st, &grid));
+   if (counted && event_end(s, ep)) return 1;
+   const unsigned long long total_tiles = (unsigned long long)a.n_chains * a.tiles_per_chain;
+   s->ticket_base += (total_tiles + s->ticket_batch - 1) / s->ticket_batch + (unsigned long long)grid;
+   s->last_grid = grid;
+   s->tm.kernel_launches++;
+   if (counted)
+   {
+      s->tm.sweep_launches[kind]++;
+      s->tm.stages++;
+      s->tm.unknown_stages += (long long)a.rows * p.N;
+   }
+   return 0;
+}
+
 // one stage sweep of the batch currently on the device
 static int run_one_stage(rt_solver *s)
 {
@@ -520,7 +580,6 @@ static int run_one_stage(rt_solver *s)
    const int it = s->stages_done;
    int kind, out;
    int i1n, i1p, i2 = -1, ic = -1; // buffer indices: X1 for mu<0 / mu>0 rows, X2, XC
-   const bool corr = p.use_correction && p.V != 0.0; // V == 0 makes total_correction exactly zero
    if (p.ts_method == 1)
    {
       kind = KIND_BE;
@@ -552,6 +611,7 @@ static int run_one_stage(rt_solver *s)
          i2 = s->i_prev;
          s->i_half_pos = s->i_ends;
          s->i_half_neg = out;
+         s->half_stale = false;
          break;
       case 2: // second BE predictor
          kind = KIND_BE;
@@ -569,40 +629,68 @@ static int run_one_stage(rt_solver *s)
       }
    }
    if (out < 0) return fail("internal: no free time-level buffer");
+   if (launch_stage(s, kind, i1n, i1p, i2, ic, out, true)) return 1;
+   s->i_ends = out;
+   s->stages_done++;
+   s->results_valid = false;
+   return 0;
+}
 
-   SweepArgs a;
-   a.x1[0] = s->E[i1n]; a.x1[1] = s->E[i1p];
-   a.x2 = i2 >= 0 ? s->E[i2] : nullptr;
-   a.xc = ic >= 0 ? s->E[ic] : nullptr;
-   a.ix1[0] = i1n; a.ix1[1] = i1p; a.ix2 = i2 >= 0 ? i2 : 0; a.ixc = ic >= 0 ? ic : 0; a.iout = out;
-   a.coef = reinterpret_cast<const double2 *>(s->d_coef[kind] + (size_t)s->batch_start * p.M * COEF_ENTRY_DOUBLES);
+// One whole BDF2 step (4 stage sweeps) in a single pass over the state (step_kernel.cu), out of place: afterwards
+// prev_ends is the old buffer; half_ends is not stored (rt_get_ends re-materialises it on demand).
+static int run_fused_step(rt_solver *s)
+{
+   const rt_params &p = s->p;
+   const int in = s->i_ends, out = pick_free(in, -1, -1, -1);
+   StepArgs a;
+   a.x = s->E[in];
+   a.ix = in; a.iout = out;
+   for (int k = 0; k < 3; ++k)
+      a.coef[k] = reinterpret_cast<const double2 *>(s->d_coef[k] + (size_t)s->batch_start * p.M * COEF_ENTRY_DOUBLES);
    a.tile_status = s->d_tile_status;
    a.ticket = s->d_ticket; a.ticket_base = s->ticket_base; a.ticket_batch = s->ticket_batch;
    a.epoch = ++s->epoch;
    a.M = p.M; a.N = p.N; a.Np = s->Np;
    a.rows = s->batch_groups * p.M;
-   a.tiles_per_row = s->tiles_per_row[kind];
+   a.tiles_per_row = s->step_tiles_per_row;
    a.reflective_left = (p.bc_left == 2) ? 1 : 0;
    a.n_chains = a.reflective_left ? a.rows / 2 : a.rows;
    a.tiles_per_chain = a.reflective_left ? 2 * a.tiles_per_row : a.tiles_per_row;
-   a.lookback_walk = s->lookback_walk ? 1 : 0;
    a.l2_prefetch = s->l2_prefetch ? 1 : 0;
-
+   const bool corr = p.use_correction && p.V != 0.0;
    EventPair *ep;
-   if (event_begin(s, kind, &ep)) return 1;
+   if (event_begin(s, 4, &ep)) return 1;
    int grid = 0;
-   CK(launch_sweep(kind, corr, s->threads[kind], s->cpt[kind], s->ring[kind], s->maps[kind], a, s->num_sms, s->st, &grid));
+   CK(launch_step(corr, s->step_threads, s->step_cpt, s->maps_step, a, s->num_sms, s->st, &grid));
    if (event_end(s, ep)) return 1;
    const unsigned long long total_tiles = (unsigned long long)a.n_chains * a.tiles_per_chain;
    s->ticket_base += (total_tiles + s->ticket_batch - 1) / s->ticket_batch + (unsigned long long)grid;
    s->last_grid = grid;
+   s->i_prev = in;
    s->i_ends = out;
-   s->stages_done++;
-   s->tm.sweep_launches[kind]++;
+   s->i_half_neg = s->i_half_pos = -1;
+   s->half_stale = true;
+   s->stages_done += 4;
+   s->tm.step_launches++;
    s->tm.kernel_launches++;
-   s->tm.stages++;
-   s->tm.unknown_stages += (long long)a.rows * p.N;
+   s->tm.stages += 4;
+   s->tm.unknown_stages += 4ll * a.rows * p.N;
    s->results_valid = false;
+   return 0;
+}
+
+// half_ends after a fused step: re-run the step's stage 0 (BE) and stage 1 (CN) from prev_ends with the per-stage kernel
+// into the two free buffers -- half = stage-1 result for mu<0 rows, stage-0 result for mu>0 rows
+static int materialize_half(rt_solver *s)
+{
+   if (!s->half_stale) return 0;
+   const int A = s->i_prev, C = pick_free(s->i_ends, A, -1, -1), D = pick_free(s->i_ends, A, C, -1);
+   if (A < 0 || C < 0 || D < 0) return fail("internal: cannot re-materialise half_ends");
+   if (launch_stage(s, KIND_BE, A, A, -1, -1, C, false)) return 1;
+   if (launch_stage(s, KIND_CN, C, C, A, -1, D, false)) return 1;
+   s->i_half_pos = C;
+   s->i_half_neg = D;
+   s->half_stale = false;
    return 0;
 }
 
@@ -612,9 +700,20 @@ static int finish_batch(rt_solver *s);
 static int run_stages(rt_solver *s, int n)
 {
    const int per_step = s->p.ts_method == 3 ? 4 : 1;
-   for (int k = 0; k < n; ++k)
+   for (int k = 0; k < n;)
    {
-      if (run_one_stage(s)) return 1;
+      // whole BDF2 steps go through the fused step kernel; anything else (BE / CN time stepping, a partial step
+      // requested through rt_run_stages) stage by stage
+      if (s->fused && s->p.ts_method == 3 && s->stages_done % 4 == 0 && n - k >= 4)
+      {
+         if (run_fused_step(s)) return 1;
+         k += 4;
+      }
+      else
+      {
+         if (run_one_stage(s)) return 1;
+         k += 1;
+      }
       if (s->step_phi_host && s->stages_done % per_step == 0)
          if (step_output(s)) return 1;
    }
@@ -807,7 +906,11 @@ extern "C" int rt_get_ends(rt_solver *s, int which, double *ends)
    int ineg, ipos;
    if (which == 0) ineg = ipos = s->i_ends;
    else if (which == 1) ineg = ipos = s->i_prev;
-   else if (which == 2) { ineg = s->i_half_neg; ipos = s->i_half_pos; }
+   else if (which == 2)
+   {
+      if (materialize_half(s)) return 1;
+      ineg = s->i_half_neg; ipos = s->i_half_pos;
+   }
    else return fail("rt_get_ends: which must be 0, 1 or 2");
    if (ineg < 0 || ipos < 0) { std::fill(ends, ends + n, 0.0); return 0; } // never assigned yet: zero (like a fresh resize in the oracle)
    double *d_tmp = nullptr;

@@ -1,0 +1,30 @@
+// step_kernel.cuh -- launch interface of the fused BDF2-step kernel (step_kernel.cu).
+#pragma once
+#include "rt_common.cuh"
+
+namespace rtk
+{
+// Arguments of one fused BDF2-step launch (all four stages of solver.cpp:706-809 for every owned row of the batch).
+struct StepArgs
+{
+   const double2 *x;     // ends^n, raw pointer (row-indexed with pitch Np): one-cell halo copies and the L2 prefetch
+   int ix, iout;         // ends^n and ends^(n+1) as indices into SweepMaps::m (out of place: prev_ends stays intact)
+   const double2 *coef[3]; // stepper constants of the batch's rows for BE(dt/2), CN(dt/2), BDF(dt/2, dt)
+   double2 *tile_status;   // FOUR {value, flag} words per tile: one look-back chain per stage
+   unsigned long long *ticket;
+   unsigned long long ticket_base;
+   int ticket_batch;
+   unsigned int epoch;
+   int M, N, Np;
+   int rows;
+   int tiles_per_row;
+   int reflective_left;
+   int n_chains, tiles_per_chain;
+   int l2_prefetch;
+};
+
+bool step_shape_supported(int threads, int cpt);
+// The caller must advance its ticket base by ceil(n_chains*tiles_per_chain / ticket_batch) + *grid_out afterwards.
+cudaError_t launch_step(bool corr, int threads, int cpt, const SweepMaps &maps, const StepArgs &a, int num_sms, cudaStream_t st,
+                        int *grid_out);
+} // namespace rtk

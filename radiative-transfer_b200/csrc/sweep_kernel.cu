@@ -47,104 +47,11 @@
 #include <cstdlib>
 
 #include "rt_common.cuh"
+#include "sweep_device.cuh"
 #include "sweep_kernel.cuh"
 
 namespace rtk
 {
-// ------------------------------------------------------------------------------------------ PTX wrappers
-__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count)
-{
-   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes)
-{
-   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(unsigned long long *bar, unsigned parity)
-{
-   unsigned ok;
-   asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
-      "selp.u32 %0, 1, 0, p;\n"
-      "}\n"
-      : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity)
-      : "memory");
-   return ok != 0;
-}
-// Every spin in this kernel is bounded: a wait that does not end within seconds of polling is a bug (or a dead
-// predecessor) and traps -- the launch fails loudly instead of hanging the device.
-constexpr long long SPIN_LIMIT = 1ll << 22;
-__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity)
-{
-   long long spins = 0;
-   while (!mbar_try_wait(bar, parity))
-      if (++spins > SPIN_LIMIT) __trap();
-}
-// 3-D tiled tensor load: coordinates (element in chunk, chunk in row, row)
-__device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *map, int c0, int c1, int c2, unsigned long long *bar)
-{
-   asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
-                ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
-                : "memory");
-}
-__device__ __forceinline__ void tma_store_3d(const CUtensorMap *map, int c0, int c1, int c2, const void *src)
-{
-   asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%1, %2, %3}], [%4];"
-                ::"l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(src))
-                : "memory");
-}
-// plain bulk copy global -> shared (16-byte granules), completing on an mbarrier
-__device__ __forceinline__ void bulk_load(void *dst, const void *src, unsigned bytes, unsigned long long *bar)
-{
-   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar))
-                : "memory");
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-// HBM -> L2 only (no shared-memory landing zone needed): used two tiles ahead of the tile being scanned
-__device__ __forceinline__ void prefetch_l2_bulk(const void *gmem, unsigned bytes)
-{
-   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gmem), "r"(bytes) : "memory");
-}
-
-template <int THREADS, int CPT_>
-struct TileShape
-{
-   static constexpr int CPT = CPT_; // cells per thread: 8 or 4
-   static constexpr int TILE = THREADS * CPT;
-   static constexpr int TILE_BYTES = TILE * 16;
-   static constexpr int WARPS = THREADS / 32;
-};
-
-// Byte offset of cell j of a tile in its SWIZZLE_128B shared-memory image (tile base 1024-byte aligned):
-// 128-byte line r = j/8 holds 8 cells; the 16-byte chunk index is XORed with (r mod 8).
-__device__ __forceinline__ int swz(int j) { return ((j >> 3) << 7) | ((((j & 7) ^ ((j >> 3) & 7))) << 4); }
-
-// Per-row stepper constants (identical formulas for both signs of mu, see rt_common.cuh).  They depend on
-// (stage kind, group, direction) only, so they are evaluated ONCE per solver by coef_table_kernel into a table of
-// 144-byte entries; the sweep kernel stages the entry of a tile's row in shared memory with the tile itself
-// (one cp.async group) -- no divisions, no dependent global loads of cross sections on the per-tile critical path.
-struct RowCoef
-{
-   double alpha, gamma, id, io; // recurrence factors and d/det, o/det
-   double qa, qb;               // q = qa + qb*(u+v) of the cell the source is evaluated at
-   double c_uu, c_uv, c_vu, c_vv;     // weights of X1 (ends or half_ends) in (ru, rv)
-   double p_uu, p_uv, p_vu, p_vv;     // weights of X2 (prev_ends) in (ru, rv)   [BDF]
-   double up1, up2;                   // weights of the upstream old-level outflow nodes X1(j-1).v, X2(j-1).v in ru
-   double kbc;                        // boundary multiplier
-   double inflow0;                    // kbc * bdry_cond of this (direction, group): inflow of the row's first cell
-};
-static_assert(sizeof(RowCoef) == COEF_ENTRY_DOUBLES * sizeof(double), "coefficient table entry size");
-static_assert(sizeof(RowCoef) % 16 == 0, "entries are staged with 16-byte cp.async copies");
-
 __device__ __forceinline__ RowCoef make_coef(int kind, bool corr, const CoefArgs &a, int g, int i)
 {
    RowCoef c;
@@ -217,79 +124,6 @@ void launch_coef_table(int kind, bool corr, const CoefArgs &a, double *table, cu
 {
    const int n = a.groups * a.M;
    coef_table_kernel<<<(n + 127) / 128, 128, 0, st>>>(kind, corr ? 1 : 0, a, reinterpret_cast<RowCoef *>(table));
-}
-
-// ---- tile status word: {value, flag} in ONE aligned 16-byte word, written and read with single 128-bit
-// accesses (the same single-copy-atomicity CUB's decoupled look-back relies on for 16-byte descriptors), so no
-// fence is needed between value and flag.
-__device__ __forceinline__ double2 ld_status(const double2 *p)
-{
-   double2 v;
-   asm volatile("ld.volatile.global.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p) : "memory");
-   return v;
-}
-__device__ __forceinline__ void st_status(double2 *p, double value, unsigned flag)
-{
-   const double f = __longlong_as_double((long long)flag);
-   asm volatile("st.volatile.global.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(value), "d"(f) : "memory");
-}
-__device__ __forceinline__ unsigned status_flag(const double2 &v) { return (unsigned)__double_as_longlong(v.y); }
-
-// Everything the CTA needs to know about one ticket; decoded by ONE thread and handed to the others through
-// shared memory.
-struct TileDesc
-{
-   long long row_off;    // element offset of the tile's first cell in a time-level buffer
-   long long status_idx; // index of the tile's look-back word
-   int row, p, sgn, tile_start, valid, junction;
-};
-
-// ticket -> (tile position p, chain) -> (row, tile in row); p-major so that all chains advance together.
-// Consecutive tickets are decoded by increments; the divisions only run after a jump (new batch of tickets).
-struct TicketCursor
-{
-   long long ticket;
-   int chain, p, gl, pp; // gl = chain / dm, pp = chain % dm with dm = M/2 (reflective left) or M
-};
-
-__device__ __forceinline__ TileDesc decode_ticket(const SweepArgs &a, TicketCursor &cu, long long ticket, int tile_cells)
-{
-   const int half_m = a.M >> 1, dm = a.reflective_left ? half_m : a.M;
-   if (ticket == cu.ticket + 1)
-   {
-      ++cu.chain;
-      if (++cu.pp == dm) { cu.pp = 0; ++cu.gl; }
-      if (cu.chain == a.n_chains) { cu.chain = 0; cu.gl = 0; cu.pp = 0; ++cu.p; }
-   }
-   else
-   {
-      cu.p = (int)(ticket / a.n_chains);
-      cu.chain = (int)(ticket - (long long)cu.p * a.n_chains);
-      cu.gl = cu.chain / dm;
-      cu.pp = cu.chain - cu.gl * dm;
-   }
-   cu.ticket = ticket;
-   TileDesc ti;
-   int t;
-   ti.p = cu.p;
-   if (a.reflective_left)
-   {
-      ti.sgn = (cu.p >= a.tiles_per_row) ? 1 : 0;
-      ti.row = cu.gl * a.M + (ti.sgn ? half_m + cu.pp : half_m - 1 - cu.pp);
-      t = ti.sgn ? cu.p - a.tiles_per_row : cu.p;
-   }
-   else
-   {
-      ti.sgn = (cu.pp >= half_m) ? 1 : 0;
-      ti.row = cu.chain;
-      t = cu.p;
-   }
-   ti.junction = (t == 0 && cu.p > 0) ? 1 : 0; // reflective: first tile of the mu>0 row, fed by the mirrored mu<0 row
-   ti.tile_start = t * tile_cells;
-   ti.valid = min(tile_cells, a.N - ti.tile_start);
-   ti.row_off = (long long)ti.row * a.Np + ti.tile_start;
-   ti.status_idx = (long long)cu.chain * a.tiles_per_chain + cu.p;
-   return ti;
 }
 
 // RING = number of shared-memory slots for the X1 / result tile:

@@ -4,7 +4,7 @@
 TAG=$1; shift
 OUT=gpurun_out/$TAG
 mkdir -p $OUT
-timeout 240 python -m pytest tests/test_gpu_parity.py -x -q -k "synthetic or golden_final" > $OUT/pytest.log 2>&1; echo "pytest exit $?"; tail -3 $OUT/pytest.log
+timeout 300 python -m pytest tests/test_gpu_parity.py tests/test_gpu_edge.py -x -q > $OUT/pytest.log 2>&1; echo "pytest exit $?"; tail -4 $OUT/pytest.log
 i=0
 for cfg in "$@"; do
   i=$((i+1))
@@ -14,8 +14,8 @@ for cfg in "$@"; do
 import json,sys
 try:
     d=json.load(open(sys.argv[1]))
-    r=d["roofline"]; bk=r["by_kind"]
-    print(f"{sys.argv[2]:50s} value {d['value']:.4e} ms/step {d['ms_per_step']:.2f} frac {r['frac']:.3f} | " + " ".join(f"{k} {v['GBps']:.0f}" for k,v in bk.items()) + f" | grid {d['sweep_grid']} clk {d['clocks']['sm_mhz']} {d['clocks']['reasons']}")
+    r=d["roofline"]; bk=r.get("by_kind",{})
+    print(f"{sys.argv[2]:44s} value {d['value']:.4e} ms/step {d['ms_per_step']:.2f} frac {r['frac']:.3f} avg_launch_ms {r['avg_launch_ms']:.2f} | " + " ".join(f"{k} {v['GBps']:.0f}" for k,v in bk.items()) + f" | grid {d['sweep_grid']} clk {d['clocks']['sm_mhz']} pw {d['clocks'].get('power_w_max')} {d['clocks']['reasons']}")
 except Exception as e:
     print("failed:", e)
 PY
