@@ -41,6 +41,7 @@ WORKLOADS = {
     "c5": (32, 4096, 1 << 20, 1, 1),
     "small": (16, 32, 1 << 16, 2, 1),
     "mid": (16, 64, 1 << 18, 2, 1),
+    "wide": (16, 128, 1 << 17, 2, 1),  # as many rows (2048) as one resident batch of c4, 1/8 of its cells: profiling
 }
 
 

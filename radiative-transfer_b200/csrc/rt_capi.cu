@@ -60,6 +60,7 @@ struct rt_solver
    double *d_sigma = nullptr, *d_srcB = nullptr, *d_de_ave = nullptr, *d_sums = nullptr;
    double *d_psi_source = nullptr, *d_bdry = nullptr;
    double *d_coef[3] = {nullptr, nullptr, nullptr}; // per stage kind: Gl*M entries of COEF_ENTRY_DOUBLES doubles
+   double *d_coef_step = nullptr;                   // the three kinds packed per row (STEP_COEF_DOUBLES each)
    double sums[3] = {0, 0, 0};
    // batching
    int Gl = 0, Gb = 0, n_batches = 0, Np = 0;
@@ -98,7 +99,7 @@ struct rt_solver
    bool timing_on = true;
    // fused BDF2-step kernel (step_kernel.cu): RT_CUDA_FUSED=0 runs every step stage by stage
    bool fused = true, half_stale = false;
-   int step_threads = 64, step_cpt = 8, step_tile_cells = 512, step_tiles_per_row = 0;
+   int step_threads = 32, step_cpt = 8, step_chain = 4, step_box_cells = 256, step_tile_cells = 1024, step_tiles_per_row = 0;
    SweepMaps maps_step;
    int ticket_batch = 8;       // tickets per atomic draw (RT_CUDA_TICKET_BATCH)
    bool l2_prefetch = true;    // RT_CUDA_L2_PREFETCH=0 switches the two-tiles-ahead L2 prefetch off
@@ -282,6 +283,8 @@ static int compute_group_tables(rt_solver *s)
       launch_coef_table(kind, corr, c, s->d_coef[kind], s->st);
       s->tm.kernel_launches++;
    }
+   launch_pack_step_coef(s->d_coef[0], s->d_coef[1], s->d_coef[2], s->d_coef_step, s->Gl * p.M, s->st);
+   s->tm.kernel_launches++;
    CK(cudaGetLastError());
    return 0;
 }
@@ -319,7 +322,7 @@ extern "C" int rt_destroy(rt_solver *s)
                      s->d_dEB, s->d_dsig, s->d_dkap, s->d_cor1, s->d_cor2, s->d_cor3, s->d_sigma, s->d_srcB, s->d_de_ave,
                      s->d_sums, s->d_psi_source, s->d_bdry, s->d_phi, s->d_phip, s->d_F,
                      s->d_balance, s->d_left, s->d_right, s->d_stage, s->d_step_phi[0], s->d_step_phi[1],
-                     s->d_coef[0], s->d_coef[1], s->d_coef[2]};
+                     s->d_coef[0], s->d_coef[1], s->d_coef[2], s->d_coef_step};
    for (double *t : tabs) if (t) cudaFree(t);
    for (int k = 0; k < 4; ++k) if (s->E[k]) cudaFreeAsync(s->E[k], s->st);
    if (s->st) cudaStreamSynchronize(s->st);
@@ -411,7 +414,11 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       env3("RT_CUDA_STEP_THREADS", st3);
       env3("RT_CUDA_STEP_CPT", sc3);
       if (step_shape_supported(st3[0], sc3[0])) { s->step_threads = st3[0]; s->step_cpt = sc3[0]; }
-      s->step_tile_cells = s->step_threads * s->step_cpt;
+      const char *ce = getenv("RT_CUDA_STEP_CHAIN");
+      if (ce && step_chain_supported(atoi(ce))) s->step_chain = atoi(ce);
+      if (s->step_threads != 32) s->step_chain = 1;
+      s->step_box_cells = s->step_threads * s->step_cpt;          // one TMA box: a CTA tile, or one warp's sub-tile
+      s->step_tile_cells = s->step_box_cells * s->step_chain;     // cells per ticket
       s->step_tiles_per_row = (N + s->step_tile_cells - 1) / s->step_tile_cells;
       s->max_tiles_per_row = std::max(s->max_tiles_per_row, 4 * s->step_tiles_per_row); // 4 look-back words per tile
       const char *fe = getenv("RT_CUDA_FUSED");
@@ -441,6 +448,7 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
    CKD(dalloc(&s->d_psi_source, (size_t)M * G)); CKD(dalloc(&s->d_bdry, (size_t)M * G));
    CKD(dalloc(&s->d_balance, s->Gl)); CKD(dalloc(&s->d_left, s->Gl)); CKD(dalloc(&s->d_right, s->Gl));
    for (int k = 0; k < 3; ++k) CKD(dalloc(&s->d_coef[k], (size_t)s->Gl * M * COEF_ENTRY_DOUBLES));
+   CKD(dalloc(&s->d_coef_step, (size_t)s->Gl * M * STEP_COEF_DOUBLES));
    CKD(dalloc(&s->d_ticket, 1));
    CKC(cudaMemsetAsync(s->d_ticket, 0, sizeof(unsigned long long), s->st));
    CKC(cudaMemsetAsync(s->d_B, 0, G * sizeof(double), s->st));
@@ -486,7 +494,7 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
    {
       CKD(pool_alloc(s, &s->E[k], s->buf_elems));
       for (int kind = 0; kind < 3; ++kind) CKC(make_tile_map(&s->maps[kind].m[k], s->E[k], gb * M, s->Np, s->tile_cells[kind]));
-      CKC(make_tile_map(&s->maps_step.m[k], s->E[k], gb * M, s->Np, s->step_tile_cells));
+      CKC(make_tile_map(&s->maps_step.m[k], s->E[k], gb * M, s->Np, s->step_box_cells));
    }
    const size_t ntiles = (size_t)gb * M * s->max_tiles_per_row;
    CKD(dalloc(&s->d_tile_status, ntiles));
@@ -647,8 +655,10 @@ static int run_fused_step(rt_solver *s)
    a.ix = in; a.iout = out;
    for (int k = 0; k < 3; ++k)
       a.coef[k] = reinterpret_cast<const double2 *>(s->d_coef[k] + (size_t)s->batch_start * p.M * COEF_ENTRY_DOUBLES);
+   a.coef_step = s->d_coef_step + (size_t)s->batch_start * p.M * STEP_COEF_DOUBLES;
    a.tile_status = s->d_tile_status;
-   a.ticket = s->d_ticket; a.ticket_base = s->ticket_base; a.ticket_batch = s->ticket_batch;
+   const int tb = std::min(s->ticket_batch, 8); // the warp-tile kernel decodes a batch with 8 lanes at most
+   a.ticket = s->d_ticket; a.ticket_base = s->ticket_base; a.ticket_batch = tb;
    a.epoch = ++s->epoch;
    a.M = p.M; a.N = p.N; a.Np = s->Np;
    a.rows = s->batch_groups * p.M;
@@ -661,10 +671,10 @@ static int run_fused_step(rt_solver *s)
    EventPair *ep;
    if (event_begin(s, 4, &ep)) return 1;
    int grid = 0;
-   CK(launch_step(corr, s->step_threads, s->step_cpt, s->maps_step, a, s->num_sms, s->st, &grid));
+   CK(launch_step(corr, s->step_threads, s->step_cpt, s->step_chain, s->maps_step, a, s->num_sms, s->st, &grid));
    if (event_end(s, ep)) return 1;
    const unsigned long long total_tiles = (unsigned long long)a.n_chains * a.tiles_per_chain;
-   s->ticket_base += (total_tiles + s->ticket_batch - 1) / s->ticket_batch + (unsigned long long)grid;
+   s->ticket_base += (total_tiles + tb - 1) / tb + (unsigned long long)grid;
    s->last_grid = grid;
    s->i_prev = in;
    s->i_ends = out;

@@ -348,11 +348,12 @@ static cudaError_t launch_one(const SweepMaps &maps, const StepArgs &a, int num_
    return cudaGetLastError();
 }
 
-bool step_shape_supported(int threads, int cpt) { return (threads == 64 || threads == 128) && (cpt == 4 || cpt == 8); }
+bool step_shape_supported(int threads, int cpt) { return (threads == 32 || threads == 64 || threads == 128) && (cpt == 4 || cpt == 8); }
 
-cudaError_t launch_step(bool corr, int threads, int cpt, const SweepMaps &maps, const StepArgs &a, int num_sms, cudaStream_t st,
-                        int *grid_out)
+cudaError_t launch_step(bool corr, int threads, int cpt, int chain_warps, const SweepMaps &maps, const StepArgs &a, int num_sms,
+                        cudaStream_t st, int *grid_out)
 {
+   if (threads == 32) return launch_step_warp(corr, cpt, chain_warps, maps, a, num_sms, st, grid_out);
    switch ((threads * 16 + cpt) * 2 + (corr ? 1 : 0))
    {
    case (64 * 16 + 8) * 2 + 0: return launch_one<false, 64, 8>(maps, a, num_sms, st, grid_out);

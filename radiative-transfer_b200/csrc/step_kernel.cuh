@@ -10,6 +10,7 @@ struct StepArgs
    const double2 *x;     // ends^n, raw pointer (row-indexed with pitch Np): one-cell halo copies and the L2 prefetch
    int ix, iout;         // ends^n and ends^(n+1) as indices into SweepMaps::m (out of place: prev_ends stays intact)
    const double2 *coef[3]; // stepper constants of the batch's rows for BE(dt/2), CN(dt/2), BDF(dt/2, dt)
+   const double *coef_step; // the same constants packed per row, STEP_COEF_DOUBLES each (warp-tile kernel)
    double2 *tile_status;   // FOUR {value, flag} words per tile: one look-back chain per stage
    unsigned long long *ticket;
    unsigned long long ticket_base;
@@ -23,8 +24,16 @@ struct StepArgs
    int l2_prefetch;
 };
 
+constexpr int STEP_COEF_DOUBLES = 64; // packed BE + CN + BDF constants of one row (step_warp_kernel.cu)
+
+// threads = 32: one warp per tile (step_warp_kernel.cu, the default); 64 / 128: CTA-wide tiles (step_kernel.cu)
 bool step_shape_supported(int threads, int cpt);
+void launch_pack_step_coef(const double *be, const double *cn, const double *bdf, double *out, int rows, cudaStream_t st);
+bool step_chain_supported(int chain_warps); // warps (consecutive 32*cpt-cell sub-tiles) per CTA tile: 1, 2, 4 or 8
+cudaError_t launch_step_warp(bool corr, int cpt, int chain_warps, const SweepMaps &maps, const StepArgs &a, int num_sms, cudaStream_t st,
+                             int *grid_out);
 // The caller must advance its ticket base by ceil(n_chains*tiles_per_chain / ticket_batch) + *grid_out afterwards.
-cudaError_t launch_step(bool corr, int threads, int cpt, const SweepMaps &maps, const StepArgs &a, int num_sms, cudaStream_t st,
-                        int *grid_out);
+// chain_warps only matters for threads = 32.
+cudaError_t launch_step(bool corr, int threads, int cpt, int chain_warps, const SweepMaps &maps, const StepArgs &a, int num_sms,
+                        cudaStream_t st, int *grid_out);
 } // namespace rtk

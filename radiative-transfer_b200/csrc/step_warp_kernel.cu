@@ -1,0 +1,574 @@
+// step_warp_kernel.cu -- the fused BDF2-step kernel (see step_kernel.cu for the stage algebra) built from WARP tiles.
+//
+// Profile of the CTA-wide version (profiles/r01_v5_step_cta_ncu.txt): 24 % of the warp time waits at __syncthreads,
+// another ~40 % hangs on work only thread 0 does (tickets, TMA issue, look-back), 12 warps per SM.  A row's recurrence
+// needs no CTA-wide barrier at all:
+//
+//   * a warp owns a sub-tile of 32 lanes x CPT cells (256 cells, 4 KB) with its own TMA pipeline (2 x X, one H/OUT
+//     tile, one mbarrier per X slot).  The NW warps of a CTA take NW CONSECUTIVE sub-tiles of one row (the CTA's tile,
+//     one ticket) and hand the recurrence carry from warp to warp through shared memory ({value, sequence} words, a
+//     few hundred cycles per hop); only warp 0 looks back to the previous CTA tile through global memory (a few
+//     thousand cycles per hop under load -- with single-warp tiles that hop bounds the whole launch once there are
+//     more tiles in flight than chains).  No __syncthreads after the prologue: the warps of a CTA run skewed by one
+//     scan each and never wait for each other in steady state.
+//   * seeded scan: the carry into the sub-tile is folded into lane 0's chunk BEFORE the warp scan, so the scan
+//     delivers true values directly: no alpha^(CPT*lane) powers, no fix-up pass.  Warp 0 probes the predecessor
+//     tile's four status words (one per stage) when the tile starts, lanes 0..3 holding one word each.
+//   * pass 2 re-runs the cell recurrence v_j = alpha v_(j-1) + beta_j from the true inflow (no alpha^j powers).
+//   * tickets are drawn in batches (one atomic per batch) by warp 0 and the whole batch is decoded by as many lanes
+//     in parallel into a 16-entry descriptor ring shared by the CTA's warps.
+//   * only the stage result that is this row's half_ends (stage 0 for mu>0 rows, stage 1 for mu<0 rows) is
+//     parked in shared memory, thread-private; the stage-3 result overwrites it in place and leaves by TMA store.
+//   * the row constants of the three stage kinds come as one packed 256-byte entry (pack_step_coef_kernel).
+#include <cstdlib>
+#include <type_traits>
+
+#include "rt_common.cuh"
+#include "step_kernel.cuh"
+#include "sweep_device.cuh"
+
+namespace rtk
+{
+// packed per-row constants of a BDF2 step: 64 doubles.  *_POW: alpha^1 .. alpha^8 of the kind (pass 2 and the scan
+// factor alpha^CPT come from here: no power chains on the critical path)
+enum StepCoefIndex
+{
+   SC_BE = 0,      // alpha gamma id io qa qb c_uu inflow0
+   SC_BE_POW = 8,
+   SC_CN = 16,     // alpha gamma id io qa qb c_uu c_uv up2 inflow0
+   SC_CN_POW = 26,
+   SC_BDF = 34,    // alpha gamma id io qa qb c_uu c_uv p_uu p_uv up1 up2 inflow0
+   SC_BDF_POW = 48,
+   SC_DOUBLES = STEP_COEF_DOUBLES
+};
+static_assert(SC_BDF + 13 <= SC_BDF_POW && SC_BDF_POW + 8 <= SC_DOUBLES, "packed entry layout");
+
+__global__ void pack_step_coef_kernel(const RowCoef *__restrict__ be, const RowCoef *__restrict__ cn,
+                                      const RowCoef *__restrict__ bdf, double *__restrict__ out, int rows)
+{
+   const int r = blockIdx.x * blockDim.x + threadIdx.x;
+   if (r >= rows) return;
+   double *o = out + (size_t)r * SC_DOUBLES;
+   const RowCoef a = be[r], b = cn[r], c = bdf[r];
+   for (int i = 0; i < SC_DOUBLES; ++i) o[i] = 0.0;
+   o[SC_BE + 0] = a.alpha; o[SC_BE + 1] = a.gamma; o[SC_BE + 2] = a.id; o[SC_BE + 3] = a.io;
+   o[SC_BE + 4] = a.qa; o[SC_BE + 5] = a.qb; o[SC_BE + 6] = a.c_uu; o[SC_BE + 7] = a.inflow0;
+   o[SC_CN + 0] = b.alpha; o[SC_CN + 1] = b.gamma; o[SC_CN + 2] = b.id; o[SC_CN + 3] = b.io;
+   o[SC_CN + 4] = b.qa; o[SC_CN + 5] = b.qb; o[SC_CN + 6] = b.c_uu; o[SC_CN + 7] = b.c_uv;
+   o[SC_CN + 8] = b.up2; o[SC_CN + 9] = b.inflow0;
+   o[SC_BDF + 0] = c.alpha; o[SC_BDF + 1] = c.gamma; o[SC_BDF + 2] = c.id; o[SC_BDF + 3] = c.io;
+   o[SC_BDF + 4] = c.qa; o[SC_BDF + 5] = c.qb; o[SC_BDF + 6] = c.c_uu; o[SC_BDF + 7] = c.c_uv;
+   o[SC_BDF + 8] = c.p_uu; o[SC_BDF + 9] = c.p_uv; o[SC_BDF + 10] = c.up1; o[SC_BDF + 11] = c.up2;
+   o[SC_BDF + 12] = c.inflow0;
+   double pa = 1.0, pb = 1.0, pc = 1.0;
+   for (int j = 0; j < 8; ++j)
+   {
+      pa *= a.alpha; pb *= b.alpha; pc *= c.alpha;
+      o[SC_BE_POW + j] = pa; o[SC_CN_POW + j] = pb; o[SC_BDF_POW + j] = pc;
+   }
+}
+
+void launch_pack_step_coef(const double *be, const double *cn, const double *bdf, double *out, int rows, cudaStream_t st)
+{
+   pack_step_coef_kernel<<<(rows + 127) / 128, 128, 0, st>>>(reinterpret_cast<const RowCoef *>(be), reinterpret_cast<const RowCoef *>(cn),
+                                                            reinterpret_cast<const RowCoef *>(bdf), out, rows);
+}
+
+// one tile descriptor of the ring: 16 bytes
+struct WarpTile
+{
+   int row;   // row of the batch, -1 = ticket past the end
+   int chain; // look-back chain (row, or pair of mirrored rows with a reflective left boundary)
+   int p;     // tile position in the chain
+   int tf;    // tile in row * 4 + sgn * 2 + junction
+};
+
+// right-hand sides of one cell -> (beta, U); same formulas as stage_pass1 (sweep_device.cuh)
+template <int KIND, bool CORR>
+__device__ __forceinline__ void cell_rhs(const double *c, const double2 x1, const double2 x2, const double xs, const double up1,
+                                         const double up2, const bool use_up, double &beta, double &U)
+{
+   // c: this kind's slice of the packed entry
+   const double id = c[2], io = c[3];
+   double q = c[4];
+   if (CORR) q = fma(c[5], xs, c[4]);
+   double ru, rv;
+   if (KIND == KIND_BE)
+   {
+      ru = fma(c[6], x1.x, q);
+      rv = fma(c[6], x1.y, q);
+   }
+   else
+   {
+      ru = q + c[6] * x1.x + c[7] * x1.y;
+      rv = q - c[7] * x1.x + c[6] * x1.y;
+   }
+   if (KIND == KIND_BDF)
+   {
+      ru += c[8] * x2.x + c[9] * x2.y;
+      rv += c[8] * x2.y - c[9] * x2.x;
+   }
+   if (KIND != KIND_BE && use_up)
+   {
+      if (KIND == KIND_BDF) ru += c[10] * up1 + c[11] * up2;
+      else ru += c[8] * up2;
+   }
+   beta = io * ru + id * rv;
+   U = id * ru - io * rv;
+}
+
+// {value, sequence} carry words between the warps of a CTA: one 128-bit shared-memory access each way
+__device__ __forceinline__ double2 lds_word(const double2 *p)
+{
+   double2 v;
+   asm volatile("ld.volatile.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(smem_u32(p)) : "memory");
+   return v;
+}
+__device__ __forceinline__ void sts_word(double2 *p, double value, int seq1)
+{
+   const double f = __longlong_as_double((long long)seq1);
+   asm volatile("st.volatile.shared.v2.f64 [%0], {%1, %2};" ::"r"(smem_u32(p)), "d"(value), "d"(f) : "memory");
+}
+__device__ __forceinline__ int ld_flag(const int *p)
+{
+   int v;
+   asm volatile("ld.volatile.shared.s32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)) : "memory");
+   return v;
+}
+__device__ __forceinline__ void st_flag(int *p, int v)
+{
+   asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory");
+}
+
+template <bool CORR, int CPT, int NW>
+__global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __grid_constant__ SweepMaps maps, const StepArgs a)
+{
+   constexpr int WT = 32 * CPT, WT_BYTES = WT * 16; // one warp's sub-tile
+   constexpr int TILE = WT * NW;                    // the CTA's tile: NW consecutive sub-tiles of one row
+   static_assert(CPT == 8 || CPT == 4, "the swizzled tile image is conflict-free for 4 or 8 cells per thread");
+
+   // dynamic shared memory, 1024-byte aligned by hand: per warp [X slot 0][X slot 1][H / OUT]
+   extern __shared__ unsigned char smem_raw[];
+   unsigned char *const tiles = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+   __shared__ __align__(16) double s_coef[NW][2][SC_DOUBLES];
+   __shared__ __align__(16) double2 s_halo[NW][2];     // X at the cell upstream of the sub-tile
+   __shared__ __align__(16) double2 s_carry[4][4][NW]; // [tile sequence & 3][stage][warp]: inclusive value of a sub-tile
+   __shared__ __align__(16) WarpTile s_desc[16];
+   __shared__ __align__(8) unsigned long long s_full[NW][2];
+   __shared__ int s_decoded; // ring entries decoded by warp 0 so far
+   __shared__ int s_done;    // tiles the last warp has finished
+
+   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+   const unsigned flag_incl = a.epoch * 2u + 2u;
+   const long long total_tiles = (long long)a.n_chains * a.tiles_per_chain;
+   const int half_m = a.M >> 1, dm = a.reflective_left ? half_m : a.M;
+   const int batch = a.ticket_batch; // <= 8 (launch_step_warp)
+   unsigned char *const wt = tiles + warp * 3 * WT_BYTES;
+   unsigned char *const th = wt + 2 * WT_BYTES;
+
+   // ---- tickets (warp 0): one atomic per batch, the batch decoded by `batch` lanes in parallel into the ring
+   long long q_start = -1; // start ticket of the last draw
+   bool ended = false;     // a ticket past the end has been seen: no more draws
+   int dec = 0;            // ring entries decoded so far (sequence numbers 0 .. dec-1)
+   auto draw = [&]() {
+      unsigned long long t0 = 0;
+      if (lane == 0) t0 = atomicAdd(a.ticket, 1ull);
+      t0 = __shfl_sync(0xffffffffu, t0, 0);
+      q_start = (long long)(t0 - a.ticket_base) * batch;
+      if (lane < batch)
+      {
+         const long long t = q_start + lane;
+         WarpTile d;
+         d.row = -1; d.chain = 0; d.p = 0; d.tf = 0;
+         if (t < total_tiles)
+         {
+            int p, chain;
+            if (total_tiles < 0x7fffffffll)
+            {
+               p = (int)((unsigned)t / (unsigned)a.n_chains);
+               chain = (int)((unsigned)t - (unsigned)p * (unsigned)a.n_chains);
+            }
+            else
+            {
+               p = (int)(t / a.n_chains);
+               chain = (int)(t - (long long)p * a.n_chains);
+            }
+            const int gl = chain / dm, pp = chain - gl * dm;
+            int sgn, row, tr;
+            if (a.reflective_left)
+            {
+               sgn = (p >= a.tiles_per_row) ? 1 : 0;
+               row = gl * a.M + (sgn ? half_m + pp : half_m - 1 - pp);
+               tr = sgn ? p - a.tiles_per_row : p;
+            }
+            else
+            {
+               sgn = (pp >= half_m) ? 1 : 0;
+               row = chain;
+               tr = p;
+            }
+            d.row = row; d.chain = chain; d.p = p;
+            d.tf = tr * 4 + sgn * 2 + ((tr == 0 && p > 0) ? 1 : 0);
+         }
+         s_desc[(dec + lane) & 15] = d;
+      }
+      if (q_start + batch > total_tiles) ended = true;
+      dec += batch;
+      __syncwarp();
+      if (NW > 1 && lane == 0)
+      {
+         __threadfence_block();
+         st_flag(&s_decoded, dec);
+      }
+   };
+
+   // ---- lane 0 of each warp: TMA / bulk loads of the warp's sub-tile of tile d into its pipeline buffer b
+   auto issue_loads = [&](const WarpTile &d, int sub_start, int b) {
+      const bool halo = sub_start > 0;
+      mbar_expect_tx(&s_full[warp][b], (unsigned)(WT_BYTES + SC_DOUBLES * 8) + (halo ? 16u : 0u));
+      tma_load_3d(wt + b * WT_BYTES, &maps.m[a.ix], 0, sub_start >> 3, d.row, &s_full[warp][b]);
+      bulk_load(&s_coef[warp][b][0], a.coef_step + (size_t)d.row * SC_DOUBLES, (unsigned)(SC_DOUBLES * 8), &s_full[warp][b]);
+      if (halo) bulk_load(&s_halo[warp][b], a.x + (size_t)d.row * a.Np + sub_start - 1, 16u, &s_full[warp][b]);
+   };
+
+   if (lane == 0)
+   {
+      mbar_init(&s_full[warp][0], 1);
+      mbar_init(&s_full[warp][1], 1);
+      fence_proxy_async();
+   }
+   if (NW > 1)
+   {
+      for (int i = threadIdx.x; i < 4 * 4 * NW; i += 32 * NW) (&s_carry[0][0][0])[i] = make_double2(0.0, 0.0);
+      if (threadIdx.x == 0) { s_decoded = 0; s_done = 0; }
+      __syncthreads(); // the only CTA-wide barrier
+   }
+   else __syncwarp();
+
+   unsigned phase = 0;
+   int issued = 0; // tiles whose loads this warp has issued (or skipped: sub-tile past the end of the row)
+   for (int seq = 0;; ++seq)
+   {
+      int avail;
+      if (warp == 0)
+      {
+         while (!ended && dec < seq + 3) draw();
+         avail = dec;
+         if (NW > 1)
+         {
+            // back-pressure: at most two tiles ahead of the last warp (bounds the carry and descriptor rings)
+            long long spins = 0;
+            while (ld_flag(&s_done) < seq - 2)
+               if (++spins > SPIN_LIMIT) __trap();
+         }
+      }
+      else
+      {
+         long long spins = 0;
+         while ((avail = ld_flag(&s_decoded)) <= seq)
+            if (++spins > SPIN_LIMIT) __trap();
+         __threadfence_block();
+      }
+      const WarpTile ti = s_desc[seq & 15];
+      if (ti.row < 0) break;
+      __syncwarp(); // every lane is done with the X slot, constants and halo that are refilled now
+      while (issued <= seq + 1 && issued < avail)
+      {
+         if (lane == 0)
+         {
+            const WarpTile d = s_desc[issued & 15];
+            const int sub = (d.tf >> 2) * TILE + warp * WT;
+            if (d.row >= 0 && sub < a.N) issue_loads(d, sub, issued & 1);
+            if (a.l2_prefetch && issued + 1 < avail)
+            {
+               const WarpTile da = s_desc[(issued + 1) & 15];
+               const int sa = (da.tf >> 2) * TILE + warp * WT;
+               if (da.row >= 0 && sa < a.N) prefetch_l2_bulk(a.x + (size_t)da.row * a.Np + sa, (unsigned)min(WT, a.N - sa) * 16u);
+            }
+         }
+         ++issued;
+      }
+      const int tile_start = (ti.tf >> 2) * TILE, sub_start = tile_start + warp * WT;
+      const int valid_total = min(TILE, a.N - tile_start);
+      const int valid = min(WT, valid_total - warp * WT); // cells of this warp's sub-tile inside the row (<= 0: none)
+      if (valid > 0)
+      {
+         const int buf = seq & 1;
+         const bool sgn = (ti.tf & 2) != 0, junction = (ti.tf & 1) != 0 && warp == 0;
+         const bool is_last = valid_total <= (warp + 1) * WT; // the row's tile ends inside (or at the end of) this sub-tile
+         const bool first_sub = (warp == 0);                  // carry from the previous CTA tile / the boundary
+         double2 *const status = a.tile_status + 4 * ((size_t)ti.chain * a.tiles_per_chain + ti.p);
+         double2 *const carry_slot = &s_carry[seq & 3][0][0];
+
+         // warp 0: probe the predecessor tile's four look-back words now; lane k holds the word of stage k
+         double2 wpre = make_double2(0.0, 0.0);
+         if (first_sub && ti.p > 0 && lane < 4) wpre = ld_status(status - 4 + lane);
+
+         mbar_wait(&s_full[warp][buf], (phase >> buf) & 1u); // sub-tile, constants and halo cell have landed
+         phase ^= 1u << buf;
+
+         const unsigned char *const sx = wt + buf * WT_BYTES;
+         const double *const cf = s_coef[warp][buf];
+         const int j0 = lane * CPT;
+         const bool row_first = (sub_start == 0) && (lane == 0);
+         auto ldx = [&](int j) { return *reinterpret_cast<const double2 *>(sx + swz(j)); };
+         // X outflow node of the cell upstream of this lane's first cell
+         double up_x = 0.0;
+         if (lane == 0) { if (sub_start > 0) up_x = s_halo[warp][buf].y; }
+         else up_x = ldx(j0 - 1).y;
+
+         // ---- carry into the sub-tile for stage k.  Every lane runs the same loads (one broadcast access), so the warp
+         // stays converged: no divergent spin, no reconvergence code around the shuffles that follow.
+         auto carry_in = [&](auto kc, const double kbc, const double inflow0) -> double {
+            constexpr int k = decltype(kc)::value;
+            if (first_sub)
+            {
+               // boundary inflow, or the previous CTA tile's inclusive value (global look-back word)
+               double2 w;
+               w.x = __shfl_sync(0xffffffffu, wpre.x, k);
+               w.y = __shfl_sync(0xffffffffu, wpre.y, k);
+               if (ti.p == 0) return inflow0;
+               long long spins = 0;
+               while ((int)(status_flag(w) - flag_incl) < 0)
+               {
+                  w = ld_status(status - 4 + k);
+                  if (++spins > SPIN_LIMIT) __trap();
+               }
+               return junction ? kbc * w.x : w.x;
+            }
+            // the previous warp's inclusive value of this tile and stage, through shared memory
+            const double2 *src = carry_slot + k * NW + (warp - 1);
+            long long spins = 0;
+            double2 w = lds_word(src);
+            while ((int)__double_as_longlong(w.y) != seq + 1)
+            {
+               w = lds_word(src);
+               if (++spins > SPIN_LIMIT) __trap();
+            }
+            return w.x;
+         };
+         // ---- seeded warp scan of one stage: incl = this lane's chunk total with zero inflow; returns the true inflow
+         // of the lane's chunk and publishes the sub-tile's inclusive value (ragged sub-tiles publish after pass 2)
+         auto scan = [&](auto kc, const double achunk, const double kbc, const double inflow0, double incl) -> double {
+            constexpr int k = decltype(kc)::value;
+            double f = achunk; // alpha^CPT
+            const double ctile = carry_in(kc, kbc, inflow0);
+            const double seeded = fma(f, ctile, incl);
+            if (lane == 0) incl = seeded;
+#pragma unroll
+            for (int s = 0; s < 5; ++s)
+            {
+               const double o = __shfl_up_sync(0xffffffffu, incl, 1 << s);
+               const double t = fma(f, o, incl);
+               if (lane >= (1 << s)) incl = t;
+               f = f * f;
+            }
+            double cin = __shfl_up_sync(0xffffffffu, incl, 1);
+            if (lane == 0) cin = ctile;
+            if (lane == 31)
+            {
+               if (!is_last) sts_word(carry_slot + k * NW + warp, incl, seq + 1);
+               else if (valid == WT) st_status(status + k, incl, flag_incl);
+            }
+            return cin;
+         };
+         // ragged sub-tile: the outflow node of the row's last cell is the chain's inclusive value
+         auto publish_ragged = [&](auto kc, const double (&v)[CPT]) {
+            constexpr int k = decltype(kc)::value;
+            const int last = valid - 1;
+            if (lane == last / CPT)
+            {
+               const int jo = last % CPT;
+               double vs = v[0];
+#pragma unroll
+               for (int jj = 1; jj < CPT; ++jj)
+                  if (jj <= jo) vs = v[jj];
+               st_status(status + k, vs, flag_incl);
+            }
+         };
+
+         double wl[CPT], U[CPT], vv[CPT]; // wl: the lane's local scan with zero inflow
+         double2 r[CPT];
+         double up_h = 0.0;
+
+         // ================= stage 0: BE predictor, x1 = X (ends^n)
+         {
+            const double *c = cf + SC_BE, *pw = cf + SC_BE_POW;
+            const double alpha = c[0], gamma = c[1];
+            double w = 0.0;
+#pragma unroll
+            for (int jj = 0; jj < CPT; ++jj)
+            {
+               const double2 x = ldx(j0 + jj);
+               double b;
+               cell_rhs<KIND_BE, CORR>(c, x, x, x.x + x.y, 0.0, 0.0, false, b, U[jj]);
+               w = fma(alpha, w, b);
+               wl[jj] = w;
+            }
+            const double cin = scan(std::integral_constant<int, 0>{}, pw[CPT - 1], 1.0, c[7], w);
+            if (sgn) up_h = cin;
+            if (lane == 0) bulk_wait_read<0>(); // the previous tile's TMA store has read H / OUT
+            __syncwarp();
+            double v = cin;
+#pragma unroll
+            for (int jj = 0; jj < CPT; ++jj)
+            {
+               const double vn = fma(pw[jj], cin, wl[jj]);
+               r[jj] = make_double2(fma(gamma, v, U[jj]), vn);
+               vv[jj] = vn;
+               v = vn;
+            }
+            if (sgn)
+            {
+#pragma unroll
+               for (int jj = 0; jj < CPT; ++jj) *reinterpret_cast<double2 *>(th + swz(j0 + jj)) = r[jj];
+            }
+            if (valid != WT) publish_ragged(std::integral_constant<int, 0>{}, vv);
+         }
+         // ================= stage 1: CN corrector, x1 = stage-0 result, upstream X
+         {
+            const double *c = cf + SC_CN, *pw = cf + SC_CN_POW;
+            const double alpha = c[0], gamma = c[1];
+            double w = 0.0, up2 = up_x;
+#pragma unroll
+            for (int jj = 0; jj < CPT; ++jj)
+            {
+               double b;
+               cell_rhs<KIND_CN, CORR>(c, r[jj], r[jj], r[jj].x + r[jj].y, 0.0, up2, !(row_first && jj == 0), b, U[jj]);
+               w = fma(alpha, w, b);
+               wl[jj] = w;
+               if (jj + 1 < CPT) up2 = ldx(j0 + jj).y;
+            }
+            const double cin = scan(std::integral_constant<int, 1>{}, pw[CPT - 1], 2.0, c[9], w);
+            if (!sgn) up_h = cin;
+            double v = cin;
+#pragma unroll
+            for (int jj = 0; jj < CPT; ++jj)
+            {
+               const double vn = fma(pw[jj], cin, wl[jj]);
+               r[jj] = make_double2(fma(gamma, v, U[jj]), vn);
+               vv[jj] = vn;
+               v = vn;
+            }
+            if (!sgn)
+            {
+#pragma unroll
+               for (int jj = 0; jj < CPT; ++jj) *reinterpret_cast<double2 *>(th + swz(j0 + jj)) = r[jj];
+            }
+            if (valid != WT) publish_ragged(std::integral_constant<int, 1>{}, vv);
+         }
+         // ================= stage 2: BE predictor, x1 = stage-1 result; only u+v survives (the BDF stage's source)
+         double xs[CPT];
+         {
+            const double *c = cf + SC_BE, *pw = cf + SC_BE_POW;
+            const double alpha = c[0], gamma = c[1];
+            double w = 0.0;
+#pragma unroll
+            for (int jj = 0; jj < CPT; ++jj)
+            {
+               double b;
+               cell_rhs<KIND_BE, CORR>(c, r[jj], r[jj], r[jj].x + r[jj].y, 0.0, 0.0, false, b, U[jj]);
+               w = fma(alpha, w, b);
+               wl[jj] = w;
+            }
+            const double cin = scan(std::integral_constant<int, 2>{}, pw[CPT - 1], 1.0, c[7], w);
+            double v = cin;
+#pragma unroll
+            for (int jj = 0; jj < CPT; ++jj)
+            {
+               const double vn = fma(pw[jj], cin, wl[jj]);
+               xs[jj] = fma(gamma, v, U[jj]) + vn;
+               vv[jj] = vn;
+               v = vn;
+            }
+            if (valid != WT) publish_ragged(std::integral_constant<int, 2>{}, vv);
+         }
+         // ================= stage 3: BDF corrector, x1 = half_ends (parked in H), x2 = X -> ends^(n+1)
+         {
+            const double *c = cf + SC_BDF, *pw = cf + SC_BDF_POW;
+            const double alpha = c[0], gamma = c[1];
+            double w = 0.0, up1 = up_h, up2 = up_x;
+#pragma unroll
+            for (int jj = 0; jj < CPT; ++jj)
+            {
+               const double2 h = *reinterpret_cast<const double2 *>(th + swz(j0 + jj));
+               const double2 x = ldx(j0 + jj);
+               double b;
+               cell_rhs<KIND_BDF, CORR>(c, h, x, xs[jj], up1, up2, !(row_first && jj == 0), b, U[jj]);
+               w = fma(alpha, w, b);
+               wl[jj] = w;
+               up1 = h.y;
+               up2 = x.y;
+            }
+            const double cin = scan(std::integral_constant<int, 3>{}, pw[CPT - 1], 6.0, c[12], w);
+            double v = cin;
+#pragma unroll
+            for (int jj = 0; jj < CPT; ++jj)
+            {
+               const double vn = fma(pw[jj], cin, wl[jj]);
+               *reinterpret_cast<double2 *>(th + swz(j0 + jj)) = make_double2(fma(gamma, v, U[jj]), vn);
+               vv[jj] = vn;
+               v = vn;
+            }
+            if (valid != WT) publish_ragged(std::integral_constant<int, 3>{}, vv);
+            fence_proxy_async(); // generic-proxy writes -> visible to the TMA store
+            __syncwarp();
+            if (lane == 0)
+            {
+               tma_store_3d(&maps.m[a.iout], 0, sub_start >> 3, ti.row, th); // cells past the row's end are clipped
+               bulk_commit();
+            }
+         }
+      }
+      if (NW > 1 && warp == NW - 1)
+      {
+         __syncwarp();
+         if (lane == 0) st_flag(&s_done, seq + 1);
+      }
+   }
+   if (lane == 0) bulk_wait_read<0>();
+   if (warp == 0 && lane == 0 && q_start < total_tiles) atomicAdd(a.ticket, 1ull); // every CTA makes exactly one draw past the end
+}
+
+template <bool CORR, int CPT, int NW>
+static cudaError_t launch_warp_one(const SweepMaps &maps, const StepArgs &a, int num_sms, cudaStream_t st, int *grid_out)
+{
+   static int ctas_per_sm = -1;
+   auto kern = step_warp_kernel<CORR, CPT, NW>;
+   const size_t smem = (size_t)NW * 3 * 32 * CPT * 16 + 1024; // per warp 2 X + H/OUT, + alignment slack
+   if (ctas_per_sm < 0)
+   {
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return e;
+      int occ = 0;
+      e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32 * NW, smem);
+      if (e != cudaSuccess) return e;
+      ctas_per_sm = occ > 0 ? occ : 1;
+      const char *cap = getenv("RT_CUDA_STEP_CTAS"); // resident CTAs per SM (experiments)
+      if (cap && atoi(cap) >= 1 && atoi(cap) < ctas_per_sm) ctas_per_sm = atoi(cap);
+   }
+   const long long total = (long long)a.n_chains * a.tiles_per_chain;
+   long long grid = (long long)num_sms * ctas_per_sm;
+   if (grid > total) grid = total;
+   if (grid < 1) grid = 1;
+   if (grid_out) *grid_out = (int)grid;
+   kern<<<(unsigned)grid, 32 * NW, smem, st>>>(maps, a);
+   return cudaGetLastError();
+}
+
+bool step_chain_supported(int nw) { return nw == 1 || nw == 2 || nw == 4 || nw == 8; }
+
+cudaError_t launch_step_warp(bool corr, int cpt, int chain_warps, const SweepMaps &maps, const StepArgs &a, int num_sms, cudaStream_t st,
+                             int *grid_out)
+{
+   if (a.ticket_batch < 1 || a.ticket_batch > 8 || !a.coef_step) return cudaErrorInvalidValue;
+#define RT_STEP_CASE(C, P, W) \
+   if (corr == C && cpt == P && chain_warps == W) return launch_warp_one<C, P, W>(maps, a, num_sms, st, grid_out);
+   RT_STEP_CASE(true, 8, 1) RT_STEP_CASE(true, 8, 2) RT_STEP_CASE(true, 8, 4) RT_STEP_CASE(true, 8, 8)
+   RT_STEP_CASE(false, 8, 1) RT_STEP_CASE(false, 8, 2) RT_STEP_CASE(false, 8, 4) RT_STEP_CASE(false, 8, 8)
+   RT_STEP_CASE(true, 4, 1) RT_STEP_CASE(true, 4, 2) RT_STEP_CASE(true, 4, 4) RT_STEP_CASE(true, 4, 8)
+   RT_STEP_CASE(false, 4, 1) RT_STEP_CASE(false, 4, 2) RT_STEP_CASE(false, 4, 4) RT_STEP_CASE(false, 4, 8)
+#undef RT_STEP_CASE
+   return cudaErrorInvalidValue;
+}
+} // namespace rtk
