@@ -12,7 +12,7 @@ import subprocess
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "librt_cuda.so")
+LIB_PATH = os.environ.get("RT_CUDA_LIB") or os.path.join(HERE, "librt_cuda.so")  # RT_CUDA_LIB: A/B builds of the same ABI
 CSRC = os.path.join(HERE, "csrc")
 
 _dp = C.POINTER(C.c_double)

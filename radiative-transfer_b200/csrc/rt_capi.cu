@@ -103,6 +103,7 @@ struct rt_solver
    SweepMaps maps_step;
    int ticket_batch = 8;       // tickets per atomic draw (RT_CUDA_TICKET_BATCH)
    bool l2_prefetch = true;    // RT_CUDA_L2_PREFETCH=0 switches the two-tiles-ahead L2 prefetch off
+   bool step_l2_prefetch = false; // fused step: every warp already has a tile in flight; RT_CUDA_STEP_L2_PREFETCH=1 turns it on
    bool lookback_walk = false; // RT_CUDA_LOOKBACK=walk: aggregate walk-back (faster with very few rows, not bitwise reproducible)
 };
 
@@ -433,6 +434,7 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
    }
    const char *penv = getenv("RT_CUDA_L2_PREFETCH");
    s->l2_prefetch = !(penv && penv[0] == '0');
+   { const char *se = getenv("RT_CUDA_STEP_L2_PREFETCH"); s->step_l2_prefetch = se && se[0] == '1'; }
    const char *lenv = getenv("RT_CUDA_LOOKBACK");
    s->lookback_walk = lenv && std::strcmp(lenv, "walk") == 0;
 
@@ -666,7 +668,7 @@ static int run_fused_step(rt_solver *s)
    a.reflective_left = (p.bc_left == 2) ? 1 : 0;
    a.n_chains = a.reflective_left ? a.rows / 2 : a.rows;
    a.tiles_per_chain = a.reflective_left ? 2 * a.tiles_per_row : a.tiles_per_row;
-   a.l2_prefetch = s->l2_prefetch ? 1 : 0;
+   a.l2_prefetch = s->step_l2_prefetch ? 1 : 0;
    const bool corr = p.use_correction && p.V != 0.0;
    EventPair *ep;
    if (event_begin(s, 4, &ep)) return 1;

@@ -1,0 +1,148 @@
+"""GPU parity of the fused BDF2-step kernels (step_warp_kernel.cu, step_kernel.cu) through the C ABI.
+
+A whole BDF2 step (reference src/solver.cpp:706-809, four stage sweeps) runs as ONE launch by default; RT_CUDA_FUSED=0
+runs the same step stage by stage with the per-stage kernel.  Covered here: fused == staged == oracle, every fused tile
+shape (warp tiles with 1/2/4/8 chained warps, CTA-wide tiles), rows that end inside a warp's sub-tile / at a sub-tile
+boundary / inside the CTA tile, a step that starts in the middle of a solve (partial steps run staged), prev_ends and
+the on-demand re-materialised half_ends after a fused step, chains whose predecessor tile is still in flight."""
+import numpy as np
+import pytest
+
+from parity_util import RTOL, make_oracle, state_err, state_ok, synthetic_parameters
+
+pytestmark = pytest.mark.gpu
+
+
+def _oracle_state(oracle, rt, p, stages, threads=2):
+    o = make_oracle(oracle, rt, p, num_threads=threads)
+    o.run_stages(stages)
+    out = dict(B=o.group_terms()["B"], psi=o.psi(), ends=o.ends(0), prev=o.ends(1), half=o.ends(2))
+    o.close()
+    return out
+
+
+def _check(s, ref, what=("psi", "ends")):
+    worst = 0.0
+    ok = True
+    for name in what:
+        got = s.psi_mat_ref if name == "psi" else s.ends({"ends": 0, "prev": 1, "half": 2}[name])
+        k, w, _ = state_ok(got, ref[name], ref["B"])
+        ok, worst = ok and k, max(worst, w)
+    return ok, worst
+
+
+@pytest.mark.parametrize("bcl", [2, 1])
+def test_fused_equals_staged_equals_oracle(rt, oracle, monkeypatch, bcl):
+    p = synthetic_parameters(rt, M=8, G=5, N=5000, dt=1e-3, V=1.0, steps=3, bc_left=bcl, bc_right=1)
+    ref = _oracle_state(oracle, rt, p, 12)
+    with rt.Solver(p) as s:
+        s.solve()
+        assert s.timing().step_launches == 3  # three whole steps, one launch each
+        ok, worst = _check(s, ref)
+        assert ok, f"fused vs oracle: err/tol {worst:.3e}"
+        fused = (s.psi_mat_ref.copy(order="F"), s.ends(0))
+    monkeypatch.setenv("RT_CUDA_FUSED", "0")
+    with rt.Solver(p) as s:
+        s.solve()
+        assert s.timing().step_launches == 0
+        ok, worst = _check(s, ref)
+        assert ok, f"staged vs oracle: err/tol {worst:.3e}"
+        staged = (s.psi_mat_ref.copy(order="F"), s.ends(0))
+    # the two device paths round differently (seeded scan, table powers) but agree far inside the tolerance
+    assert state_err(fused[0], staged[0]) <= 1e-11 and state_err(fused[1], staged[1]) <= 1e-11
+
+
+@pytest.mark.parametrize("threads,cpt,chain", [(32, 8, 1), (32, 8, 2), (32, 8, 4), (32, 8, 8), (32, 4, 1), (32, 4, 4),
+                                               (64, 8, 1), (64, 4, 1), (128, 8, 1), (128, 4, 1)])
+@pytest.mark.parametrize("bcl", [2, 1])
+def test_step_tile_shapes(rt, oracle, monkeypatch, threads, cpt, chain, bcl):
+    monkeypatch.setenv("RT_CUDA_STEP_THREADS", str(threads))
+    monkeypatch.setenv("RT_CUDA_STEP_CPT", str(cpt))
+    monkeypatch.setenv("RT_CUDA_STEP_CHAIN", str(chain))
+    tile = threads * cpt * chain
+    p = synthetic_parameters(rt, M=8, G=3, N=2 * tile + 37, dt=1e-3, V=1.0, steps=2, bc_left=bcl, bc_right=1)
+    ref = _oracle_state(oracle, rt, p, 8)
+    with rt.Solver(p) as s:
+        s.solve()
+        assert s.timing().step_launches == 2
+        ok, worst = _check(s, ref)
+    assert ok, f"{threads}x{cpt} chain {chain}: err/tol {worst:.3e}"
+
+
+@pytest.mark.parametrize("N", [255, 256, 257, 511, 513, 767, 768, 769, 1023, 1024, 1025, 1279, 2047, 2048, 2049, 3333])
+@pytest.mark.parametrize("bcl", [2, 1])
+def test_rows_ending_inside_the_chained_tile(rt, oracle, N, bcl):
+    """default shape: 4 chained warps x 256 cells.  The row ends in warp 0/1/2/3's sub-tile, exactly at a sub-tile or
+    tile boundary, or one cell past it: the warp holding the last cell publishes the chain's inclusive value, the
+    warps behind it sit the tile out"""
+    p = synthetic_parameters(rt, M=4, G=3, N=N, dt=1e-3, V=1.0, steps=2, bc_left=bcl, bc_right=1)
+    ref = _oracle_state(oracle, rt, p, 8)
+    with rt.Solver(p) as s:
+        s.solve()
+        ok, worst = _check(s, ref)
+    assert ok, f"N={N}: err/tol {worst:.3e}"
+
+
+def test_partial_steps_run_staged_and_rejoin(rt, oracle):
+    """6 stages = one fused step + BE + CN staged; 2 more stages finish the second step staged; then one fused step"""
+    p = synthetic_parameters(rt, M=8, G=4, N=3000, dt=1e-3, V=1.0, steps=3)
+    with rt.Solver(p) as s:
+        s.run_stages(6)
+        assert s.timing().step_launches == 1
+        ok, worst = _check(s, _oracle_state(oracle, rt, p, 6), ("psi", "ends", "prev", "half"))
+        assert ok, f"after 6 stages: err/tol {worst:.3e}"
+        s.run_stages(2)
+        assert s.timing().step_launches == 1
+        s.run_stages(4)
+        assert s.timing().step_launches == 2
+        ok, worst = _check(s, _oracle_state(oracle, rt, p, 12))
+        assert ok, f"after 12 stages: err/tol {worst:.3e}"
+
+
+def test_prev_and_half_ends_after_a_fused_step(rt, oracle):
+    """the fused step keeps prev_ends (it is out of place) and does not store half_ends: rt_get_ends(which=2)
+    re-materialises it (stage 0 for mu>0 rows, stage 1 for mu<0 rows) and the solve carries on unchanged"""
+    p = synthetic_parameters(rt, M=8, G=4, N=3000, dt=1e-3, V=1.0, steps=3)
+    ref = _oracle_state(oracle, rt, p, 8)
+    with rt.Solver(p) as s:
+        s.run_stages(8)
+        ok, worst = _check(s, ref, ("ends", "prev", "half"))
+        assert ok, f"ends/prev/half after 2 fused steps: err/tol {worst:.3e}"
+        s.run_stages(4)
+        ok, worst = _check(s, _oracle_state(oracle, rt, p, 12))
+        assert ok, f"after the re-materialisation: err/tol {worst:.3e}"
+
+
+@pytest.mark.parametrize("chain", [1, 4])
+def test_few_chains_many_tiles(rt, oracle, monkeypatch, chain):
+    """2 rows, hundreds of tiles each: every tile's predecessor is still in flight, the global look-back polls"""
+    monkeypatch.setenv("RT_CUDA_STEP_CHAIN", str(chain))
+    p = synthetic_parameters(rt, M=2, G=1, N=200000, dt=5e-3, V=0.5, steps=2, bc_left=1, bc_right=1)
+    ref = _oracle_state(oracle, rt, p, 8, threads=1)
+    with rt.Solver(p) as s:
+        s.solve()
+        ok, worst = _check(s, ref)
+    assert ok, f"chain {chain}: err/tol {worst:.3e}"
+
+
+def test_fused_bitwise_reproducible(rt):
+    p = synthetic_parameters(rt, M=8, G=4, N=30000, dt=1e-3, V=1.0, steps=3)
+    outs = []
+    for _ in range(3):
+        with rt.Solver(p) as s:
+            s.solve()
+            assert s.timing().step_launches == 3
+            outs.append(s.ends(0))
+    assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
+
+
+def test_staged_path_still_matches_the_oracle(rt, oracle, monkeypatch):
+    """RT_CUDA_FUSED=0: the per-stage kernels keep their own coverage now that whole steps default to the fused one"""
+    monkeypatch.setenv("RT_CUDA_FUSED", "0")
+    for N, bcl in ((513, 2), (4097, 1)):
+        p = synthetic_parameters(rt, M=4, G=3, N=N, dt=1e-3, V=1.0, steps=2, bc_left=bcl, bc_right=1)
+        ref = _oracle_state(oracle, rt, p, 8)
+        with rt.Solver(p) as s:
+            s.solve()
+            ok, worst = _check(s, ref)
+        assert ok, f"staged N={N}: err/tol {worst:.3e}"
