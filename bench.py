@@ -308,12 +308,13 @@ def main():
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                     "traffic": per_unknown * unknowns_per_launch if per_unknown else None,
                     "algorithmic_bytes_per_launch": alg, "avg_launch_ms": avg_ms, "peak_source": peak_src,
-                    "kernel": "rtk::step_kernel<CORR,T,CPT> (BE,CN,BE,BDF fused: one launch per BDF2 step and batch)",
+                    "kernel": "rtk::step_warp_kernel<CORR,CPT,NW> (BE,CN,BE,BDF fused: one launch per BDF2 step and batch)",
                     "algorithmic_bytes_per_unknown_step": STEP_BYTES_PER_UNKNOWN,
-                    "note": "the fused step is fp64-pipe bound, not HBM bound (profiles/: sm__pipe_fp64_cycles_active); run stage by "
-                            "stage the same step needs 176 B per unknown",
+                    "note": "DRAM traffic = the algorithmic 32 B per unknown and step; the kernel is issue/latency bound at 16 warps "
+                            "per SM (profiles/r01_v5_step_ncu_full_wide.txt: issue slots 58 %, fp64 pipe 42 %); run stage by stage "
+                            "the same step moves 176 B per unknown",
                     "staged_equivalent_GBps": sum(BYTES_PER_UNKNOWN[k] * (2 if k == "BE" else 1) for k in kinds) * unknowns_per_launch / (avg_ms * 1e-3) / 1e9,
-                    "fp64_pipe_pct": tr.get("step_fp64_pipe_pct")}
+                    "fp64_pipe_pct": tr.get("step_fp64_pipe_pct"), "issue_active_pct": tr.get("step_issue_active_pct")}
     else:
         alg_bytes = sum(BYTES_PER_UNKNOWN[k] * unknowns_per_launch * tm.sweep_launches[i] for i, k in enumerate(kinds))
         sweep_ms = sum(tm.sweep_ms)
@@ -378,7 +379,8 @@ def main():
                            "l2": "inputs larger than L2 (each launch streams >= 10 GB)" if M * min(plan.groups_per_batch, gn) * N * 32 > 2e8 else "inputs smaller than L2"},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": gpu_launches,
                 "clocks": clk.summary(), "s_per_bdf2_step": ms_max / K * 1e-3,
-                "sweep_grid": plan.sweep_grid, "sweep_block": plan.sweep_block}
+                "sweep_grid": plan.sweep_grid, "sweep_block": plan.sweep_block, "fused_step": bool(plan.fused),
+                "step_tile_cells": plan.step_tile_cells, "step_chain_warps": plan.step_chain}
         emit(line)
     if dist is not None:
         dist.barrier()

@@ -75,8 +75,12 @@ typedef struct rt_timing
 typedef struct rt_plan
 {
    int groups_per_batch, n_batches, resident; /* resident = 1 when one batch holds every owned group */
-   int tile_cells, tiles_per_row, sweep_grid, sweep_block;
+   int tile_cells, tiles_per_row, sweep_grid, sweep_block; /* grid / block of the most recent sweep or step launch */
    size_t bytes_per_group, state_bytes, free_bytes, total_bytes;
+   int fused;            /* 1: whole BDF2 steps run as one fused launch (RT_CUDA_FUSED=0 turns it off)          */
+   int step_tile_cells;  /* cells per ticket of the fused step kernel (sub-tile x chained warps)                 */
+   int step_block;       /* threads per CTA of the fused step kernel                                             */
+   int step_chain;       /* warps chained per CTA tile (1 for the CTA-wide tile shapes)                          */
 } rt_plan;
 
 const char *rt_last_error(void);

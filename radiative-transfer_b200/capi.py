@@ -54,6 +54,7 @@ class RtPlan(C.Structure):
         ("tiles_per_row", C.c_int), ("sweep_grid", C.c_int), ("sweep_block", C.c_int),
         ("bytes_per_group", C.c_size_t), ("state_bytes", C.c_size_t), ("free_bytes", C.c_size_t),
         ("total_bytes", C.c_size_t),
+        ("fused", C.c_int), ("step_tile_cells", C.c_int), ("step_block", C.c_int), ("step_chain", C.c_int),
     ]
 
 

@@ -75,7 +75,7 @@ struct rt_solver
    unsigned long long *d_ticket = nullptr;
    unsigned long long ticket_base = 0;
    unsigned epoch = 0;
-   int last_grid = 0;
+   int last_grid = 0, last_block = 0;
    // tile shape per stage kind {BE, CN, BDF}: CTA size, cells per thread, X1 ring depth (0 = automatic)
    // (measured on C4, gpurun exp8/exp9: 64 x 8 is best or equal for all three kinds)
    int threads[3] = {64, 64, 64}, cpt[3] = {8, 8, 8}, ring[3] = {0, 0, 0};
@@ -523,7 +523,11 @@ extern "C" int rt_get_plan(const rt_solver *s, rt_plan *plan)
    plan->tile_cells = s->tile_cells[KIND_BE];
    plan->tiles_per_row = s->tiles_per_row[KIND_BE];
    plan->sweep_grid = s->last_grid;
-   plan->sweep_block = s->threads[KIND_BE];
+   plan->sweep_block = s->last_block ? s->last_block : s->threads[KIND_BE];
+   plan->fused = (s->fused && s->p.ts_method == 3) ? 1 : 0;
+   plan->step_tile_cells = s->step_tile_cells;
+   plan->step_block = s->step_threads * s->step_chain;
+   plan->step_chain = s->step_chain;
    plan->bytes_per_group = (size_t)4 * s->p.M * s->Np * sizeof(double2);
    plan->state_bytes = 4 * s->buf_elems * sizeof(double2);
    cudaSetDevice(s->p.device);
@@ -573,6 +577,7 @@ static int launch_stage(rt_solver *s, int kind, int i1n, int i1p, int i2, int ic
    const unsigned long long total_tiles = (unsigned long long)a.n_chains * a.tiles_per_chain;
    s->ticket_base += (total_tiles + s->ticket_batch - 1) / s->ticket_batch + (unsigned long long)grid;
    s->last_grid = grid;
+   s->last_block = s->threads[kind];
    s->tm.kernel_launches++;
    if (counted)
    {
@@ -678,6 +683,7 @@ static int run_fused_step(rt_solver *s)
    const unsigned long long total_tiles = (unsigned long long)a.n_chains * a.tiles_per_chain;
    s->ticket_base += (total_tiles + tb - 1) / tb + (unsigned long long)grid;
    s->last_grid = grid;
+   s->last_block = s->step_threads * s->step_chain;
    s->i_prev = in;
    s->i_ends = out;
    s->i_half_neg = s->i_half_pos = -1;

@@ -28,6 +28,11 @@ rows = list(csv.reader(io.StringIO(src)))
 hdr = rows[1]
 data = [x for x in rows[2:] if len(x) == len(hdr)]
 ix = {h: i for i, h in enumerate(hdr)}
+first = data[0][ix["Address"]]  # a report with several launches repeats the listing: keep the first copy
+for i in range(1, len(data)):
+    if data[i][ix["Address"]] == first:
+        data = data[:i]
+        break
 stalls = [h for h in hdr if h.startswith("stall_") and "Not Issued" not in h]
 def n(x, k):
     try:
