@@ -41,17 +41,18 @@ WORKLOADS = {
     "c5": (32, 4096, 1 << 20, 1, 1),
     "small": (16, 32, 1 << 16, 2, 1),
     "mid": (16, 64, 1 << 18, 2, 1),
+    "c5r": (32, 4096, 1 << 14, 1, 1),  # resident variant of c5 (137 GB state on one GPU, no batching)
     "wide": (16, 128, 1 << 17, 2, 1),  # as many rows (2048) as one resident batch of c4, 1/8 of its cells: profiling
 }
 
 
-def synthetic_parameters(rt, M, G, N, bc_left, bc_right, dt, steps, seed=20261104):
+def synthetic_parameters(rt, M, G, N, bc_left, bc_right, dt, steps, seed=20261104, V=1.0):
     """uniform slab dx=0.01, rho=T=1, V=1 (correction live), log groups 0.01..30 keV,
     kappa_g = 10^U(-1,2) from PCG64(seed), equilibrium boundary sources, BDF2."""
     rng = np.random.Generator(np.random.PCG64(seed))
     kap = 10.0 ** rng.uniform(-1.0, 2.0, size=G)
     p = rt.Parameters(M=M, G=G, N=N, X=N * 0.01, efirst=0.01, elast=30.0, bc_left_indicator=bc_left,
-                      bc_right_indicator=bc_right, use_mg_equilib=True, V=1.0, use_correction=True, ts_method=3,
+                      bc_right_indicator=bc_right, use_mg_equilib=True, V=V, use_correction=True, ts_method=3,
                       dt=dt, max_timesteps=steps, include_validation=False, rho=1.0, T=1.0)
     p.have_group_absorption_opacities = True
     p.group_kappa = kap
@@ -238,6 +239,7 @@ def main():
     ap.add_argument("--impl", default="own", choices=["own", "reference"])
     ap.add_argument("--workload", default="auto", choices=["auto"] + sorted(WORKLOADS))
     ap.add_argument("--dt", type=float, default=1e-3, help="1e-3: alpha~0.9 long-range coupling (default); 1e-5: local")
+    ap.add_argument("--V", type=float, default=1.0, help="material speed: 1 = correction source live (default); 0 = the source vanishes")
     ap.add_argument("--groups-per-batch", type=int, default=0)
     ap.add_argument("--cells", type=int, default=0, help="override the number of cells (debug)")
     ap.add_argument("--groups", type=int, default=0, help="override the number of groups (debug)")
@@ -272,7 +274,7 @@ def main():
     sharding = importlib.import_module("radiative-transfer_b200.sharding")
     g0, gn = sharding.group_range(G, world, rank)
     K, W = args.steps, args.warmup
-    p = synthetic_parameters(rt, M, G, N, bcl, bcr, args.dt, K)
+    p = synthetic_parameters(rt, M, G, N, bcl, bcr, args.dt, K, V=args.V)
 
     # ------------------------------------------------------------- device-resident timing (`value`)
     s = rt.Solver(p, device=local_rank, group_begin=g0, group_count=gn, groups_per_batch=args.groups_per_batch, fetch_psi=False)
@@ -298,6 +300,9 @@ def main():
     unknowns_per_launch = M * min(plan.groups_per_batch, gn) * N
     tr_path = os.path.join(ROOT, "profiles", "sweep_traffic.json")
     tr = json.load(open(tr_path)) if os.path.exists(tr_path) else {}
+    bpu = dict(BYTES_PER_UNKNOWN)
+    if args.V == 0.0:
+        bpu["BDF"] = 48  # no correction source: the BDF stage does not read the stage-2 result
     if tm.step_launches > 0:
         # fused BDF2-step kernel: one pass over the state per time step -- reads ends^n (16 B), writes ends^(n+1) (16 B)
         n_launches = int(tm.step_launches)
@@ -313,10 +318,10 @@ def main():
                     "note": "DRAM traffic = the algorithmic 32 B per unknown and step; the kernel is issue/latency bound at 16 warps "
                             "per SM (profiles/r01_v5_step_ncu_full_wide.txt: issue slots 58 %, fp64 pipe 42 %); run stage by stage "
                             "the same step moves 176 B per unknown",
-                    "staged_equivalent_GBps": sum(BYTES_PER_UNKNOWN[k] * (2 if k == "BE" else 1) for k in kinds) * unknowns_per_launch / (avg_ms * 1e-3) / 1e9,
+                    "staged_equivalent_GBps": sum(bpu[k] * (2 if k == "BE" else 1) for k in kinds) * unknowns_per_launch / (avg_ms * 1e-3) / 1e9,
                     "fp64_pipe_pct": tr.get("step_fp64_pipe_pct"), "issue_active_pct": tr.get("step_issue_active_pct")}
     else:
-        alg_bytes = sum(BYTES_PER_UNKNOWN[k] * unknowns_per_launch * tm.sweep_launches[i] for i, k in enumerate(kinds))
+        alg_bytes = sum(bpu[k] * unknowns_per_launch * tm.sweep_launches[i] for i, k in enumerate(kinds))
         sweep_ms = sum(tm.sweep_ms)
         n_launches = int(sum(tm.sweep_launches))
         achieved = alg_bytes / (sweep_ms * 1e-3) / 1e9 if sweep_ms > 0 else None
@@ -325,7 +330,7 @@ def main():
             if tm.sweep_ms[i] > 0:
                 nl = tm.sweep_launches[i]
                 by_kind[k] = {"launches": int(nl), "avg_ms": tm.sweep_ms[i] / nl,
-                              "GBps": BYTES_PER_UNKNOWN[k] * unknowns_per_launch * nl / (tm.sweep_ms[i] * 1e-3) / 1e9}
+                              "GBps": bpu[k] * unknowns_per_launch * nl / (tm.sweep_ms[i] * 1e-3) / 1e9}
         # measured DRAM traffic of the sweep launches (ncu --set full capture, per unknown and stage kind), scaled to the
         # unknowns one launch of THIS run processes and averaged over the launches like `achieved`
         traffic = None
@@ -336,7 +341,7 @@ def main():
                     "traffic": traffic, "algorithmic_bytes_per_launch": (alg_bytes / n_launches) if n_launches else None,
                     "avg_launch_ms": (sweep_ms / n_launches) if n_launches else None, "peak_source": peak_src,
                     "kernel": "rtk::sweep_kernel<KIND,CORR,T,CPT,RING> (BE,CN,BE,BDF per step)",
-                    "algorithmic_bytes_per_unknown": BYTES_PER_UNKNOWN, "by_kind": by_kind}
+                    "algorithmic_bytes_per_unknown": bpu, "by_kind": by_kind}
     gpu_launches = int(tm.kernel_launches)
 
     # ------------------------------------------------------------- end to end through the public API (`e2e`)
@@ -374,7 +379,7 @@ def main():
                 "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "strong" if workload == "c5" else "weak",
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": workload, "M": M, "G": G, "N": N, "dt": args.dt, "ts_method": "BDF2 (BE,CN,BE,BDF)",
-                           "bc": [bcl, bcr], "V": 1.0, "use_correction": True, "parallelism": f"groups sharded x{world}",
+                           "bc": [bcl, bcr], "V": args.V, "use_correction": True, "parallelism": f"groups sharded x{world}",
                            "groups_per_rank": gn, "groups_per_batch": plan.groups_per_batch, "batches": plan.n_batches,
                            "l2": "inputs larger than L2 (each launch streams >= 10 GB)" if M * min(plan.groups_per_batch, gn) * N * 32 > 2e8 else "inputs smaller than L2"},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": gpu_launches,
