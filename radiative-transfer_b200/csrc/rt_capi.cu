@@ -284,7 +284,7 @@ static int compute_group_tables(rt_solver *s)
       launch_coef_table(kind, corr, c, s->d_coef[kind], s->st);
       s->tm.kernel_launches++;
    }
-   launch_pack_step_coef(s->d_coef[0], s->d_coef[1], s->d_coef[2], s->d_coef_step, s->Gl * p.M, s->st);
+   launch_pack_step_coef(s->d_coef[0], s->d_coef[1], s->d_coef[2], s->d_coef_step, s->Gl * p.M, corr, s->st);
    s->tm.kernel_launches++;
    CK(cudaGetLastError());
    return 0;

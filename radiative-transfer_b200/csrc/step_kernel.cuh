@@ -28,7 +28,7 @@ constexpr int STEP_COEF_DOUBLES = 64; // packed BE + CN + BDF constants of one r
 
 // threads = 32: one warp per tile (step_warp_kernel.cu, the default); 64 / 128: CTA-wide tiles (step_kernel.cu)
 bool step_shape_supported(int threads, int cpt);
-void launch_pack_step_coef(const double *be, const double *cn, const double *bdf, double *out, int rows, cudaStream_t st);
+void launch_pack_step_coef(const double *be, const double *cn, const double *bdf, double *out, int rows, bool corr, cudaStream_t st);
 bool step_chain_supported(int chain_warps); // warps (consecutive 32*cpt-cell sub-tiles) per CTA tile: 1, 2, 4 or 8
 cudaError_t launch_step_warp(bool corr, int cpt, int chain_warps, const SweepMaps &maps, const StepArgs &a, int num_sms, cudaStream_t st,
                              int *grid_out);

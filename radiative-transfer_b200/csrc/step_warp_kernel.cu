@@ -29,49 +29,83 @@
 
 namespace rtk
 {
-// packed per-row constants of a BDF2 step: 64 doubles.  *_POW: alpha^1 .. alpha^8 of the kind (pass 2 and the scan
-// factor alpha^CPT come from here: no power chains on the critical path)
+// packed per-row constants of a BDF2 step: 64 doubles.  The per-cell right-hand sides are FOLDED: with
+//   ru = q + c_uu x + c_uv y + p_uu X + p_uv Y + up1c up1 + up2c up2 ,  rv = q - c_uv x + c_uu y - p_uv X + p_uu Y ,
+//   beta = io ru + id rv ,  U = id ru - io rv      (x, y = X1 nodes ; X, Y = X2 nodes ; q = qa + qb (u+v))
+// (the formulas of stage_pass1, sweep_device.cuh) beta and U are linear in the cell's inputs, so their coefficients are
+// formed once per row:
+//   B0 = (io+id) qa, Bq = (io+id) qb, Bx = io c_uu - id c_uv, By = io c_uv + id c_uu, BX = io p_uu - id p_uv,
+//   BY = io p_uv + id p_uu, Bup1 = io up1c, Bup2 = io up2c ;  U likewise with (id, -io) in place of (io, id).
+// In stages 0..2 the source cell IS the X1 cell (u+v = x+y), so Bq / Uq are folded into Bx, By / Ux, Uy as well:
+// a BE cell costs 2 + 2 fused multiply-adds instead of 9 operations.  *_POW: alpha^1 .. alpha^8 of the kind (pass 2,
+// the scan factor alpha^CPT and alpha itself come from here: no power chains on the critical path).
 enum StepCoefIndex
 {
-   SC_BE = 0,      // alpha gamma id io qa qb c_uu inflow0
+   SC_BE = 0,       // gamma inflow0 | B0 Bx By | U0 Ux Uy
    SC_BE_POW = 8,
-   SC_CN = 16,     // alpha gamma id io qa qb c_uu c_uv up2 inflow0
+   SC_CN = 16,      // gamma inflow0 | B0 Bx By Bup2 | U0 Ux Uy Uup2
    SC_CN_POW = 26,
-   SC_BDF = 34,    // alpha gamma id io qa qb c_uu c_uv p_uu p_uv up1 up2 inflow0
-   SC_BDF_POW = 48,
+   SC_BDF = 34,     // gamma inflow0 | B0 Bx By Bq BX BY Bup1 Bup2 | U0 Ux Uy Uq UX UY Uup1 Uup2
+   SC_BDF_POW = 52,
    SC_DOUBLES = STEP_COEF_DOUBLES
 };
-static_assert(SC_BDF + 13 <= SC_BDF_POW && SC_BDF_POW + 8 <= SC_DOUBLES, "packed entry layout");
+static_assert(SC_BDF + 18 <= SC_BDF_POW && SC_BDF_POW + 8 <= SC_DOUBLES, "packed entry layout");
 
 __global__ void pack_step_coef_kernel(const RowCoef *__restrict__ be, const RowCoef *__restrict__ cn,
-                                      const RowCoef *__restrict__ bdf, double *__restrict__ out, int rows)
+                                      const RowCoef *__restrict__ bdf, double *__restrict__ out, int rows, int corr)
 {
    const int r = blockIdx.x * blockDim.x + threadIdx.x;
    if (r >= rows) return;
    double *o = out + (size_t)r * SC_DOUBLES;
-   const RowCoef a = be[r], b = cn[r], c = bdf[r];
    for (int i = 0; i < SC_DOUBLES; ++i) o[i] = 0.0;
-   o[SC_BE + 0] = a.alpha; o[SC_BE + 1] = a.gamma; o[SC_BE + 2] = a.id; o[SC_BE + 3] = a.io;
-   o[SC_BE + 4] = a.qa; o[SC_BE + 5] = a.qb; o[SC_BE + 6] = a.c_uu; o[SC_BE + 7] = a.inflow0;
-   o[SC_CN + 0] = b.alpha; o[SC_CN + 1] = b.gamma; o[SC_CN + 2] = b.id; o[SC_CN + 3] = b.io;
-   o[SC_CN + 4] = b.qa; o[SC_CN + 5] = b.qb; o[SC_CN + 6] = b.c_uu; o[SC_CN + 7] = b.c_uv;
-   o[SC_CN + 8] = b.up2; o[SC_CN + 9] = b.inflow0;
-   o[SC_BDF + 0] = c.alpha; o[SC_BDF + 1] = c.gamma; o[SC_BDF + 2] = c.id; o[SC_BDF + 3] = c.io;
-   o[SC_BDF + 4] = c.qa; o[SC_BDF + 5] = c.qb; o[SC_BDF + 6] = c.c_uu; o[SC_BDF + 7] = c.c_uv;
-   o[SC_BDF + 8] = c.p_uu; o[SC_BDF + 9] = c.p_uv; o[SC_BDF + 10] = c.up1; o[SC_BDF + 11] = c.up2;
-   o[SC_BDF + 12] = c.inflow0;
-   double pa = 1.0, pb = 1.0, pc = 1.0;
-   for (int j = 0; j < 8; ++j)
+   // kind: 0 BE, 1 CN, 2 BDF ; entries that are structurally absent for a kind are forced to zero (cf. fold_coef)
+   for (int kind = 0; kind < 3; ++kind)
    {
-      pa *= a.alpha; pb *= b.alpha; pc *= c.alpha;
-      o[SC_BE_POW + j] = pa; o[SC_CN_POW + j] = pb; o[SC_BDF_POW + j] = pc;
+      const RowCoef c = (kind == 0) ? be[r] : (kind == 1 ? cn[r] : bdf[r]);
+      const double io = c.io, id = c.id, qb = corr ? c.qb : 0.0;
+      const double cuu = c.c_uu, cuv = (kind == 0) ? 0.0 : c.c_uv;
+      const double puu = (kind == 2) ? c.p_uu : 0.0, puv = (kind == 2) ? c.p_uv : 0.0;
+      const double u1 = (kind == 2) ? c.up1 : 0.0, u2 = (kind != 0) ? c.up2 : 0.0;
+      const double sb = io + id, su = id - io;
+      const double B0 = sb * c.qa, Bq = sb * qb, Bx = io * cuu - id * cuv, By = io * cuv + id * cuu;
+      const double U0 = su * c.qa, Uq = su * qb, Ux = id * cuu + io * cuv, Uy = id * cuv - io * cuu;
+      if (kind == 0)
+      {
+         double *k = o + SC_BE;
+         k[0] = c.gamma; k[1] = c.inflow0;
+         k[2] = B0; k[3] = Bx + Bq; k[4] = By + Bq;
+         k[5] = U0; k[6] = Ux + Uq; k[7] = Uy + Uq;
+      }
+      else if (kind == 1)
+      {
+         double *k = o + SC_CN;
+         k[0] = c.gamma; k[1] = c.inflow0;
+         k[2] = B0; k[3] = Bx + Bq; k[4] = By + Bq; k[5] = io * u2;
+         k[6] = U0; k[7] = Ux + Uq; k[8] = Uy + Uq; k[9] = id * u2;
+      }
+      else
+      {
+         double *k = o + SC_BDF;
+         k[0] = c.gamma; k[1] = c.inflow0;
+         k[2] = B0; k[3] = Bx; k[4] = By; k[5] = Bq; k[6] = io * puu - id * puv; k[7] = io * puv + id * puu;
+         k[8] = io * u1; k[9] = io * u2;
+         k[10] = U0; k[11] = Ux; k[12] = Uy; k[13] = Uq; k[14] = id * puu + io * puv; k[15] = id * puv - io * puu;
+         k[16] = id * u1; k[17] = id * u2;
+      }
+      double *pw = o + (kind == 0 ? SC_BE_POW : (kind == 1 ? SC_CN_POW : SC_BDF_POW));
+      double pa = 1.0;
+      for (int j = 0; j < 8; ++j)
+      {
+         pa *= c.alpha;
+         pw[j] = pa;
+      }
    }
 }
 
-void launch_pack_step_coef(const double *be, const double *cn, const double *bdf, double *out, int rows, cudaStream_t st)
+void launch_pack_step_coef(const double *be, const double *cn, const double *bdf, double *out, int rows, bool corr, cudaStream_t st)
 {
    pack_step_coef_kernel<<<(rows + 127) / 128, 128, 0, st>>>(reinterpret_cast<const RowCoef *>(be), reinterpret_cast<const RowCoef *>(cn),
-                                                            reinterpret_cast<const RowCoef *>(bdf), out, rows);
+                                                            reinterpret_cast<const RowCoef *>(bdf), out, rows, corr ? 1 : 0);
 }
 
 // one tile descriptor of the ring: 16 bytes
@@ -82,40 +116,6 @@ struct WarpTile
    int p;     // tile position in the chain
    int tf;    // tile in row * 4 + sgn * 2 + junction
 };
-
-// right-hand sides of one cell -> (beta, U); same formulas as stage_pass1 (sweep_device.cuh)
-template <int KIND, bool CORR>
-__device__ __forceinline__ void cell_rhs(const double *c, const double2 x1, const double2 x2, const double xs, const double up1,
-                                         const double up2, const bool use_up, double &beta, double &U)
-{
-   // c: this kind's slice of the packed entry
-   const double id = c[2], io = c[3];
-   double q = c[4];
-   if (CORR) q = fma(c[5], xs, c[4]);
-   double ru, rv;
-   if (KIND == KIND_BE)
-   {
-      ru = fma(c[6], x1.x, q);
-      rv = fma(c[6], x1.y, q);
-   }
-   else
-   {
-      ru = q + c[6] * x1.x + c[7] * x1.y;
-      rv = q - c[7] * x1.x + c[6] * x1.y;
-   }
-   if (KIND == KIND_BDF)
-   {
-      ru += c[8] * x2.x + c[9] * x2.y;
-      rv += c[8] * x2.y - c[9] * x2.x;
-   }
-   if (KIND != KIND_BE && use_up)
-   {
-      if (KIND == KIND_BDF) ru += c[10] * up1 + c[11] * up2;
-      else ru += c[8] * up2;
-   }
-   beta = io * ru + id * rv;
-   U = id * ru - io * rv;
-}
 
 // {value, sequence} carry words between the warps of a CTA: one 128-bit shared-memory access each way
 __device__ __forceinline__ double2 lds_word(const double2 *p)
@@ -394,18 +394,18 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
          // ================= stage 0: BE predictor, x1 = X (ends^n)
          {
             const double *c = cf + SC_BE, *pw = cf + SC_BE_POW;
-            const double alpha = c[0], gamma = c[1];
+            const double alpha = pw[0], gamma = c[0];
             double w = 0.0;
 #pragma unroll
             for (int jj = 0; jj < CPT; ++jj)
             {
                const double2 x = ldx(j0 + jj);
-               double b;
-               cell_rhs<KIND_BE, CORR>(c, x, x, x.x + x.y, 0.0, 0.0, false, b, U[jj]);
+               const double b = fma(c[4], x.y, fma(c[3], x.x, c[2]));
+               U[jj] = fma(c[7], x.y, fma(c[6], x.x, c[5]));
                w = fma(alpha, w, b);
                wl[jj] = w;
             }
-            const double cin = scan(std::integral_constant<int, 0>{}, pw[CPT - 1], 1.0, c[7], w);
+            const double cin = scan(std::integral_constant<int, 0>{}, pw[CPT - 1], 1.0, c[1], w);
             if (sgn) up_h = cin;
             if (lane == 0) bulk_wait_read<0>(); // the previous tile's TMA store has read H / OUT
             __syncwarp();
@@ -428,18 +428,18 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
          // ================= stage 1: CN corrector, x1 = stage-0 result, upstream X
          {
             const double *c = cf + SC_CN, *pw = cf + SC_CN_POW;
-            const double alpha = c[0], gamma = c[1];
-            double w = 0.0, up2 = up_x;
+            const double alpha = pw[0], gamma = c[0];
+            double w = 0.0, up2 = row_first ? 0.0 : up_x; // a row's first cell has no upstream term (solver.cpp:695-697)
 #pragma unroll
             for (int jj = 0; jj < CPT; ++jj)
             {
-               double b;
-               cell_rhs<KIND_CN, CORR>(c, r[jj], r[jj], r[jj].x + r[jj].y, 0.0, up2, !(row_first && jj == 0), b, U[jj]);
+               const double b = fma(c[5], up2, fma(c[4], r[jj].y, fma(c[3], r[jj].x, c[2])));
+               U[jj] = fma(c[9], up2, fma(c[8], r[jj].y, fma(c[7], r[jj].x, c[6])));
                w = fma(alpha, w, b);
                wl[jj] = w;
                if (jj + 1 < CPT) up2 = ldx(j0 + jj).y;
             }
-            const double cin = scan(std::integral_constant<int, 1>{}, pw[CPT - 1], 2.0, c[9], w);
+            const double cin = scan(std::integral_constant<int, 1>{}, pw[CPT - 1], 2.0, c[1], w);
             if (!sgn) up_h = cin;
             double v = cin;
 #pragma unroll
@@ -461,17 +461,17 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
          double xs[CPT];
          {
             const double *c = cf + SC_BE, *pw = cf + SC_BE_POW;
-            const double alpha = c[0], gamma = c[1];
+            const double alpha = pw[0], gamma = c[0];
             double w = 0.0;
 #pragma unroll
             for (int jj = 0; jj < CPT; ++jj)
             {
-               double b;
-               cell_rhs<KIND_BE, CORR>(c, r[jj], r[jj], r[jj].x + r[jj].y, 0.0, 0.0, false, b, U[jj]);
+               const double b = fma(c[4], r[jj].y, fma(c[3], r[jj].x, c[2]));
+               U[jj] = fma(c[7], r[jj].y, fma(c[6], r[jj].x, c[5]));
                w = fma(alpha, w, b);
                wl[jj] = w;
             }
-            const double cin = scan(std::integral_constant<int, 2>{}, pw[CPT - 1], 1.0, c[7], w);
+            const double cin = scan(std::integral_constant<int, 2>{}, pw[CPT - 1], 1.0, c[1], w);
             double v = cin;
 #pragma unroll
             for (int jj = 0; jj < CPT; ++jj)
@@ -486,21 +486,29 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
          // ================= stage 3: BDF corrector, x1 = half_ends (parked in H), x2 = X -> ends^(n+1)
          {
             const double *c = cf + SC_BDF, *pw = cf + SC_BDF_POW;
-            const double alpha = c[0], gamma = c[1];
-            double w = 0.0, up1 = up_h, up2 = up_x;
+            const double alpha = pw[0], gamma = c[0];
+            double w = 0.0, up1 = row_first ? 0.0 : up_h, up2 = row_first ? 0.0 : up_x;
 #pragma unroll
             for (int jj = 0; jj < CPT; ++jj)
             {
                const double2 h = *reinterpret_cast<const double2 *>(th + swz(j0 + jj));
                const double2 x = ldx(j0 + jj);
-               double b;
-               cell_rhs<KIND_BDF, CORR>(c, h, x, xs[jj], up1, up2, !(row_first && jj == 0), b, U[jj]);
+               double b = fma(c[4], h.y, fma(c[3], h.x, c[2]));
+               double u = fma(c[12], h.y, fma(c[11], h.x, c[10]));
+               if (CORR)
+               {
+                  b = fma(c[5], xs[jj], b);
+                  u = fma(c[13], xs[jj], u);
+               }
+               b = fma(c[9], up2, fma(c[8], up1, fma(c[7], x.y, fma(c[6], x.x, b))));
+               u = fma(c[17], up2, fma(c[16], up1, fma(c[15], x.y, fma(c[14], x.x, u))));
+               U[jj] = u;
                w = fma(alpha, w, b);
                wl[jj] = w;
                up1 = h.y;
                up2 = x.y;
             }
-            const double cin = scan(std::integral_constant<int, 3>{}, pw[CPT - 1], 6.0, c[12], w);
+            const double cin = scan(std::integral_constant<int, 3>{}, pw[CPT - 1], 6.0, c[1], w);
             double v = cin;
 #pragma unroll
             for (int jj = 0; jj < CPT; ++jj)
