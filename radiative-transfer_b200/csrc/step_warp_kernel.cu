@@ -271,6 +271,11 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
       }
       const WarpTile ti = s_desc[seq & 15];
       if (ti.row < 0) break;
+      // warp 0: probe the predecessor tile's four look-back words first of all (lane k holds the word of stage k), so
+      // that the L2 round trip overlaps the issue of the next tile's loads below and pass 1 of stage 0
+      double2 *const status = a.tile_status + 4 * ((size_t)ti.chain * a.tiles_per_chain + ti.p);
+      double2 wpre = make_double2(0.0, 0.0);
+      if (warp == 0 && ti.p > 0 && lane < 4) wpre = ld_status(status - 4 + lane);
       __syncwarp(); // every lane is done with the X slot, constants and halo that are refilled now
       while (issued <= seq + 1 && issued < avail)
       {
@@ -297,12 +302,7 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
          const bool sgn = (ti.tf & 2) != 0, junction = (ti.tf & 1) != 0 && warp == 0;
          const bool is_last = valid_total <= (warp + 1) * WT; // the row's tile ends inside (or at the end of) this sub-tile
          const bool first_sub = (warp == 0);                  // carry from the previous CTA tile / the boundary
-         double2 *const status = a.tile_status + 4 * ((size_t)ti.chain * a.tiles_per_chain + ti.p);
          double2 *const carry_slot = &s_carry[seq & 3][0][0];
-
-         // warp 0: probe the predecessor tile's four look-back words now; lane k holds the word of stage k
-         double2 wpre = make_double2(0.0, 0.0);
-         if (first_sub && ti.p > 0 && lane < 4) wpre = ld_status(status - 4 + lane);
 
          mbar_wait(&s_full[warp][buf], (phase >> buf) & 1u); // sub-tile, constants and halo cell have landed
          phase ^= 1u << buf;
