@@ -316,7 +316,7 @@ def main():
                     "kernel": "rtk::step_warp_kernel<CORR,CPT,NW> (BE,CN,BE,BDF fused: one launch per BDF2 step and batch)",
                     "algorithmic_bytes_per_unknown_step": STEP_BYTES_PER_UNKNOWN,
                     "note": "DRAM traffic = the algorithmic 32 B per unknown and step; the kernel is issue/latency bound at 16 warps "
-                            "per SM (profiles/r01_v5_step_ncu_full_wide.txt: issue slots 58 %, fp64 pipe 42 %); run stage by stage "
+                            "per SM (profiles/r01_v6_step_ncu_full_wide.txt: issue slots 55 %, fp64 pipe 35 %); run stage by stage "
                             "the same step moves 176 B per unknown",
                     "staged_equivalent_GBps": sum(bpu[k] * (2 if k == "BE" else 1) for k in kinds) * unknowns_per_launch / (avg_ms * 1e-3) / 1e9,
                     "fp64_pipe_pct": tr.get("step_fp64_pipe_pct"), "issue_active_pct": tr.get("step_issue_active_pct")}

@@ -184,6 +184,55 @@ class Solver:
         dump("right_ends.csv", col(self.right_ends))
 
     # ------------------------------------------------------------------ extras used by tests / bench
+    # ---- per-step snapshot stream: parity "at each step" inspectable without re-running ---------
+    SNAPSHOT_MAGIC = b"RTSNAP01"
+
+    def solve_with_snapshots(self, path: str, every: int = 1, with_ends: bool = False) -> int:
+        """Run the remaining time steps like solve() and append one record per `every` time steps to the binary file
+        `path`: header {magic, M, G, N, group_begin, group_count, stages per step, with_ends} (int64 each after the
+        8-byte magic), then per record {time step, stages done} (int64) + phi, phi_plus, F as [group][cell] float64
+        (+ ends in the reference's (i, g, cell, node) order when with_ends).  Needs every owned group resident
+        (a batched solve runs its batches one after the other through all time steps).  Returns the record count."""
+        if not self.resident:
+            raise capi.RtError("solve_with_snapshots: the solve is group-batched; snapshots need a resident state")
+        per_step = 4 if self.ph.ts_method == 3 else 1
+        n = 0
+        with open(path, "wb") as f:
+            f.write(self.SNAPSHOT_MAGIC)
+            np.array([self.M, self.num_groups, self.N, self.group_begin, self.group_count, per_step, int(with_ends)],
+                     dtype=np.int64).tofile(f)
+            while self.stages_done < self.total_stages:
+                todo = min(every * per_step, self.total_stages - self.stages_done)
+                capi.check(capi.lib().rt_run_stages(self._h, int(todo)))
+                phi, pp, F = self.moments_group_major()
+                np.array([self.stages_done // per_step, self.stages_done], dtype=np.int64).tofile(f)
+                for a in (phi, pp, F):
+                    np.ascontiguousarray(a).tofile(f)
+                if with_ends:
+                    np.asfortranarray(self.ends(0)).ravel(order="F").tofile(f)
+                n += 1
+        if self._fetch_psi:
+            self._pull_psi()
+        return n
+
+    @classmethod
+    def read_snapshots(cls, path: str):
+        """Generator over the records of a snapshot stream: dicts with step, stages, phi, phi_plus, F (+ ends)."""
+        with open(path, "rb") as f:
+            if f.read(8) != cls.SNAPSHOT_MAGIC:
+                raise ValueError(f"{path}: not a snapshot stream")
+            M, G, N, g0, gc, per_step, with_ends = (int(v) for v in np.fromfile(f, dtype=np.int64, count=7))
+            while True:
+                head = np.fromfile(f, dtype=np.int64, count=2)
+                if head.size < 2:
+                    return
+                rec = {"step": int(head[0]), "stages": int(head[1]), "group_begin": g0}
+                for k in ("phi", "phi_plus", "F"):
+                    rec[k] = np.fromfile(f, dtype=np.float64, count=gc * N).reshape(gc, N)
+                if with_ends:
+                    rec["ends"] = np.fromfile(f, dtype=np.float64, count=M * gc * N * 2).reshape((M, gc, N, 2), order="F")
+                yield rec
+
     def _pull_psi(self):
         capi.check(capi.lib().rt_get_psi(self._h, capi.ptr(self.psi_mat_ref)))
 

@@ -146,3 +146,26 @@ def test_staged_path_still_matches_the_oracle(rt, oracle, monkeypatch):
             s.solve()
             ok, worst = _check(s, ref)
         assert ok, f"staged N={N}: err/tol {worst:.3e}"
+
+
+def test_snapshot_stream_matches_golden_steps(rt, tmp_path):
+    """the per-step snapshot stream (binary) reproduces the reference's state at intermediate time
+    steps (golden vectors from reference runs with max_timesteps = k) and re-reads to what the solver reports"""
+    from conftest import GOLDEN_CASES
+    from parity_util import load_case, load_golden
+    name = "multi_group_equilibrium" if "multi_group_equilibrium" in GOLDEN_CASES else GOLDEN_CASES[0]
+    p = load_case(rt, name)
+    g = load_golden(name)
+    ks = sorted(int(k[len("ends_steps"):]) for k in g if k.startswith("ends_steps"))
+    assert ks
+    path = str(tmp_path / "snap.bin")
+    with rt.Solver(p) as s:
+        n = s.solve_with_snapshots(path, every=1, with_ends=True)
+        assert n == p.max_timesteps and s.stages_done == s.total_stages
+        final_phi = s.moments_group_major()[0]
+    recs = {r["step"]: r for r in rt.Solver.read_snapshots(path)}
+    assert sorted(recs) == list(range(1, p.max_timesteps + 1))
+    for k in ks:
+        ok, worst, _ = state_ok(recs[k]["ends"], g[f"ends_steps{k}"], g["B"])
+        assert ok, f"{name}@step{k}: err/tol {worst:.3e}"
+    assert np.array_equal(recs[p.max_timesteps]["phi"], final_phi)
