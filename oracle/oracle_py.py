@@ -35,6 +35,7 @@ class _Params(C.Structure):
         ("dx", C.c_double), ("dt", C.c_double), ("rho", C.c_double), ("T", C.c_double),
         ("V", C.c_double), ("kappa_grey", C.c_double),
         ("mu", _dp), ("wt", _dp), ("e_edge", _dp), ("kappa", _dp), ("psi_source", _dp),
+        ("rho_cell", _dp), ("T_cell", _dp), ("kappa_cell", _dp),
     ]
 
 
@@ -146,7 +147,10 @@ class Oracle:
     arrays indexed [i, g, c(, s)] (Fortran order views)."""
 
     def __init__(self, *, M, N, G, ts_method, max_timesteps, bc_left, bc_right, use_correction, use_mg_equilib,
-                 dx, dt, rho, T, V, kappa_grey, mu, wt, e_edge, kappa, psi_source=None, num_threads=1):
+                 dx, dt, rho, T, V, kappa_grey, mu, wt, e_edge, kappa, psi_source=None, num_threads=1,
+                 rho_cell=None, T_cell=None, kappa_cell=None):
+        """rho_cell[N], T_cell[N], kappa_cell[G, N]: the cell-dependent material extension; all None =
+        the reference's uniform slab"""
         self.M, self.N, self.G = M, N, G
         self._keep = [np.ascontiguousarray(a, dtype=np.float64) for a in (mu, wt, e_edge, kappa)]
         ps = None
@@ -157,6 +161,11 @@ class Oracle:
                       int(bool(use_mg_equilib)), num_threads, dx, dt, rho, T, V, kappa_grey,
                       _p(self._keep[0]), _p(self._keep[1]), _p(self._keep[2]), _p(self._keep[3]),
                       ps.ctypes.data_as(_dp) if ps is not None else None)
+        for name, a, shape in (("rho_cell", rho_cell, (N,)), ("T_cell", T_cell, (N,)), ("kappa_cell", kappa_cell, (G, N))):
+            if a is not None:
+                a = np.asfortranarray(np.asarray(a, dtype=np.float64).reshape(shape))
+                self._keep.append(a)
+                setattr(prm, name, a.ctypes.data_as(_dp))
         self._h = lib().rto_create(C.byref(prm))
 
     def close(self):
@@ -235,7 +244,9 @@ def oracle_from_parameters(p, mu, wt, e_edge, kappa, num_threads=1) -> Oracle:
                   bc_left=p.bc_left_indicator, bc_right=p.bc_right_indicator, use_correction=p.use_correction,
                   use_mg_equilib=p.use_mg_equilib, dx=p.dx, dt=p.dt, rho=p.rho, T=p.T, V=p.V,
                   kappa_grey=p.kappa_grey, mu=mu, wt=wt, e_edge=e_edge, kappa=kappa,
-                  psi_source=p.psi_source if need_src else None, num_threads=num_threads)
+                  psi_source=p.psi_source if need_src else None, num_threads=num_threads,
+                  rho_cell=getattr(p, "rho_cell", None), T_cell=getattr(p, "T_cell", None),
+                  kappa_cell=getattr(p, "kappa_cell", None))
 
 
 # ---------------------------------------------------------------- oracle-1 (the reference itself)

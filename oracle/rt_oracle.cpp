@@ -35,8 +35,33 @@ struct rto_solver
    rto::GroupTerms gt;
    rto::Sweep sw;
    int stages_done;
-   rto_solver() : gauss(rto::PLANCK_ACCURACY), stages_done(0) {}
+   bool var;            // EXTENSION: cell-dependent material fields
+   rto::CellTables ct;
+   rto_solver() : gauss(rto::PLANCK_ACCURACY), stages_done(0), var(false) {}
 };
+
+// per-cell group terms (extension): the reference's G-length Correction pipeline evaluated with the cell's rho, T, kappa
+static void rto_cell_tables(rto_solver *s)
+{
+   const int N = s->p.N, G = s->p.G;
+   rto::CellTables &ct = s->ct;
+   const size_t n = (size_t)G * N;
+   ct.B.assign(n, 0.0); ct.dEB.assign(n, 0.0); ct.cor1.assign(n, 0.0); ct.cor2.assign(n, 0.0); ct.cor3.assign(n, 0.0);
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static) num_threads(s->p.num_threads > 0 ? s->p.num_threads : 1)
+#endif
+   for (int c = 0; c < N; c++)
+   {
+      rto::GroupTerms g;
+      g.setup(G, s->gt.e_edge.data(), &ct.kappa[(size_t)G * c], ct.rho[c]);
+      g.per_stage(s->gauss, ct.T[c]);
+      for (int k = 0; k < G; k++)
+      {
+         const size_t o = (size_t)k + (size_t)G * c;
+         ct.B[o] = g.B[k]; ct.dEB[o] = g.dEB[k]; ct.cor1[o] = g.cor1[k]; ct.cor2[o] = g.cor2[k]; ct.cor3[o] = g.cor3[k];
+      }
+   }
+}
 
 extern "C" {
 
@@ -144,6 +169,18 @@ rto_solver *rto_create(const rto_params *p)
    sw.psi_source.assign((size_t)M * G, 0.0);
    if (p->psi_source) std::copy(p->psi_source, p->psi_source + (size_t)M * G, sw.psi_source.begin());
    s->p.psi_source = sw.psi_source.data();
+   s->var = p->rho_cell || p->T_cell || p->kappa_cell;
+   if (s->var)
+   {
+      rto::CellTables &ct = s->ct;
+      ct.rho.assign(N, p->rho); ct.T.assign(N, p->T); ct.kappa.assign((size_t)G * N, 0.0);
+      if (p->rho_cell) std::copy(p->rho_cell, p->rho_cell + N, ct.rho.begin());
+      if (p->T_cell) std::copy(p->T_cell, p->T_cell + N, ct.T.begin());
+      for (int c = 0; c < N; c++)
+         for (int g = 0; g < G; g++) ct.kappa[(size_t)g + (size_t)G * c] = p->kappa_cell ? p->kappa_cell[(size_t)g + (size_t)G * c] : p->kappa[g];
+      s->p.rho_cell = ct.rho.data(); s->p.T_cell = ct.T.data(); s->p.kappa_cell = ct.kappa.data();
+      rto_cell_tables(s);
+   }
    // Correction ctor computes the Planck integrals once (correction.cpp:318-319); the solver then
    // initialises psi = ends(L) = ends(R) = B_g (solver.cpp:166-181).
    rto::planck_groups(s->gauss, p->T, G, s->gt.e_edge.data(), s->gt.B.data(), s->gt.dBdT.data());
@@ -151,7 +188,7 @@ rto_solver *rto_create(const rto_params *p)
       for (int g = 0; g < G; g++)
          for (int i = 0; i < M; i++)
          {
-            double v = s->gt.B[g];
+            double v = s->var ? s->ct.B[(size_t)g + (size_t)G * c] : s->gt.B[g];
             sw.psi[sw.ip(i, g, c)] = v;
             sw.ends[sw.ie(i, g, c, 0)] = v;
             sw.ends[sw.ie(i, g, c, 1)] = v;
@@ -181,10 +218,17 @@ void rto_run_stages(rto_solver *s, int n)
          for (int i = 0; i < M; i++)
             for (int g = 0; g < G; g++)
             {
-               double val = 4 * gt.B[g] - gt.dEB[g];
+               double Bg = gt.B[g], dEBg = gt.dEB[g];
+               if (s->var)
+               {
+                  // extension: the boundary cell's material state (cell 0 feeds mu > 0, cell N-1 feeds mu < 0)
+                  const size_t o = (size_t)g + (size_t)G * (s->mu[i] < 0. ? p.N - 1 : 0);
+                  Bg = s->ct.B[o]; dEBg = s->ct.dEB[o];
+               }
+               double val = 4 * Bg - dEBg;
                double mult = s->mu[i] * p.V / rto::C_LIGHT;
                val *= mult;
-               val += gt.B[g];
+               val += Bg;
                sw.psi_source[i + (size_t)M * g] = val;
             }
       }
@@ -207,7 +251,7 @@ void rto_run_stages(rto_solver *s, int n)
 #endif
       for (int g = 0; g < G; g++)
          sw.sweep_group(g, kind, tau, snapshot, s->mu.data(), p.bc_left, p.bc_right, gt.rho[g], gt.kappa[g], gt.B[g],
-                        p.use_correction != 0, gt.cor1[g], gt.cor2[g], gt.cor3[g], beta);
+                        p.use_correction != 0, gt.cor1[g], gt.cor2[g], gt.cor3[g], beta, s->var ? &s->ct : nullptr);
       s->stages_done++;
    }
 }
@@ -265,8 +309,10 @@ void rto_balance(const rto_solver *s, double *balance)
       }
       for (int c = 0; c < N; c++)
       {
-         a += s->gt.rho[g] * s->gt.kappa[g] * phi[g + (size_t)G * c] * sw.dx;
-         src += s->gt.rho[g] * s->gt.kappa[g] * ac * std::pow(s->p.T, 4) * sw.dx;
+         double rho = s->gt.rho[g], kap = s->gt.kappa[g], T = s->p.T;
+         if (s->var) { rho = s->ct.rho[c]; kap = s->ct.kappa[(size_t)g + (size_t)G * c]; T = s->ct.T[c]; }
+         a += rho * kap * phi[g + (size_t)G * c] * sw.dx;
+         src += rho * kap * ac * std::pow(T, 4) * sw.dx;
       }
       double sources = j_half_plus + jN_half_minus + src;
       double sinks = jN_half_plus + j_half_minus + a;

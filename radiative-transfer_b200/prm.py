@@ -104,6 +104,11 @@ class Parameters:
     max_timesteps: int = 1000
     include_validation: bool = True
     source_file: str = field(default="", compare=False)
+    # EXTENSION (the reference's slab is uniform, solver.cpp:150-157 TODO): material fields per cell.
+    # All None = the reference's uniform slab; any given switches the solve to the cell-dependent kernels.
+    rho_cell: Optional[np.ndarray] = field(default=None, compare=False)    # N
+    T_cell: Optional[np.ndarray] = field(default=None, compare=False)      # N
+    kappa_cell: Optional[np.ndarray] = field(default=None, compare=False)  # (G, N)
 
     @property
     def dx(self) -> float:
