@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 1
+#define RT_ABI_VERSION 2
 
 typedef struct rt_params
 {
@@ -55,6 +55,16 @@ typedef struct rt_params
    const double *e_edge;     /* G+1  group edges (solver.cpp:96-100)                      */
    const double *kappa;      /* G    group opacities (solver.cpp:145-152)                 */
    const double *psi_source; /* M*G  boundary sources or NULL (=0) (solver.cpp:67-73)     */
+   /* EXTENSION (ABI version 2).  The reference's slab is uniform: rho, T, kappa_g are filled with
+    * constants and the spatial variation is a TODO (solver.cpp:150-157, correction.h:91).  All three NULL = that uniform
+    * slab, the pinned path.  Any non-NULL switches the solve to the cell-dependent kernels (csrc/var_kernel.cu; missing
+    * fields are filled with the scalars above): per-stage launches only, all owned groups resident, validate must be 0.
+    * Equilibrium boundary sources use the state of the boundary cell (cell 0 for mu > 0, cell N-1 for mu < 0).
+    * Parity: checked against the oracle's cell-dependent restatement, which is bit-identical to the reference-pinned
+    * uniform oracle for uniform arrays; beyond uniform inputs there is no reference to compare with. */
+   const double *rho_cell;   /* N    or NULL */
+   const double *T_cell;     /* N    or NULL */
+   const double *kappa_cell; /* G*N at g + G*c, or NULL */
 } rt_params;
 
 typedef struct rt_solver rt_solver;

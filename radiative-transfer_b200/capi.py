@@ -36,6 +36,7 @@ class RtParams(C.Structure):
         ("dx", C.c_double), ("dt", C.c_double), ("rho", C.c_double), ("T", C.c_double), ("V", C.c_double),
         ("kappa_grey", C.c_double),
         ("mu", _dp), ("wt", _dp), ("e_edge", _dp), ("kappa", _dp), ("psi_source", _dp),
+        ("rho_cell", _dp), ("T_cell", _dp), ("kappa_cell", _dp),  # extension (ABI 2): cell-dependent material fields
     ]
 
 

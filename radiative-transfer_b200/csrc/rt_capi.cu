@@ -17,6 +17,7 @@
 #include "moments.cuh"
 #include "rt_common.cuh"
 #include "step_kernel.cuh"
+#include "var_kernel.cuh"
 #include "sweep_kernel.cuh"
 
 using namespace rtk;
@@ -62,6 +63,12 @@ struct rt_solver
    double *d_coef[3] = {nullptr, nullptr, nullptr}; // per stage kind: Gl*M entries of COEF_ENTRY_DOUBLES doubles
    double *d_coef_step = nullptr;                   // the three kinds packed per row (STEP_COEF_DOUBLES each)
    double sums[3] = {0, 0, 0};
+   // cell-dependent material fields (extension, var_kernel.cu): inputs, Planck per cell, per-cell tables [gl][c]
+   bool var = false;
+   std::vector<double> rho_cell, T_cell, kappa_cell;
+   double *d_rho_c = nullptr, *d_T_c = nullptr, *d_kappa_c = nullptr, *d_B_c = nullptr, *d_dBdT_c = nullptr;
+   double *d_vt[5] = {nullptr, nullptr, nullptr, nullptr, nullptr}; // sigma, srcB, cor1, cor2, cor3
+   double *d_edge_state[4] = {nullptr, nullptr, nullptr, nullptr};  // B_left, dEB_left, B_right, dEB_right (G each)
    // batching
    int Gl = 0, Gb = 0, n_batches = 0, Np = 0;
    size_t buf_elems = 0; // double2 elements per time-level buffer
@@ -287,6 +294,23 @@ static int compute_group_tables(rt_solver *s)
    launch_pack_step_coef(s->d_coef[0], s->d_coef[1], s->d_coef[2], s->d_coef_step, s->Gl * p.M, corr, s->st);
    s->tm.kernel_launches++;
    CK(cudaGetLastError());
+   if (s->var)
+   {
+      // extension: Planck integrals per (cell, group), the Correction pipeline per cell, boundary sources from the
+      // boundary cells (these overwrite the uniform boundary table built above)
+      s->tm.kernel_launches += launch_planck(p.G, p.N, s->d_e_edge, s->d_T_c, s->d_B_c, s->d_dBdT_c, s->st);
+      CellTermsArgs ca;
+      ca.G = p.G; ca.N = p.N; ca.G0 = p.group_begin; ca.groups = s->Gl;
+      ca.e_edge = s->d_e_edge; ca.kappa_cell = s->d_kappa_c; ca.rho_cell = s->d_rho_c; ca.T_cell = s->d_T_c; ca.B_cell = s->d_B_c;
+      ca.sigma = s->d_vt[0]; ca.srcB = s->d_vt[1]; ca.cor1 = s->d_vt[2]; ca.cor2 = s->d_vt[3]; ca.cor3 = s->d_vt[4];
+      ca.B_left = s->d_edge_state[0]; ca.dEB_left = s->d_edge_state[1]; ca.B_right = s->d_edge_state[2]; ca.dEB_right = s->d_edge_state[3];
+      launch_cell_terms(ca, s->st);
+      if (upload(s, s->d_psi_source, s->psi_source.data(), (size_t)p.M * p.G)) return 1; // the caller's sources, before the BC switch
+      launch_boundary_table_var(p.M, p.G, p.bc_left, p.bc_right, p.use_mg_equilib, p.V, s->d_mu, s->d_edge_state[0], s->d_edge_state[1],
+                                s->d_edge_state[2], s->d_edge_state[3], s->d_psi_source, s->d_bdry, s->st);
+      s->tm.kernel_launches += 2;
+      CK(cudaGetLastError());
+   }
    return 0;
 }
 
@@ -308,7 +332,8 @@ static int load_batch(rt_solver *s, int start)
    s->i_prev = s->i_half_neg = s->i_half_pos = -1;
    s->half_stale = false;
    s->stages_done = 0;
-   launch_init_state(s->E[0], s->d_B, s->p.M, s->p.N, s->Np, s->p.group_begin + start, s->batch_groups, s->st);
+   if (s->var) launch_init_state_var(s->E[0], s->d_B_c, s->p.M, s->p.N, s->Np, s->p.G, s->p.group_begin + start, s->batch_groups, s->st);
+   else launch_init_state(s->E[0], s->d_B, s->p.M, s->p.N, s->Np, s->p.group_begin + start, s->batch_groups, s->st);
    s->tm.kernel_launches += 1;
    CK(cudaGetLastError());
    return 0;
@@ -325,6 +350,9 @@ extern "C" int rt_destroy(rt_solver *s)
                      s->d_balance, s->d_left, s->d_right, s->d_stage, s->d_step_phi[0], s->d_step_phi[1],
                      s->d_coef[0], s->d_coef[1], s->d_coef[2], s->d_coef_step};
    for (double *t : tabs) if (t) cudaFree(t);
+   double *vtabs[] = {s->d_rho_c, s->d_T_c, s->d_kappa_c, s->d_B_c, s->d_dBdT_c, s->d_vt[0], s->d_vt[1], s->d_vt[2], s->d_vt[3],
+                      s->d_vt[4], s->d_edge_state[0], s->d_edge_state[1], s->d_edge_state[2], s->d_edge_state[3]};
+   for (double *t : vtabs) if (t) cudaFree(t);
    for (int k = 0; k < 4; ++k) if (s->E[k]) cudaFreeAsync(s->E[k], s->st);
    if (s->st) cudaStreamSynchronize(s->st);
    if (!pool_keep())
@@ -357,6 +385,8 @@ static int validate_params(const rt_params *p)
    for (int i = 0; i < p->M; ++i)
       if (p->mu[i] == 0.0 || (i < p->M / 2) != (p->mu[i] < 0.0)) return fail("mu should not be 0 and must be ascending with M/2 negative nodes");
    if (p->max_timesteps < 0) return fail("rt_create: max_timesteps < 0");
+   if ((p->rho_cell || p->T_cell || p->kappa_cell) && p->validate)
+      return fail("rt_create: the validation sums (correction.cpp:39-63) are defined for the uniform slab only; set validate = 0 with cell-dependent fields");
    return 0;
 }
 
@@ -386,6 +416,19 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
    if (p->psi_source) std::copy(p->psi_source, p->psi_source + (size_t)M * G, s->psi_source.begin());
    s->p.mu = s->mu.data(); s->p.wt = s->wt.data(); s->p.e_edge = s->e_edge.data(); s->p.kappa = s->kappa.data();
    s->p.psi_source = s->psi_source.data();
+   s->var = p->rho_cell || p->T_cell || p->kappa_cell;
+   if (s->var)
+   {
+      s->rho_cell.assign(N, p->rho);
+      s->T_cell.assign(N, p->T);
+      s->kappa_cell.resize((size_t)G * N);
+      if (p->rho_cell) std::copy(p->rho_cell, p->rho_cell + N, s->rho_cell.begin());
+      if (p->T_cell) std::copy(p->T_cell, p->T_cell + N, s->T_cell.begin());
+      for (int c = 0; c < N; ++c)
+         for (int g = 0; g < G; ++g)
+            s->kappa_cell[(size_t)g + (size_t)G * c] = p->kappa_cell ? p->kappa_cell[(size_t)g + (size_t)G * c] : p->kappa[g];
+      s->p.rho_cell = s->rho_cell.data(); s->p.T_cell = s->T_cell.data(); s->p.kappa_cell = s->kappa_cell.data();
+   }
    s->num_sms = prop.multiProcessorCount;
    s->Gl = p->group_count;
    s->Np = (N + 7) & ~7;
@@ -423,7 +466,7 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       s->step_tiles_per_row = (N + s->step_tile_cells - 1) / s->step_tile_cells;
       s->max_tiles_per_row = std::max(s->max_tiles_per_row, 4 * s->step_tiles_per_row); // 4 look-back words per tile
       const char *fe = getenv("RT_CUDA_FUSED");
-      s->fused = !(fe && fe[0] == '0');
+      s->fused = !(fe && fe[0] == '0') && !s->var; // the cell-dependent kernels are per-stage only
    }
    const char *tenv = getenv("RT_CUDA_TIMING");
    s->timing_on = !(tenv && tenv[0] == '0');
@@ -463,6 +506,17 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       gauss12_host(pt, w);
       upload_gauss_rule(pt, w);
    }
+   if (s->var)
+   {
+      CKD(dalloc(&s->d_rho_c, N)); CKD(dalloc(&s->d_T_c, N)); CKD(dalloc(&s->d_kappa_c, (size_t)G * N));
+      CKD(dalloc(&s->d_B_c, (size_t)G * N)); CKD(dalloc(&s->d_dBdT_c, (size_t)G * N));
+      for (int k = 0; k < 5; ++k) CKD(dalloc(&s->d_vt[k], (size_t)s->Gl * N));
+      for (int k = 0; k < 4; ++k) CKD(dalloc(&s->d_edge_state[k], G));
+      CKC(cudaMemsetAsync(s->d_B_c, 0, (size_t)G * N * sizeof(double), s->st));
+      CKC(cudaMemsetAsync(s->d_dBdT_c, 0, (size_t)G * N * sizeof(double), s->st));
+      CKD(upload(s, s->d_rho_c, s->rho_cell.data(), N)); CKD(upload(s, s->d_T_c, s->T_cell.data(), N));
+      CKD(upload(s, s->d_kappa_c, s->kappa_cell.data(), (size_t)G * N));
+   }
 
    // ---- memory plan: 4 time-level buffers of (u,v) per unknown + look-back state
    size_t free_b = 0, total_b = 0;
@@ -489,6 +543,12 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       gb = (s->Gl + nb - 1) / nb;
    }
    gb = std::min(gb, s->Gl);
+   if (s->var && gb < s->Gl)
+   {
+      fail("rt_create: cell-dependent fields need all %d owned groups resident (only %d fit / were asked for)", s->Gl, gb);
+      rt_destroy(s);
+      return 1;
+   }
    s->Gb = gb;
    s->n_batches = (s->Gl + gb - 1) / gb;
    s->buf_elems = (size_t)gb * M * s->Np;
@@ -572,6 +632,28 @@ static int launch_stage(rt_solver *s, int kind, int i1n, int i1p, int i2, int ic
    EventPair *ep = nullptr;
    if (counted && event_begin(s, kind, &ep)) return 1;
    int grid = 0;
+   if (s->var)
+   {
+      // cell-dependent material fields (extension): one CTA per chain, no tickets, no look-back state
+      VarSweepArgs v;
+      v.x1[0] = s->E[i1n]; v.x1[1] = s->E[i1p]; v.x2 = a.x2; v.xc = a.xc; v.out = s->E[out];
+      v.t.sigma = s->d_vt[0]; v.t.srcB = s->d_vt[1]; v.t.cor1 = s->d_vt[2]; v.t.cor2 = s->d_vt[3]; v.t.cor3 = s->d_vt[4];
+      v.mu = s->d_mu; v.bdry = s->d_bdry;
+      v.M = p.M; v.N = p.N; v.Np = s->Np; v.G0 = p.group_begin; v.rows = a.rows; v.reflective_left = a.reflective_left;
+      v.dx = p.dx; v.tau = (p.ts_method == 3) ? p.dt / 2. : p.dt; v.dt = p.dt; v.beta = p.V / C_LIGHT;
+      CK(launch_var_sweep(kind, corr, v, s->st, &grid));
+      if (counted && event_end(s, ep)) return 1;
+      s->last_grid = grid;
+      s->last_block = 128;
+      s->tm.kernel_launches++;
+      if (counted)
+      {
+         s->tm.sweep_launches[kind]++;
+         s->tm.stages++;
+         s->tm.unknown_stages += (long long)a.rows * p.N;
+      }
+      return 0;
+   }
    CK(launch_sweep(kind, corr, s->threads[kind], s->cpt[kind], s->ring[kind], s->maps[kind], a, s->num_sms, s->st, &grid));
    if (counted && event_end(s, ep)) return 1;
    const unsigned long long total_tiles = (unsigned long long)a.n_chains * a.tiles_per_chain;
@@ -810,9 +892,14 @@ static int finish_batch(rt_solver *s)
    if (event_begin(s, 3, &ep)) return 1;
    launch_moments(s->E[s->i_ends], s->d_mu, s->d_wt, p.M, p.N, s->Np, s->batch_groups, s->d_phi + off, s->d_phip + off,
                   s->d_F + off, s->st);
-   launch_diagnostics(s->E[s->i_ends], s->d_phi + off, s->d_mu, s->d_wt, s->d_sigma, s->d_de_ave, p.M, p.N, s->Np,
-                      p.group_begin + s->batch_start, s->batch_groups, p.dx, p.T, s->d_balance + s->batch_start,
-                      s->d_left + s->batch_start, s->d_right + s->batch_start, s->st);
+   if (s->var)
+      launch_diagnostics_var(s->E[s->i_ends], s->d_phi + off, s->d_mu, s->d_wt, s->d_vt[0], s->d_T_c, s->d_de_ave, p.M, p.N, s->Np,
+                             p.group_begin + s->batch_start, s->batch_groups, p.dx, s->d_balance + s->batch_start,
+                             s->d_left + s->batch_start, s->d_right + s->batch_start, s->st);
+   else
+      launch_diagnostics(s->E[s->i_ends], s->d_phi + off, s->d_mu, s->d_wt, s->d_sigma, s->d_de_ave, p.M, p.N, s->Np,
+                         p.group_begin + s->batch_start, s->batch_groups, p.dx, p.T, s->d_balance + s->batch_start,
+                         s->d_left + s->batch_start, s->d_right + s->batch_start, s->st);
    if (event_end(s, ep)) return 1;
    s->tm.kernel_launches += 2;
    CK(cudaGetLastError());

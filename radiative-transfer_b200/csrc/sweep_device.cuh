@@ -100,6 +100,69 @@ struct RowCoef
 static_assert(sizeof(RowCoef) == COEF_ENTRY_DOUBLES * sizeof(double), "coefficient table entry size");
 static_assert(sizeof(RowCoef) % 16 == 0, "entries are staged with 16-byte cp.async copies");
 
+// The stepper constants of one (stage kind, direction, material state): sigma = rho*kappa_g, srcB = sigma*B_g, cor1..3 the
+// correction terms of the group.  Used once per row by coef_table_kernel (the reference's uniform slab) and once per
+// CELL by the cell-dependent kernels (var_kernel.cu).  inflow0 is left to the caller.
+__device__ __forceinline__ RowCoef coef_from_material(int kind, bool corr, double mu, double sig, double srcB, double cor1,
+                                                      double cor2, double cor3, double dx, double tau, double dt, double beta)
+{
+   RowCoef c;
+   const double amu = fabs(mu);
+   const double ctau = C_LIGHT * tau;
+   const double hq = 0.5 * ctau * dx; // 0.5*c*timestep*dx (solver.cpp:337)
+   c.qa = hq * srcB;
+   c.qb = 0.0;
+   if (corr)
+   {
+      // total_correction = (cor1*psi + cor2)*mu*beta - cor3*mu^2*beta^2 (correction.cpp:392-394), psi = (u+v)/2
+      const double mb = mu * beta;
+      c.qa += hq * (cor2 * mb - cor3 * mb * mb);
+      c.qb = 0.5 * hq * cor1 * mb;
+   }
+   double k, d;
+   c.p_uu = c.p_uv = c.p_vu = c.p_vv = 0.0;
+   c.up1 = c.up2 = 0.0;
+   if (kind == KIND_BE)
+   {
+      // solver.cpp:324-334,344-345,381-382
+      k = ctau * amu;
+      d = 0.5 * ((1.0 + ctau * sig) * dx + k);
+      c.c_uu = 0.5 * dx; c.c_uv = 0.0; c.c_vu = 0.0; c.c_vv = 0.5 * dx;
+      c.kbc = 1.0;
+   }
+   else if (kind == KIND_CN)
+   {
+      // solver.cpp:411-425,435-436,469-470
+      const double t = 0.5 * ctau * sig;
+      k = 0.5 * C_LIGHT * amu * tau;
+      d = 0.5 * ((1.0 + t) * dx + k);
+      const double e1 = 0.5 * ((1.0 - t) * dx - k);
+      c.c_uu = e1; c.c_uv = -0.5 * k; c.c_vu = 0.5 * k; c.c_vv = e1;
+      c.up2 = k; // a * in_prev, in_prev = prev_ends(j-1).v
+      c.kbc = 2.0;
+   }
+   else
+   {
+      // solver.cpp:498-512,522-527,561-566 ; streaming constant uses the FULL dt
+      const double t = C_LIGHT * sig * tau / 6.0;
+      k = C_LIGHT * amu * dt / 6.0;
+      d = 0.5 * ((1.0 + t) * dx + k);
+      const double f1 = 0.5 * ((1.0 - 4.0 * t) * dx - 4.0 * k), g1 = 0.5 * (k + t * dx);
+      c.c_uu = f1; c.c_uv = -2.0 * k; c.c_vu = 2.0 * k; c.c_vv = f1;
+      c.p_uu = -g1; c.p_uv = -0.5 * k; c.p_vu = 0.5 * k; c.p_vv = -g1;
+      c.up1 = 4.0 * k; // b * 4 * in_half, in_half = half_ends(j-1).v
+      c.up2 = k;       // b * in_prev
+      c.kbc = 6.0;
+   }
+   const double o = 0.5 * k, det = d * d + o * o;
+   c.id = d / det;
+   c.io = o / det;
+   c.alpha = c.io * k;
+   c.gamma = c.id * k;
+   c.inflow0 = 0.0;
+   return c;
+}
+
 // ---- tile status word: {value, flag} in ONE aligned 16-byte word, written and read with single 128-bit
 // accesses (the same single-copy-atomicity CUB's decoupled look-back relies on for 16-byte descriptors), so no
 // fence is needed between value and flag.

@@ -54,59 +54,8 @@ namespace rtk
 {
 __device__ __forceinline__ RowCoef make_coef(int kind, bool corr, const CoefArgs &a, int g, int i)
 {
-   RowCoef c;
-   const double mu = a.mu[i], amu = fabs(mu), sig = a.sigma[g];
-   const double ctau = C_LIGHT * a.tau;
-   const double hq = 0.5 * ctau * a.dx; // 0.5*c*timestep*dx (solver.cpp:337)
-   c.qa = hq * a.srcB[g];
-   c.qb = 0.0;
-   if (corr)
-   {
-      // total_correction = (cor1*psi + cor2)*mu*beta - cor3*mu^2*beta^2 (correction.cpp:392-394), psi = (u+v)/2
-      const double mb = mu * a.beta;
-      c.qa += hq * (a.cor2[g] * mb - a.cor3[g] * mb * mb);
-      c.qb = 0.5 * hq * a.cor1[g] * mb;
-   }
-   double k, d;
-   c.p_uu = c.p_uv = c.p_vu = c.p_vv = 0.0;
-   c.up1 = c.up2 = 0.0;
-   if (kind == KIND_BE)
-   {
-      // solver.cpp:324-334,344-345,381-382
-      k = ctau * amu;
-      d = 0.5 * ((1.0 + ctau * sig) * a.dx + k);
-      c.c_uu = 0.5 * a.dx; c.c_uv = 0.0; c.c_vu = 0.0; c.c_vv = 0.5 * a.dx;
-      c.kbc = 1.0;
-   }
-   else if (kind == KIND_CN)
-   {
-      // solver.cpp:411-425,435-436,469-470
-      const double t = 0.5 * ctau * sig;
-      k = 0.5 * C_LIGHT * amu * a.tau;
-      d = 0.5 * ((1.0 + t) * a.dx + k);
-      const double e1 = 0.5 * ((1.0 - t) * a.dx - k);
-      c.c_uu = e1; c.c_uv = -0.5 * k; c.c_vu = 0.5 * k; c.c_vv = e1;
-      c.up2 = k; // a * in_prev, in_prev = prev_ends(j-1).v
-      c.kbc = 2.0;
-   }
-   else
-   {
-      // solver.cpp:498-512,522-527,561-566 ; streaming constant uses the FULL dt
-      const double t = C_LIGHT * sig * a.tau / 6.0;
-      k = C_LIGHT * amu * a.dt / 6.0;
-      d = 0.5 * ((1.0 + t) * a.dx + k);
-      const double f1 = 0.5 * ((1.0 - 4.0 * t) * a.dx - 4.0 * k), g1 = 0.5 * (k + t * a.dx);
-      c.c_uu = f1; c.c_uv = -2.0 * k; c.c_vu = 2.0 * k; c.c_vv = f1;
-      c.p_uu = -g1; c.p_uv = -0.5 * k; c.p_vu = 0.5 * k; c.p_vv = -g1;
-      c.up1 = 4.0 * k; // b * 4 * in_half, in_half = half_ends(j-1).v
-      c.up2 = k;       // b * in_prev
-      c.kbc = 6.0;
-   }
-   const double o = 0.5 * k, det = d * d + o * o;
-   c.id = d / det;
-   c.io = o / det;
-   c.alpha = c.io * k;
-   c.gamma = c.id * k;
+   RowCoef c = coef_from_material(kind, corr, a.mu[i], a.sigma[g], a.srcB[g], corr ? a.cor1[g] : 0.0, corr ? a.cor2[g] : 0.0,
+                                  corr ? a.cor3[g] : 0.0, a.dx, a.tau, a.dt, a.beta);
    c.inflow0 = c.kbc * a.bdry[(size_t)i + (size_t)a.M * g];
    return c;
 }

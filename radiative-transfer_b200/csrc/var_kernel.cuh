@@ -1,0 +1,58 @@
+// var_kernel.cuh -- cell-dependent material fields rho(c), T(c), kappa_g(c): EXTENSION.
+//
+// The reference's slab is uniform -- rho, T and kappa_g are filled with constants, the spatial variation is a TODO at
+// solver.cpp:150-157 and correction.h:91 -- so this path has no reference to compare with beyond uniform inputs
+// (where it must, and does, reproduce the uniform path).  Its oracle is the cell-dependent restatement in
+// oracle/rt_oracle.cpp, which is bit-identical to the reference-pinned uniform oracle for uniform arrays.
+#pragma once
+#include "rt_common.cuh"
+
+namespace rtk
+{
+// Per-cell tables of the owned groups, row layout [gl][c] (c contiguous): what the steppers need of the material state.
+struct CellTables
+{
+   const double *sigma, *srcB, *cor1, *cor2, *cor3; // rho*kappa_g, rho*kappa_g*B_g, correction terms (correction.cpp:328-340)
+};
+
+struct CellTermsArgs
+{
+   int G, N, G0, groups;     // all groups enter the edge stencils; tables are written for the owned ones [G0, G0+groups)
+   const double *e_edge;     // G+1
+   const double *kappa_cell; // g + G*c
+   const double *rho_cell;   // N
+   const double *T_cell;     // N
+   const double *B_cell;     // g + G*c, jk units (planck kernels with ncell = N)
+   double *sigma, *srcB, *cor1, *cor2, *cor3; // [gl][c]
+   double *B_left, *dEB_left, *B_right, *dEB_right; // G each: material state of cell 0 / cell N-1 (boundary sources)
+};
+void launch_cell_terms(const CellTermsArgs &a, cudaStream_t st);
+
+// bdry(i,g) and, with use_mg_equilib, psi_source(i,g) from the boundary cells' state (mu>0: cell 0, mu<0: cell N-1)
+void launch_boundary_table_var(int M, int G, int bc_left, int bc_right, int use_mg_equilib, double V, const double *mu,
+                               const double *B_left, const double *dEB_left, const double *B_right, const double *dEB_right,
+                               double *psi_source, double *bdry, cudaStream_t st);
+
+// psi = ends(L) = ends(R) = B_g(T(c)) (solver.cpp:166-181 with the cell's temperature)
+void launch_init_state_var(double2 *buf, const double *B_cell, int M, int N, int Np, int G, int G0, int groups, cudaStream_t st);
+
+struct VarSweepArgs
+{
+   const double2 *x1[2]; // X1 for mu<0 / mu>0 rows
+   const double2 *x2;    // CN, BDF
+   const double2 *xc;    // BDF with the correction: source cell values
+   double2 *out;
+   CellTables t;
+   const double *mu;   // M
+   const double *bdry; // i + M*g (global group)
+   int M, N, Np, G0, rows, reflective_left;
+   double dx, tau, dt, beta;
+};
+// one CTA per chain, tiles in sequence (no look-back): BE / CN / BDF stage with cell-dependent stepper constants
+cudaError_t launch_var_sweep(int kind, bool corr, const VarSweepArgs &a, cudaStream_t st, int *grid_out);
+
+// balance (solver.cpp:240-284) with per-cell sigma and T, group-end spectra (826-850)
+void launch_diagnostics_var(const double2 *ends, const double *phi, const double *mu, const double *wt, const double *sigma_cell,
+                            const double *T_cell, const double *de_ave, int M, int N, int Np, int G0, int groups, double dx,
+                            double *balance, double *left_ends, double *right_ends, cudaStream_t st);
+} // namespace rtk

@@ -79,6 +79,14 @@ class Solver:
         p.mu, p.wt = capi.ptr(self.m_mu), capi.ptr(self.m_wt)
         p.e_edge, p.kappa = capi.ptr(self.e_edge), capi.ptr(self.kappa_vec)
         p.psi_source = capi.ptr(src) if src is not None else None
+        # extension: cell-dependent material fields; all None = the reference's uniform slab
+        self._cell_fields = []
+        for name, shape in (("rho_cell", (ph.N,)), ("T_cell", (ph.N,)), ("kappa_cell", (ph.G, ph.N))):
+            a = getattr(ph, name, None)
+            if a is not None:
+                a = np.asfortranarray(np.asarray(a, dtype=np.float64).reshape(shape))  # kappa(g, c) at g + G*c
+                self._cell_fields.append(a)
+                setattr(p, name, capi.ptr(a))
         self._h = C.c_void_p()
         capi.check(capi.lib().rt_create(C.byref(p), C.byref(self._h)))
         self.resident = self.plan().resident == 1

@@ -1,0 +1,106 @@
+"""GPU parity of the cell-dependent material extension (csrc/var_kernel.cu) through the C ABI.
+
+The reference's slab is uniform (solver.cpp:150-157 TODO), so: (1) with UNIFORM per-cell arrays the cell-dependent
+kernels must agree with the uniform kernels and with the reference-pinned oracle; (2) with varying fields they are
+checked against the oracle's cell-dependent restatement (tests/test_oracle_cell_fields.py pins that one to the uniform
+oracle bit for bit for uniform arrays) at the same 1e-9 tolerance, every time-stepping method and boundary condition."""
+import numpy as np
+import pytest
+
+from parity_util import make_oracle, state_err, state_ok, synthetic_parameters
+
+pytestmark = pytest.mark.gpu
+
+
+def _fields(p, seed=11, T_amp=0.3, rho_amp=0.5, kap_dec=1.0):
+    rng = np.random.Generator(np.random.PCG64(seed))
+    x = (np.arange(p.N) + 0.5) / p.N
+    p.T_cell = 1.0 + T_amp * np.sin(2 * np.pi * x) ** 2 + (0.2 if T_amp else 0.0) * (x > 0.6)
+    p.rho_cell = 1.0 + rho_amp * np.cos(3 * np.pi * x)
+    p.kappa_cell = np.asarray(p.group_kappa)[:, None] * 10.0 ** rng.uniform(-kap_dec, kap_dec, size=(p.G, p.N))
+    return p
+
+
+def _compare(rt, oracle, p, stages, threads=4):
+    o = make_oracle(oracle, rt, p, num_threads=threads)
+    o.run_stages(stages)
+    B = np.maximum(o.group_terms()["B"], 1e-300)
+    ref = dict(psi=o.psi(), ends=o.ends(0), prev=o.ends(1), half=o.ends(2), phi=o.moments()[0], bal=o.balance(),
+               ge=o.group_ends(), src=o.psi_source())
+    o.close()
+    with rt.Solver(p) as s:
+        s.run_stages(stages)
+        assert s.timing().step_launches == 0  # per-stage launches only
+        worst = 0.0
+        for got, want in ((s.psi_mat_ref, ref["psi"]), (s.ends(0), ref["ends"]), (s.ends(1), ref["prev"]), (s.ends(2), ref["half"])):
+            ok, w, _ = state_ok(got, want, B)
+            assert ok, f"err/tol {w:.3e}"
+            worst = max(worst, w)
+        ok, w, _ = state_ok(s.moments()[0], ref["phi"], B, group_axis=0)
+        assert ok, f"phi err/tol {w:.3e}"
+        s.compute_balance()
+        s.compute_group_ends()
+        assert np.allclose(s.psi_source(), ref["src"], rtol=1e-12, atol=0)
+        scale = np.abs(ref["phi"]).max()
+        assert np.all(np.abs(s.get_ends("left") - ref["ge"][0]) <= 1e-9 * np.abs(ref["ge"][0]).max())
+        assert np.all(np.abs(s.get_ends("right") - ref["ge"][1]) <= 1e-9 * np.abs(ref["ge"][1]).max())
+        assert np.all(np.abs(s.get_balance() - ref["bal"]) <= 1e-6 * np.maximum(1.0, np.abs(ref["bal"])))
+        assert np.isfinite(scale)
+    return worst
+
+
+@pytest.mark.parametrize("bcl,bcr", [(2, 1), (1, 1), (0, 0)])
+def test_uniform_arrays_match_the_uniform_kernels_and_the_oracle(rt, oracle, bcl, bcr):
+    p = synthetic_parameters(rt, M=8, G=5, N=3000, dt=1e-3, V=1.0, steps=2, bc_left=bcl, bc_right=bcr)
+    with rt.Solver(p) as s:
+        s.solve()
+        uni = (s.psi_mat_ref.copy(order="F"), s.ends(0))
+    p.rho_cell = np.full(p.N, p.rho)
+    p.T_cell = np.full(p.N, p.T)
+    p.kappa_cell = np.repeat(np.asarray(p.group_kappa)[:, None], p.N, axis=1)
+    _compare(rt, oracle, p, 8)
+    with rt.Solver(p) as s:
+        s.solve()
+        assert state_err(s.psi_mat_ref, uni[0]) <= 1e-11 and state_err(s.ends(0), uni[1]) <= 1e-11
+
+
+@pytest.mark.parametrize("ts,bcl,bcr", [(3, 2, 1), (3, 1, 1), (3, 0, 0), (1, 1, 1), (2, 2, 1)])
+def test_varying_fields_vs_oracle(rt, oracle, ts, bcl, bcr):
+    p = synthetic_parameters(rt, M=8, G=6, N=2500, dt=1e-3, V=1.0, steps=2, bc_left=bcl, bc_right=bcr, ts_method=ts)
+    _fields(p)
+    _compare(rt, oracle, p, 2 * (4 if ts == 3 else 1))
+
+
+@pytest.mark.parametrize("N", [1, 3, 4, 5, 511, 512, 513, 1025])
+def test_varying_fields_ragged_rows(rt, oracle, N):
+    p = synthetic_parameters(rt, M=4, G=3, N=N, dt=1e-3, V=1.0, steps=2, bc_left=2, bc_right=1)
+    _fields(p)
+    _compare(rt, oracle, p, 8, threads=2)
+
+
+def test_no_correction_and_static_medium(rt, oracle):
+    for V, corr in ((0.0, True), (1.0, False)):
+        p = synthetic_parameters(rt, M=4, G=4, N=1500, dt=1e-4, V=V, steps=2, bc_left=1, bc_right=1, use_correction=corr)
+        _fields(p)
+        _compare(rt, oracle, p, 8, threads=2)
+
+
+def test_only_temperature_given_and_group_shards(rt, oracle):
+    """missing fields are filled with the scalars; a shard of the groups equals the same rows of the whole solve"""
+    p = synthetic_parameters(rt, M=4, G=6, N=900, dt=1e-3, V=1.0, steps=1, bc_left=2, bc_right=1)
+    p.T_cell = 1.0 + 0.4 * (np.arange(p.N) > 300)
+    _compare(rt, oracle, p, 4, threads=2)
+    with rt.Solver(p) as s:
+        s.solve()
+        whole = s.ends(0)
+    with rt.Solver(p, group_begin=2, group_count=3) as s:
+        s.solve()
+        assert np.array_equal(s.ends(0), whole[:, 2:5])
+
+
+def test_validation_is_refused_with_cell_fields(rt):
+    p = synthetic_parameters(rt, M=4, G=3, N=100, dt=1e-3, V=1.0, steps=1)
+    p.include_validation = True
+    p.T_cell = np.full(p.N, 1.0)
+    with pytest.raises(rt.capi.RtError):
+        rt.Solver(p)
