@@ -240,6 +240,8 @@ def main():
     ap.add_argument("--workload", default="auto", choices=["auto"] + sorted(WORKLOADS))
     ap.add_argument("--dt", type=float, default=1e-3, help="1e-3: alpha~0.9 long-range coupling (default); 1e-5: local")
     ap.add_argument("--V", type=float, default=1.0, help="material speed: 1 = correction source live (default); 0 = the source vanishes")
+    ap.add_argument("--cell-fields", action="store_true",
+                    help="extension (SURVEY 8(f).2): smooth synthetic rho(c), T(c), kappa_g(c); per-stage cell-dependent kernels")
     ap.add_argument("--groups-per-batch", type=int, default=0)
     ap.add_argument("--cells", type=int, default=0, help="override the number of cells (debug)")
     ap.add_argument("--groups", type=int, default=0, help="override the number of groups (debug)")
@@ -275,6 +277,11 @@ def main():
     g0, gn = sharding.group_range(G, world, rank)
     K, W = args.steps, args.warmup
     p = synthetic_parameters(rt, M, G, N, bcl, bcr, args.dt, K, V=args.V)
+    if args.cell_fields:
+        x = (np.arange(N) + 0.5) / N
+        p.T_cell = 1.0 + 0.3 * np.sin(2 * np.pi * x) ** 2
+        p.rho_cell = 1.0 + 0.5 * np.cos(3 * np.pi * x)
+        p.kappa_cell = np.asarray(p.group_kappa)[:, None] * (1.0 + 0.5 * np.sin(7 * np.pi * x))[None, :]
 
     # ------------------------------------------------------------- device-resident timing (`value`)
     s = rt.Solver(p, device=local_rank, group_begin=g0, group_count=gn, groups_per_batch=args.groups_per_batch, fetch_psi=False)
@@ -303,6 +310,10 @@ def main():
     bpu = dict(BYTES_PER_UNKNOWN)
     if args.V == 0.0:
         bpu["BDF"] = 48  # no correction source: the BDF stage does not read the stage-2 result
+    if args.cell_fields:
+        # + the per-(group, cell) tables every row of the group reads: sigma, srcB (+ cor1..3 with the correction) / M rows
+        extra = (40.0 if args.V != 0.0 else 16.0) / M
+        bpu = {k: v + extra for k, v in bpu.items()}
     if tm.step_launches > 0:
         # fused BDF2-step kernel: one pass over the state per time step -- reads ends^n (16 B), writes ends^(n+1) (16 B)
         n_launches = int(tm.step_launches)
@@ -335,12 +346,13 @@ def main():
         # unknowns one launch of THIS run processes and averaged over the launches like `achieved`
         traffic = None
         per_unknown = tr.get("dram_bytes_per_unknown") or {}
-        if n_launches and all(k in per_unknown for k in kinds):
+        if n_launches and all(k in per_unknown for k in kinds) and not args.cell_fields:
             traffic = sum(per_unknown[k] * tm.sweep_launches[i] for i, k in enumerate(kinds)) * unknowns_per_launch / n_launches
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
                     "traffic": traffic, "algorithmic_bytes_per_launch": (alg_bytes / n_launches) if n_launches else None,
                     "avg_launch_ms": (sweep_ms / n_launches) if n_launches else None, "peak_source": peak_src,
-                    "kernel": "rtk::sweep_kernel<KIND,CORR,T,CPT,RING> (BE,CN,BE,BDF per step)",
+                    "kernel": ("rtk::var_sweep_kernel<KIND,CORR> (cell-dependent material fields; BE,CN,BE,BDF per step)" if args.cell_fields
+                               else "rtk::sweep_kernel<KIND,CORR,T,CPT,RING> (BE,CN,BE,BDF per step)"),
                     "algorithmic_bytes_per_unknown": bpu, "by_kind": by_kind}
     gpu_launches = int(tm.kernel_launches)
 
@@ -379,7 +391,7 @@ def main():
                 "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "strong" if workload == "c5" else "weak",
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": workload, "M": M, "G": G, "N": N, "dt": args.dt, "ts_method": "BDF2 (BE,CN,BE,BDF)",
-                           "bc": [bcl, bcr], "V": args.V, "use_correction": True, "parallelism": f"groups sharded x{world}",
+                           "bc": [bcl, bcr], "V": args.V, "cell_fields": bool(args.cell_fields), "use_correction": True, "parallelism": f"groups sharded x{world}",
                            "groups_per_rank": gn, "groups_per_batch": plan.groups_per_batch, "batches": plan.n_batches,
                            "l2": "inputs larger than L2 (each launch streams >= 10 GB)" if M * min(plan.groups_per_batch, gn) * N * 32 > 2e8 else "inputs smaller than L2"},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": gpu_launches,
