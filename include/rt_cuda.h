@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 2
+#define RT_ABI_VERSION 3
 
 typedef struct rt_params
 {
@@ -65,6 +65,18 @@ typedef struct rt_params
    const double *rho_cell;   /* N    or NULL */
    const double *T_cell;     /* N    or NULL */
    const double *kappa_cell; /* G*N at g + G*c, or NULL */
+   /* EXTENSION (ABI version 3): material-temperature update.  PARITY UNPINNED -- the reference has no
+    * temperature update at all (its T is a scalar that never changes); the definition is the oracle's
+    * restatement (oracle/rt_oracle.cpp, rto_temperature_update), against which the device path is checked at 1e-9.
+    * cv > 0 (specific heat) switches it on, and with it the cell-dependent kernels.  After every time step (BDF2: 4 stage
+    * sweeps), per cell c with W = sum_m w_m:
+    *    A = sum_g sigma_g(c) phi_g(c)     E = W sum_g sigma_g(c) B_g(T(c))     D = W sum_g sigma_g(c) dB_g/dT(T(c))
+    *    first step or ts_method != 3:  T' = T + dt (A - E) / (rho cv + dt D)                       (backward Euler, linearised)
+    *    later BDF2 steps:              T' = [rho cv (2T - T_prev/2) + dt (A - E + D T)] / (3/2 rho cv + dt D)
+    * then the per-cell Planck integrals and correction terms are re-evaluated at T'.  The three group sums are the ONE
+    * place where energy groups couple: a handle that owns a group shard forms partial sums and hands the 3*N device
+    * buffer to the all-reduce hook (rt_set_allreduce) before the update -- NCCL over NVLink in the multi-GPU runs. */
+   double cv;
 } rt_params;
 
 typedef struct rt_solver rt_solver;
@@ -80,6 +92,9 @@ typedef struct rt_timing
    long long h2d_bytes, d2h_bytes;
    double step_ms;            /* device time spent in fused BDF2-step launches (4 stage sweeps each)  */
    long long step_launches;
+   /* material-temperature update (extension): moments + group sums + all-reduce hook + T update ; Planck + per-cell tables */
+   double tupdate_ms, tables_ms;
+   long long tupdate_count;
 } rt_timing;
 
 typedef struct rt_plan
@@ -130,6 +145,17 @@ int rt_get_psi_source(rt_solver *s, double *psi_source);   /* M*G */
 /* Correction::validate_correction (correction.cpp:39-63,100-122): sums3 = {sum B, sum dBdT, sum kappa*B};
  * *ok = 1 when all three identities hold to 1e-6 */
 int rt_validate(rt_solver *s, double *sums3, int *ok);
+
+/* Material-temperature update (extension, rt_params::cv).  rt_get_temperature: the current T(c), N doubles; sums3 (may be
+ * NULL) receives the group sums A, E, D of the most recent update, 3*N doubles, AFTER the all-reduce.
+ * rt_set_allreduce: `fn(buf, count, stream, user)` must sum the `count` fp64 values at DEVICE pointer `buf` element-wise
+ * over all handles that share the problem (in place, result on every rank) and order that work after what `stream`
+ * (a cudaStream_t) holds and before what is submitted to it next; non-zero return aborts the solve.  NULL = the handle
+ * owns every group.  The library itself does not link NCCL: the Python host passes torch.distributed's all_reduce, a
+ * C++ host its ncclAllReduce. */
+typedef int (*rt_allreduce_fn)(void *device_buf, size_t count, void *cuda_stream, void *user);
+int rt_set_allreduce(rt_solver *s, rt_allreduce_fn fn, void *user);
+int rt_get_temperature(rt_solver *s, double *T, double *sums3);
 
 /* After every completed time step (BDF2: 4 stage sweeps) copy phi (Gl*N, group-major g*N + c when
  * group_major != 0, reference order otherwise) into `phi_host`; NULL switches it off.  Used by the

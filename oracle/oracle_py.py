@@ -36,6 +36,7 @@ class _Params(C.Structure):
         ("V", C.c_double), ("kappa_grey", C.c_double),
         ("mu", _dp), ("wt", _dp), ("e_edge", _dp), ("kappa", _dp), ("psi_source", _dp),
         ("rho_cell", _dp), ("T_cell", _dp), ("kappa_cell", _dp),
+        ("cv", C.c_double),
     ]
 
 
@@ -67,6 +68,7 @@ def lib():
         L.rto_get_group_terms.argtypes = [C.c_void_p] + [_dp] * 6
         L.rto_get_psi_source.argtypes = [C.c_void_p, _dp]
         L.rto_validate.argtypes = [C.c_void_p, _dp]
+        L.rto_get_temperature.argtypes = [C.c_void_p, _dp, _dp, _dp, _dp]
         L.rto_glquad.argtypes = [C.c_int, C.c_double, _dp, _dp]
         L.rto_group_edges.argtypes = [C.c_int, C.c_double, C.c_double, _dp]
         L.rto_planck.argtypes = [C.c_double, C.c_int, _dp, _dp, _dp]
@@ -148,9 +150,10 @@ class Oracle:
 
     def __init__(self, *, M, N, G, ts_method, max_timesteps, bc_left, bc_right, use_correction, use_mg_equilib,
                  dx, dt, rho, T, V, kappa_grey, mu, wt, e_edge, kappa, psi_source=None, num_threads=1,
-                 rho_cell=None, T_cell=None, kappa_cell=None):
+                 rho_cell=None, T_cell=None, kappa_cell=None, cv=0.0):
         """rho_cell[N], T_cell[N], kappa_cell[G, N]: the cell-dependent material extension; all None =
-        the reference's uniform slab"""
+        the reference's uniform slab.  cv > 0: material-temperature update after every time step (parity
+        unpinned -- the reference has none)"""
         self.M, self.N, self.G = M, N, G
         self._keep = [np.ascontiguousarray(a, dtype=np.float64) for a in (mu, wt, e_edge, kappa)]
         ps = None
@@ -166,6 +169,7 @@ class Oracle:
                 a = np.asfortranarray(np.asarray(a, dtype=np.float64).reshape(shape))
                 self._keep.append(a)
                 setattr(prm, name, a.ctypes.data_as(_dp))
+        prm.cv = float(cv)
         self._h = lib().rto_create(C.byref(prm))
 
     def close(self):
@@ -202,6 +206,12 @@ class Oracle:
         a = np.zeros((self.M, self.G, self.N, 2), order="F")
         lib().rto_get_ends(self._h, which, _p(a))
         return a
+
+    def temperature(self, with_sums=False):
+        """T(c); with_sums also returns the group sums A, E, D of the last temperature update"""
+        T, A, E, D = (np.zeros(self.N) for _ in range(4))
+        lib().rto_get_temperature(self._h, _p(T), _p(A), _p(E), _p(D))
+        return (T, A, E, D) if with_sums else T
 
     def moments(self):
         phi, pp, F = (np.zeros((self.G, self.N), order="F") for _ in range(3))
@@ -246,7 +256,7 @@ def oracle_from_parameters(p, mu, wt, e_edge, kappa, num_threads=1) -> Oracle:
                   kappa_grey=p.kappa_grey, mu=mu, wt=wt, e_edge=e_edge, kappa=kappa,
                   psi_source=p.psi_source if need_src else None, num_threads=num_threads,
                   rho_cell=getattr(p, "rho_cell", None), T_cell=getattr(p, "T_cell", None),
-                  kappa_cell=getattr(p, "kappa_cell", None))
+                  kappa_cell=getattr(p, "kappa_cell", None), cv=getattr(p, "cv", 0.0))
 
 
 # ---------------------------------------------------------------- oracle-1 (the reference itself)

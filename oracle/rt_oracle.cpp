@@ -46,7 +46,7 @@ static void rto_cell_tables(rto_solver *s)
    const int N = s->p.N, G = s->p.G;
    rto::CellTables &ct = s->ct;
    const size_t n = (size_t)G * N;
-   ct.B.assign(n, 0.0); ct.dEB.assign(n, 0.0); ct.cor1.assign(n, 0.0); ct.cor2.assign(n, 0.0); ct.cor3.assign(n, 0.0);
+   ct.B.assign(n, 0.0); ct.dBdT.assign(n, 0.0); ct.dEB.assign(n, 0.0); ct.cor1.assign(n, 0.0); ct.cor2.assign(n, 0.0); ct.cor3.assign(n, 0.0);
 #ifdef _OPENMP
 #pragma omp parallel for schedule(static) num_threads(s->p.num_threads > 0 ? s->p.num_threads : 1)
 #endif
@@ -58,9 +58,45 @@ static void rto_cell_tables(rto_solver *s)
       for (int k = 0; k < G; k++)
       {
          const size_t o = (size_t)k + (size_t)G * c;
-         ct.B[o] = g.B[k]; ct.dEB[o] = g.dEB[k]; ct.cor1[o] = g.cor1[k]; ct.cor2[o] = g.cor2[k]; ct.cor3[o] = g.cor3[k];
+         ct.B[o] = g.B[k]; ct.dBdT[o] = g.dBdT[k]; ct.dEB[o] = g.dEB[k]; ct.cor1[o] = g.cor1[k]; ct.cor2[o] = g.cor2[k]; ct.cor3[o] = g.cor3[k];
       }
    }
+}
+
+// EXTENSION, PARITY UNPINNED -- the reference has no material-temperature update; this
+// restatement is the definition the device path is checked against (see rto_params::cv in rt_oracle.h).
+static void rto_temperature_update(rto_solver *s, bool first_step)
+{
+   const rto_params &p = s->p;
+   const rto::Sweep &sw = s->sw;
+   rto::CellTables &ct = s->ct;
+   const int M = p.M, N = p.N, G = p.G;
+   double W = 0.;
+   for (int m = 0; m < M; m++) W += s->wt[m];
+   ct.xA.assign(N, 0.0); ct.xE.assign(N, 0.0); ct.xD.assign(N, 0.0);
+   std::vector<double> Tn(N);
+   for (int c = 0; c < N; c++)
+   {
+      double A = 0., E = 0., D = 0.;
+      for (int g = 0; g < G; g++)
+      {
+         const size_t o = (size_t)g + (size_t)G * c;
+         const double sig = ct.rho[c] * ct.kappa[o];
+         double phi = 0.;
+         for (int m = 0; m < M; m++) phi += s->wt[m] * sw.psi[sw.ip(m, g, c)];
+         A += sig * phi;
+         E += W * (sig * ct.B[o]);
+         D += W * (sig * ct.dBdT[o]);
+      }
+      ct.xA[c] = A; ct.xE[c] = E; ct.xD[c] = D;
+      const double rcv = ct.rho[c] * p.cv, T = ct.T[c];
+      if (first_step || p.ts_method != 3) Tn[c] = T + p.dt * (A - E) / (rcv + p.dt * D);
+      else Tn[c] = (rcv * (2. * T - 0.5 * ct.T_prev[c]) + p.dt * (A - E + D * T)) / (1.5 * rcv + p.dt * D);
+   }
+   ct.T_prev = ct.T;
+   ct.T = Tn;
+   s->p.T_cell = ct.T.data();
+   rto_cell_tables(s);
 }
 
 extern "C" {
@@ -169,7 +205,7 @@ rto_solver *rto_create(const rto_params *p)
    sw.psi_source.assign((size_t)M * G, 0.0);
    if (p->psi_source) std::copy(p->psi_source, p->psi_source + (size_t)M * G, sw.psi_source.begin());
    s->p.psi_source = sw.psi_source.data();
-   s->var = p->rho_cell || p->T_cell || p->kappa_cell;
+   s->var = p->rho_cell || p->T_cell || p->kappa_cell || p->cv > 0.;
    if (s->var)
    {
       rto::CellTables &ct = s->ct;
@@ -253,6 +289,8 @@ void rto_run_stages(rto_solver *s, int n)
          sw.sweep_group(g, kind, tau, snapshot, s->mu.data(), p.bc_left, p.bc_right, gt.rho[g], gt.kappa[g], gt.B[g],
                         p.use_correction != 0, gt.cor1[g], gt.cor2[g], gt.cor3[g], beta, s->var ? &s->ct : nullptr);
       s->stages_done++;
+      const int per_step = p.ts_method == 3 ? 4 : 1;
+      if (p.cv > 0. && s->stages_done % per_step == 0) rto_temperature_update(s, s->stages_done == per_step);
    }
 }
 
@@ -352,6 +390,18 @@ void rto_get_group_terms(const rto_solver *s, double *B, double *dBdT, double *d
 void rto_get_psi_source(const rto_solver *s, double *out)
 {
    std::copy(s->sw.psi_source.begin(), s->sw.psi_source.end(), out);
+}
+
+void rto_get_temperature(const rto_solver *s, double *T, double *A, double *E, double *D)
+{
+   const int N = s->p.N;
+   for (int c = 0; c < N; c++)
+   {
+      if (T) T[c] = s->var ? s->ct.T[c] : s->p.T;
+      if (A) A[c] = s->ct.xA.empty() ? 0. : s->ct.xA[c];
+      if (E) E[c] = s->ct.xE.empty() ? 0. : s->ct.xE[c];
+      if (D) D[c] = s->ct.xD.empty() ? 0. : s->ct.xD[c];
+   }
 }
 
 // correction.cpp:39-63 and 100-122

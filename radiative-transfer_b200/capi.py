@@ -23,8 +23,11 @@ EXPORTS = (
     "rt_stages_done", "rt_total_stages", "rt_reset", "rt_get_psi", "rt_get_ends", "rt_moments",
     "rt_moments_group_major", "rt_balance", "rt_group_ends", "rt_get_group_terms", "rt_get_psi_source",
     "rt_validate", "rt_set_step_output", "rt_get_timing", "rt_reset_timing", "rt_planck_groups", "rt_bench_steps",
-    "rt_host_alloc", "rt_host_free", "rt_multigroup_opacities",
+    "rt_host_alloc", "rt_host_free", "rt_multigroup_opacities", "rt_set_allreduce", "rt_get_temperature",
 )
+
+#: int fn(void *device_buf, size_t count, void *cuda_stream, void *user)  (include/rt_cuda.h: rt_allreduce_fn)
+ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p)
 
 
 class RtParams(C.Structure):
@@ -37,6 +40,7 @@ class RtParams(C.Structure):
         ("kappa_grey", C.c_double),
         ("mu", _dp), ("wt", _dp), ("e_edge", _dp), ("kappa", _dp), ("psi_source", _dp),
         ("rho_cell", _dp), ("T_cell", _dp), ("kappa_cell", _dp),  # extension (ABI 2): cell-dependent material fields
+        ("cv", C.c_double),  # extension (ABI 3): material-temperature update when > 0
     ]
 
 
@@ -46,6 +50,7 @@ class RtTiming(C.Structure):
         ("stages", C.c_longlong), ("unknown_stages", C.c_longlong), ("kernel_launches", C.c_longlong),
         ("h2d_bytes", C.c_longlong), ("d2h_bytes", C.c_longlong),
         ("step_ms", C.c_double), ("step_launches", C.c_longlong),
+        ("tupdate_ms", C.c_double), ("tables_ms", C.c_double), ("tupdate_count", C.c_longlong),
     ]
 
 
@@ -106,6 +111,8 @@ def lib():
         L.rt_host_free.argtypes = [C.c_void_p]
         L.rt_planck_groups.argtypes = [C.c_int, C.c_int, _dp, C.c_int, _dp, _dp, _dp, _dp]
         L.rt_multigroup_opacities.argtypes = [C.c_int, C.c_int, _dp, C.c_double, C.c_double, _dp, _dp, _dp, _dp]
+        L.rt_set_allreduce.argtypes = [vp, ALLREDUCE_FN, C.c_void_p]
+        L.rt_get_temperature.argtypes = [vp, _dp, _dp]
         _lib = L
     return _lib
 

@@ -69,6 +69,14 @@ struct rt_solver
    double *d_rho_c = nullptr, *d_T_c = nullptr, *d_kappa_c = nullptr, *d_B_c = nullptr, *d_dBdT_c = nullptr;
    double *d_vt[5] = {nullptr, nullptr, nullptr, nullptr, nullptr}; // sigma, srcB, cor1, cor2, cor3
    double *d_edge_state[4] = {nullptr, nullptr, nullptr, nullptr};  // B_left, dEB_left, B_right, dEB_right (G each)
+   // material-temperature update (extension; rt_params::cv > 0)
+   bool tupdate = false, T_moved = false;
+   double wsum = 0.0;              // sum of the quadrature weights, ascending
+   double *d_sdB = nullptr;        // [gl][c] sigma_g dB_g/dT
+   double *d_T_prev = nullptr, *d_xsums = nullptr, *d_xpart = nullptr; // N ; 3N (A, E, D) ; chunks*3N
+   long long tsteps_done = 0;      // temperature updates since the state was initialised
+   rt_allreduce_fn allreduce = nullptr;
+   void *allreduce_user = nullptr;
    // batching
    int Gl = 0, Gb = 0, n_batches = 0, Np = 0;
    size_t buf_elems = 0; // double2 elements per time-level buffer
@@ -227,6 +235,8 @@ static int flush_events(rt_solver *s)
       CK(cudaEventElapsedTime(&ms, s->ev_pool[k].a, s->ev_pool[k].b));
       if (s->ev_pool[k].kind < 3) s->tm.sweep_ms[s->ev_pool[k].kind] += ms;
       else if (s->ev_pool[k].kind == 4) s->tm.step_ms += ms;
+      else if (s->ev_pool[k].kind == 5) s->tm.tupdate_ms += ms;
+      else if (s->ev_pool[k].kind == 6) s->tm.tables_ms += ms;
       else s->tm.moments_ms += ms;
    }
    s->ev_used = 0;
@@ -263,6 +273,37 @@ static int event_end(rt_solver *s, EventPair *ep)
 }
 
 // Planck integrals, edge stencils, correction terms, validation sums, boundary table -- all on the device.
+// extension: Planck integrals per (cell, group) and the Correction pipeline per cell at the current T(c); with
+// `with_boundary` also the boundary sources from the boundary cells (they overwrite the uniform boundary table and are
+// built ONCE: a temperature update leaves the incoming boundary intensities alone, like the oracle)
+static int compute_var_tables(rt_solver *s, bool with_boundary)
+{
+   const rt_params &p = s->p;
+   // the last group keeps "the previous value" when the grey remainder is not positive (Planck.cpp:73-76); the oracle
+   // starts every evaluation from zeroed vectors
+   CK(cudaMemset2DAsync(s->d_B_c + (p.G - 1), (size_t)p.G * sizeof(double), 0, sizeof(double), p.N, s->st));
+   CK(cudaMemset2DAsync(s->d_dBdT_c + (p.G - 1), (size_t)p.G * sizeof(double), 0, sizeof(double), p.N, s->st));
+   s->tm.kernel_launches += launch_planck(p.G, p.N, s->d_e_edge, s->d_T_c, s->d_B_c, s->d_dBdT_c, s->st);
+   CellTermsArgs ca;
+   ca.G = p.G; ca.N = p.N; ca.G0 = p.group_begin; ca.groups = s->Gl;
+   ca.e_edge = s->d_e_edge; ca.kappa_cell = s->d_kappa_c; ca.rho_cell = s->d_rho_c; ca.T_cell = s->d_T_c; ca.B_cell = s->d_B_c;
+   ca.dBdT_cell = s->d_dBdT_c;
+   ca.sigma = s->d_vt[0]; ca.srcB = s->d_vt[1]; ca.cor1 = s->d_vt[2]; ca.cor2 = s->d_vt[3]; ca.cor3 = s->d_vt[4];
+   ca.sdB = s->d_sdB;
+   ca.B_left = s->d_edge_state[0]; ca.dEB_left = s->d_edge_state[1]; ca.B_right = s->d_edge_state[2]; ca.dEB_right = s->d_edge_state[3];
+   launch_cell_terms(ca, s->st);
+   s->tm.kernel_launches += 1;
+   if (with_boundary)
+   {
+      if (upload(s, s->d_psi_source, s->psi_source.data(), (size_t)p.M * p.G)) return 1; // the caller's sources, before the BC switch
+      launch_boundary_table_var(p.M, p.G, p.bc_left, p.bc_right, p.use_mg_equilib, p.V, s->d_mu, s->d_edge_state[0], s->d_edge_state[1],
+                                s->d_edge_state[2], s->d_edge_state[3], s->d_psi_source, s->d_bdry, s->st);
+      s->tm.kernel_launches += 1;
+   }
+   CK(cudaGetLastError());
+   return 0;
+}
+
 static int compute_group_tables(rt_solver *s)
 {
    const rt_params &p = s->p;
@@ -294,23 +335,7 @@ static int compute_group_tables(rt_solver *s)
    launch_pack_step_coef(s->d_coef[0], s->d_coef[1], s->d_coef[2], s->d_coef_step, s->Gl * p.M, corr, s->st);
    s->tm.kernel_launches++;
    CK(cudaGetLastError());
-   if (s->var)
-   {
-      // extension: Planck integrals per (cell, group), the Correction pipeline per cell, boundary sources from the
-      // boundary cells (these overwrite the uniform boundary table built above)
-      s->tm.kernel_launches += launch_planck(p.G, p.N, s->d_e_edge, s->d_T_c, s->d_B_c, s->d_dBdT_c, s->st);
-      CellTermsArgs ca;
-      ca.G = p.G; ca.N = p.N; ca.G0 = p.group_begin; ca.groups = s->Gl;
-      ca.e_edge = s->d_e_edge; ca.kappa_cell = s->d_kappa_c; ca.rho_cell = s->d_rho_c; ca.T_cell = s->d_T_c; ca.B_cell = s->d_B_c;
-      ca.sigma = s->d_vt[0]; ca.srcB = s->d_vt[1]; ca.cor1 = s->d_vt[2]; ca.cor2 = s->d_vt[3]; ca.cor3 = s->d_vt[4];
-      ca.B_left = s->d_edge_state[0]; ca.dEB_left = s->d_edge_state[1]; ca.B_right = s->d_edge_state[2]; ca.dEB_right = s->d_edge_state[3];
-      launch_cell_terms(ca, s->st);
-      if (upload(s, s->d_psi_source, s->psi_source.data(), (size_t)p.M * p.G)) return 1; // the caller's sources, before the BC switch
-      launch_boundary_table_var(p.M, p.G, p.bc_left, p.bc_right, p.use_mg_equilib, p.V, s->d_mu, s->d_edge_state[0], s->d_edge_state[1],
-                                s->d_edge_state[2], s->d_edge_state[3], s->d_psi_source, s->d_bdry, s->st);
-      s->tm.kernel_launches += 2;
-      CK(cudaGetLastError());
-   }
+   if (s->var && compute_var_tables(s, true)) return 1;
    return 0;
 }
 
@@ -332,6 +357,17 @@ static int load_batch(rt_solver *s, int start)
    s->i_prev = s->i_half_neg = s->i_half_pos = -1;
    s->half_stale = false;
    s->stages_done = 0;
+   if (s->tupdate)
+   {
+      // a new run starts from the caller's T(c): rebuild the per-cell tables if an update has moved it
+      if (s->T_moved)
+      {
+         if (upload(s, s->d_T_c, s->T_cell.data(), s->p.N)) return 1;
+         if (compute_var_tables(s, false)) return 1;
+         s->T_moved = false;
+      }
+      s->tsteps_done = 0;
+   }
    if (s->var) launch_init_state_var(s->E[0], s->d_B_c, s->p.M, s->p.N, s->Np, s->p.G, s->p.group_begin + start, s->batch_groups, s->st);
    else launch_init_state(s->E[0], s->d_B, s->p.M, s->p.N, s->Np, s->p.group_begin + start, s->batch_groups, s->st);
    s->tm.kernel_launches += 1;
@@ -351,7 +387,8 @@ extern "C" int rt_destroy(rt_solver *s)
                      s->d_coef[0], s->d_coef[1], s->d_coef[2], s->d_coef_step};
    for (double *t : tabs) if (t) cudaFree(t);
    double *vtabs[] = {s->d_rho_c, s->d_T_c, s->d_kappa_c, s->d_B_c, s->d_dBdT_c, s->d_vt[0], s->d_vt[1], s->d_vt[2], s->d_vt[3],
-                      s->d_vt[4], s->d_edge_state[0], s->d_edge_state[1], s->d_edge_state[2], s->d_edge_state[3]};
+                      s->d_vt[4], s->d_edge_state[0], s->d_edge_state[1], s->d_edge_state[2], s->d_edge_state[3],
+                      s->d_sdB, s->d_T_prev, s->d_xsums, s->d_xpart};
    for (double *t : vtabs) if (t) cudaFree(t);
    for (int k = 0; k < 4; ++k) if (s->E[k]) cudaFreeAsync(s->E[k], s->st);
    if (s->st) cudaStreamSynchronize(s->st);
@@ -385,7 +422,8 @@ static int validate_params(const rt_params *p)
    for (int i = 0; i < p->M; ++i)
       if (p->mu[i] == 0.0 || (i < p->M / 2) != (p->mu[i] < 0.0)) return fail("mu should not be 0 and must be ascending with M/2 negative nodes");
    if (p->max_timesteps < 0) return fail("rt_create: max_timesteps < 0");
-   if ((p->rho_cell || p->T_cell || p->kappa_cell) && p->validate)
+   if (p->cv < 0.0) return fail("rt_create: cv must be >= 0 (0 = no material-temperature update)");
+   if ((p->rho_cell || p->T_cell || p->kappa_cell || p->cv > 0.0) && p->validate)
       return fail("rt_create: the validation sums (correction.cpp:39-63) are defined for the uniform slab only; set validate = 0 with cell-dependent fields");
    return 0;
 }
@@ -416,7 +454,8 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
    if (p->psi_source) std::copy(p->psi_source, p->psi_source + (size_t)M * G, s->psi_source.begin());
    s->p.mu = s->mu.data(); s->p.wt = s->wt.data(); s->p.e_edge = s->e_edge.data(); s->p.kappa = s->kappa.data();
    s->p.psi_source = s->psi_source.data();
-   s->var = p->rho_cell || p->T_cell || p->kappa_cell;
+   s->tupdate = p->cv > 0.0;
+   s->var = p->rho_cell || p->T_cell || p->kappa_cell || s->tupdate;
    if (s->var)
    {
       s->rho_cell.assign(N, p->rho);
@@ -512,6 +551,12 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       CKD(dalloc(&s->d_B_c, (size_t)G * N)); CKD(dalloc(&s->d_dBdT_c, (size_t)G * N));
       for (int k = 0; k < 5; ++k) CKD(dalloc(&s->d_vt[k], (size_t)s->Gl * N));
       for (int k = 0; k < 4; ++k) CKD(dalloc(&s->d_edge_state[k], G));
+      if (s->tupdate)
+      {
+         CKD(dalloc(&s->d_sdB, (size_t)s->Gl * N)); CKD(dalloc(&s->d_T_prev, N)); CKD(dalloc(&s->d_xsums, (size_t)3 * N));
+         CKD(dalloc(&s->d_xpart, (size_t)exchange_chunks(s->Gl) * 3 * N));
+         for (int m = 0; m < M; ++m) s->wsum += s->wt[m];
+      }
       CKC(cudaMemsetAsync(s->d_B_c, 0, (size_t)G * N * sizeof(double), s->st));
       CKC(cudaMemsetAsync(s->d_dBdT_c, 0, (size_t)G * N * sizeof(double), s->st));
       CKD(upload(s, s->d_rho_c, s->rho_cell.data(), N)); CKD(upload(s, s->d_T_c, s->T_cell.data(), N));
@@ -796,6 +841,40 @@ static int materialize_half(rt_solver *s)
 
 static int step_output(rt_solver *s);
 static int finish_batch(rt_solver *s);
+static int ensure_result_arrays(rt_solver *s);
+
+// Material-temperature update after a completed time step (extension; definition: rt_cuda.h, rt_params::cv;
+// oracle: rto_temperature_update).  phi of the new state -> group sums A, E, D over the owned groups -> all-reduce hook
+// (the one exchange step of the path: groups couple here and only here) -> T' -> Planck integrals and per-cell tables at T'.
+static int temperature_update(rt_solver *s)
+{
+   const rt_params &p = s->p;
+   if (ensure_result_arrays(s)) return 1;
+   EventPair *ep;
+   if (event_begin(s, 5, &ep)) return 1;
+   launch_moments(s->E[s->i_ends], s->d_mu, s->d_wt, p.M, p.N, s->Np, s->batch_groups, s->d_phi, nullptr, nullptr, s->st);
+   ExchangeArgs x;
+   x.N = p.N; x.groups = s->Gl; x.W = s->wsum;
+   x.sigma = s->d_vt[0]; x.srcB = s->d_vt[1]; x.sdB = s->d_sdB; x.phi = s->d_phi;
+   x.partial = s->d_xpart; x.sums = s->d_xsums;
+   s->tm.kernel_launches += 1 + launch_exchange_sums(x, s->st);
+   CK(cudaGetLastError());
+   if (s->allreduce)
+   {
+      const int rc = s->allreduce(s->d_xsums, (size_t)3 * p.N, (void *)s->st, s->allreduce_user);
+      if (rc) return fail("rt: the all-reduce hook failed with code %d in the temperature update after stage %d", rc, s->stages_done);
+   }
+   launch_temperature_update(p.N, p.ts_method == 3 && s->tsteps_done > 0, p.dt, p.cv, s->d_rho_c, s->d_xsums, s->d_T_c, s->d_T_prev, s->st);
+   s->tm.kernel_launches += 1;
+   if (event_end(s, ep)) return 1;
+   if (event_begin(s, 6, &ep)) return 1;
+   if (compute_var_tables(s, false)) return 1;
+   if (event_end(s, ep)) return 1;
+   s->tsteps_done++;
+   s->tm.tupdate_count++;
+   s->T_moved = true;
+   return 0;
+}
 
 static int run_stages(rt_solver *s, int n)
 {
@@ -814,6 +893,8 @@ static int run_stages(rt_solver *s, int n)
          if (run_one_stage(s)) return 1;
          k += 1;
       }
+      if (s->tupdate && s->stages_done % per_step == 0)
+         if (temperature_update(s)) return 1;
       if (s->step_phi_host && s->stages_done % per_step == 0)
          if (step_output(s)) return 1;
    }
@@ -855,6 +936,33 @@ extern "C" int rt_solve(rt_solver *s)
    if (flush_events(s)) return 1;
    CK(cudaStreamSynchronize(s->st));
    if (s->step_phi_host) CK(cudaStreamSynchronize(s->copy_st));
+   return 0;
+}
+
+extern "C" int rt_set_allreduce(rt_solver *s, rt_allreduce_fn fn, void *user)
+{
+   if (!s) return fail("rt_set_allreduce: null handle");
+   s->allreduce = fn;
+   s->allreduce_user = user;
+   return 0;
+}
+
+extern "C" int rt_get_temperature(rt_solver *s, double *T, double *sums3)
+{
+   if (!s || !T) return fail("rt_get_temperature: null argument");
+   CK(cudaSetDevice(s->p.device));
+   if (!s->var)
+   {
+      for (int c = 0; c < s->p.N; ++c) T[c] = s->p.T;
+      if (sums3) std::fill(sums3, sums3 + (size_t)3 * s->p.N, 0.0);
+      return 0;
+   }
+   if (download(s, T, s->d_T_c, s->p.N)) return 1;
+   if (sums3)
+   {
+      if (!s->tupdate || s->tsteps_done == 0) std::fill(sums3, sums3 + (size_t)3 * s->p.N, 0.0);
+      else if (download(s, sums3, s->d_xsums, (size_t)3 * s->p.N)) return 1;
+   }
    return 0;
 }
 

@@ -79,6 +79,7 @@ __global__ void cell_terms_kernel(CellTermsArgs a)
          a.cor1[o] = dsig;
          a.cor2[o] = 3.0 * sig * Bg - dkap;
          a.cor3[o] = dsig * (4.0 * Bg - dEB);
+         if (a.sdB) a.sdB[o] = sig * a.dBdT_cell[(size_t)G * c + g];
       }
    }
 }
@@ -290,6 +291,64 @@ cudaError_t launch_var_sweep(int kind, bool corr, const VarSweepArgs &a, cudaStr
    if (kind == KIND_CN) return launch_var_kind<KIND_CN>(corr, a, grid, st);
    if (kind == KIND_BDF) return launch_var_kind<KIND_BDF>(corr, a, grid, st);
    return cudaErrorInvalidValue;
+}
+
+// ------------------------------------------------------------------------------------------ material-temperature update
+// Group sums per cell, the one place where energy groups couple.  Thread per cell (the tables are [gl][c]: a warp reads
+// 256 contiguous bytes per table and group), groups cut into chunks over blockIdx.y so that N-sized problems still fill
+// the machine; the chunks are then added in ascending order (deterministic, no atomics).
+__global__ void exchange_partial_kernel(ExchangeArgs a)
+{
+   const int c = blockIdx.x * blockDim.x + threadIdx.x;
+   if (c >= a.N) return;
+   const int g0 = blockIdx.y * EXCHANGE_GROUPS_PER_CHUNK, g1 = min(a.groups, g0 + EXCHANGE_GROUPS_PER_CHUNK);
+   double A = 0.0, E = 0.0, D = 0.0;
+   for (int gl = g0; gl < g1; ++gl)
+   {
+      const size_t o = (size_t)gl * a.N + c;
+      A += a.sigma[o] * a.phi[o];
+      E += a.W * a.srcB[o];
+      D += a.W * a.sdB[o];
+   }
+   double *p = a.partial + (size_t)blockIdx.y * 3 * a.N;
+   p[c] = A; p[a.N + c] = E; p[2 * (size_t)a.N + c] = D;
+}
+
+__global__ void exchange_reduce_kernel(int N, int chunks, const double *__restrict__ partial, double *__restrict__ sums)
+{
+   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+   if (idx >= 3 * N) return;
+   double v = 0.0;
+   for (int k = 0; k < chunks; ++k) v += partial[(size_t)k * 3 * N + idx];
+   sums[idx] = v;
+}
+
+int launch_exchange_sums(const ExchangeArgs &a, cudaStream_t st)
+{
+   const int chunks = exchange_chunks(a.groups);
+   exchange_partial_kernel<<<dim3((a.N + 127) / 128, chunks), 128, 0, st>>>(a);
+   exchange_reduce_kernel<<<(3 * a.N + 255) / 256, 256, 0, st>>>(a.N, chunks, a.partial, a.sums);
+   return 2;
+}
+
+__global__ void temperature_update_kernel(int N, int bdf2, double dt, double cv, const double *__restrict__ rho_cell,
+                                          const double *__restrict__ sums, double *__restrict__ T, double *__restrict__ T_prev)
+{
+   const int c = blockIdx.x * blockDim.x + threadIdx.x;
+   if (c >= N) return;
+   const double A = sums[c], E = sums[N + c], D = sums[2 * (size_t)N + c];
+   const double rcv = rho_cell[c] * cv, t = T[c];
+   double tn;
+   if (!bdf2) tn = t + dt * (A - E) / (rcv + dt * D);
+   else tn = (rcv * (2. * t - 0.5 * T_prev[c]) + dt * (A - E + D * t)) / (1.5 * rcv + dt * D);
+   T_prev[c] = t;
+   T[c] = tn;
+}
+
+void launch_temperature_update(int N, bool bdf2, double dt, double cv, const double *rho_cell, const double *sums, double *T,
+                               double *T_prev, cudaStream_t st)
+{
+   temperature_update_kernel<<<(N + 255) / 256, 256, 0, st>>>(N, bdf2 ? 1 : 0, dt, cv, rho_cell, sums, T, T_prev);
 }
 
 // ------------------------------------------------------------------------------------------ diagnostics

@@ -23,7 +23,9 @@ struct CellTermsArgs
    const double *rho_cell;   // N
    const double *T_cell;     // N
    const double *B_cell;     // g + G*c, jk units (planck kernels with ncell = N)
+   const double *dBdT_cell;  // g + G*c ; only read when sdB is wanted
    double *sigma, *srcB, *cor1, *cor2, *cor3; // [gl][c]
+   double *sdB;              // [gl][c] sigma_g dB_g/dT, or nullptr (material-temperature update only)
    double *B_left, *dEB_left, *B_right, *dEB_right; // G each: material state of cell 0 / cell N-1 (boundary sources)
 };
 void launch_cell_terms(const CellTermsArgs &a, cudaStream_t st);
@@ -50,6 +52,24 @@ struct VarSweepArgs
 };
 // one CTA per chain, tiles in sequence (no look-back): BE / CN / BDF stage with cell-dependent stepper constants
 cudaError_t launch_var_sweep(int kind, bool corr, const VarSweepArgs &a, cudaStream_t st, int *grid_out);
+
+// ---- material-temperature update: EXTENSION, parity unpinned (the reference has none); the
+// definition is oracle/rt_oracle.cpp rto_temperature_update.
+struct ExchangeArgs
+{
+   int N, groups;            // owned groups; tables and phi are [gl][c]
+   double W;                 // sum of the quadrature weights
+   const double *sigma, *srcB, *sdB, *phi;
+   double *partial;          // [chunk][3][N] scratch, chunk = EXCHANGE_GROUPS_PER_CHUNK groups
+   double *sums;             // [3][N]: A, E, D summed over the owned groups (ascending)
+};
+constexpr int EXCHANGE_GROUPS_PER_CHUNK = 32;
+inline int exchange_chunks(int groups) { return (groups + EXCHANGE_GROUPS_PER_CHUNK - 1) / EXCHANGE_GROUPS_PER_CHUNK; }
+// absorbed / emitted power and the emission derivative per cell, summed over the owned groups; returns kernels launched
+int launch_exchange_sums(const ExchangeArgs &a, cudaStream_t st);
+// T <- T' from the (all-reduced) sums; T_prev <- T.  bdf2 = later steps of a BDF2 run
+void launch_temperature_update(int N, bool bdf2, double dt, double cv, const double *rho_cell, const double *sums, double *T,
+                               double *T_prev, cudaStream_t st);
 
 // balance (solver.cpp:240-284) with per-cell sigma and T, group-end spectra (826-850)
 void launch_diagnostics_var(const double2 *ends, const double *phi, const double *mu, const double *wt, const double *sigma_cell,

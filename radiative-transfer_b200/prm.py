@@ -109,6 +109,9 @@ class Parameters:
     rho_cell: Optional[np.ndarray] = field(default=None, compare=False)    # N
     T_cell: Optional[np.ndarray] = field(default=None, compare=False)      # N
     kappa_cell: Optional[np.ndarray] = field(default=None, compare=False)  # (G, N)
+    # EXTENSION (the reference has no temperature update): specific heat of the material.
+    # cv > 0 switches on the material-temperature update after every time step (include/rt_cuda.h, rt_params::cv).
+    cv: float = 0.0
 
     @property
     def dx(self) -> float:

@@ -1,7 +1,8 @@
 """Energy-group sharding across ranks (one process per GPU).
 
-Groups never couple in the solve (no scattering, no temperature update), so the path shards by
-contiguous blocks of groups with NO data-path collective; every rank keeps the G-length tables for all groups (the
+Groups never couple in the reference's solve (no scattering, no temperature update), so the path shards by
+contiguous blocks of groups with NO data-path collective (the material-temperature extension, rt_params::cv, adds the
+one exchange step: an all-reduce of three N-vectors per time step, `make_allreduce_hook`); every rank keeps the G-length tables for all groups (the
 edge stencils of correction.cpp:125-249 and the "remainder into the last group" of Planck.cpp:58-76 need them).
 The only communication is the final gather of per-group results, done with torch.distributed (NCCL on GPUs, gloo in the
 CPU tests)."""
@@ -80,3 +81,41 @@ def reduce_vector_sum(local: np.ndarray, dist=None, device=None) -> np.ndarray:
     t = torch.from_numpy(local.copy()).to(dev)
     dist.all_reduce(t, op=dist.ReduceOp.SUM)
     return t.cpu().numpy()
+
+
+def allreduce_tensor_(t, dist):
+    """In-place element-wise sum of a torch tensor over the ranks (NCCL for device tensors, gloo for CPU tensors)."""
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return t
+
+
+class _DevicePointer:
+    """A raw device buffer of `count` float64 as something torch.as_tensor can wrap without copying."""
+
+    def __init__(self, ptr: int, count: int):
+        self.__cuda_array_interface__ = {"shape": (count,), "typestr": "<f8", "data": (ptr, False), "version": 3,
+                                         "strides": None}
+
+
+def make_allreduce_hook(dist, device: int):
+    """The callback for rt_set_allreduce (include/rt_cuda.h): sums the 3*N group sums of the material-temperature update
+    (absorbed power, emitted power, emission derivative per cell) over the ranks with torch.distributed -- NCCL over
+    NVLink/NVSwitch on a multi-GPU box -- in place on the library's own device buffer, ordered on the library's stream.
+    Returns a ctypes function object; the caller must keep it alive as long as the handle uses it."""
+    import torch
+    from . import capi
+
+    def hook(buf, count, stream, user):
+        try:
+            dev = torch.device("cuda", device)
+            ext = torch.cuda.ExternalStream(int(stream), device=dev)
+            with torch.cuda.device(dev), torch.cuda.stream(ext):
+                t = torch.as_tensor(_DevicePointer(int(buf), int(count)), device=dev)
+                allreduce_tensor_(t, dist)
+            return 0
+        except Exception as exc:  # an exception must not unwind through the C frames
+            import sys
+            print(f"rt all-reduce hook: {exc!r}", file=sys.stderr)
+            return 1
+
+    return capi.ALLREDUCE_FN(hook)

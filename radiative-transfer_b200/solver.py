@@ -28,7 +28,7 @@ class Solver:
     def __init__(self, parameter_handler: Parameters, psi_mat: Optional[np.ndarray] = None,
                  phi: Optional[np.ndarray] = None, F: Optional[np.ndarray] = None, *, device: int = 0,
                  group_begin: int = 0, group_count: Optional[int] = None, groups_per_batch: int = 0,
-                 fetch_psi: bool = True):
+                 fetch_psi: bool = True, dist=None):
         ph = self.ph = parameter_handler
         self.M, self.N, self.num_groups = ph.M, ph.N, ph.G
         self.group_begin = group_begin
@@ -87,8 +87,16 @@ class Solver:
                 a = np.asfortranarray(np.asarray(a, dtype=np.float64).reshape(shape))  # kappa(g, c) at g + G*c
                 self._cell_fields.append(a)
                 setattr(p, name, capi.ptr(a))
+        # extension: material-temperature update when the specific heat is given
+        p.cv = float(getattr(ph, "cv", 0.0) or 0.0)
         self._h = C.c_void_p()
         capi.check(capi.lib().rt_create(C.byref(p), C.byref(self._h)))
+        # a group shard of a temperature-coupled solve: the group sums go through torch.distributed (NCCL) every step
+        self._allreduce = None
+        if p.cv > 0.0 and dist is not None and dist.is_initialized() and dist.get_world_size() > 1:
+            from . import sharding
+            self._allreduce = sharding.make_allreduce_hook(dist, device)
+            capi.check(capi.lib().rt_set_allreduce(self._h, self._allreduce, None))
         self.resident = self.plan().resident == 1
         if fetch_psi and self.resident:
             self._pull_psi()  # initial condition psi = B_g (solver.cpp:166-181)
@@ -286,6 +294,14 @@ class Solver:
         capi.check(capi.lib().rt_get_group_terms(
             self._h, *[capi.ptr(out[k]) for k in ("B", "dBdT", "dEB", "dsigEdE", "dkapEB", "kappa_edge")]))
         return out
+
+    def temperature(self, with_sums: bool = False):
+        """extension: the material temperature T(c); with_sums also the group sums A, E, D (absorbed power, emitted
+        power, emission derivative; after the all-reduce) of the most recent temperature update"""
+        T = np.zeros(self.N)
+        sums = np.zeros((3, self.N)) if with_sums else None
+        capi.check(capi.lib().rt_get_temperature(self._h, capi.ptr(T), capi.ptr(sums) if with_sums else None))
+        return (T, sums[0], sums[1], sums[2]) if with_sums else T
 
     def psi_source(self):
         a = _f((self.M, self.num_groups))

@@ -1,0 +1,27 @@
+"""Multi-GPU: the material-temperature update's all-reduce over NCCL (one process per GPU under torchrun).  Needs two
+GPUs on the box (`gpurun --gpus 2`); skipped otherwise."""
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_two_ranks_nccl_match_the_oracle():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(ROOT, "tests", "nccl_temperature_worker.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    lines = [ln for ln in r.stdout.splitlines() if ln.startswith("NCCL_TEMPERATURE")]
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert len(lines) == 2 and all("ok=True" in ln for ln in lines), lines
