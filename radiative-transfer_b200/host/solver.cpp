@@ -131,6 +131,7 @@ Solver::Solver(ParameterHandler &parameter_handler,
    p.mu = mu.data(); p.wt = wt.data(); p.e_edge = edge.data(); p.kappa = kap.data();
    p.psi_source = have_src ? src.data() : nullptr;
    p.rho_cell = p.T_cell = p.kappa_cell = nullptr; // the reference's slab is uniform (solver.cpp:150-157)
+   p.cv = 0.0;                                     // and its temperature never changes
    if (rt_create(&p, &handle)) die("Solver");
 
    // initial condition psi = B_g, evaluated on the device (solver.cpp:166-181)
