@@ -242,6 +242,9 @@ def main():
     ap.add_argument("--V", type=float, default=1.0, help="material speed: 1 = correction source live (default); 0 = the source vanishes")
     ap.add_argument("--cell-fields", action="store_true",
                     help="extension (SURVEY 8(f).2): smooth synthetic rho(c), T(c), kappa_g(c); per-stage cell-dependent kernels")
+    ap.add_argument("--cv", type=float, default=0.0,
+                    help="extension (SURVEY 8(f).4): specific heat > 0 switches the material-temperature update on (group sums "
+                         "all-reduced over the ranks every step, Planck integrals + per-cell tables rebuilt every step)")
     ap.add_argument("--groups-per-batch", type=int, default=0)
     ap.add_argument("--cells", type=int, default=0, help="override the number of cells (debug)")
     ap.add_argument("--groups", type=int, default=0, help="override the number of groups (debug)")
@@ -277,6 +280,9 @@ def main():
     g0, gn = sharding.group_range(G, world, rank)
     K, W = args.steps, args.warmup
     p = synthetic_parameters(rt, M, G, N, bcl, bcr, args.dt, K, V=args.V)
+    if args.cv > 0.0:
+        p.cv = args.cv
+        args.cell_fields = True
     if args.cell_fields:
         x = (np.arange(N) + 0.5) / N
         p.T_cell = 1.0 + 0.3 * np.sin(2 * np.pi * x) ** 2
@@ -284,7 +290,8 @@ def main():
         p.kappa_cell = np.asarray(p.group_kappa)[:, None] * (1.0 + 0.5 * np.sin(7 * np.pi * x))[None, :]
 
     # ------------------------------------------------------------- device-resident timing (`value`)
-    s = rt.Solver(p, device=local_rank, group_begin=g0, group_count=gn, groups_per_batch=args.groups_per_batch, fetch_psi=False)
+    s = rt.Solver(p, device=local_rank, group_begin=g0, group_count=gn, groups_per_batch=args.groups_per_batch, fetch_psi=False,
+                  dist=dist)
     plan = s.plan()
     if dist is not None:
         dist.barrier()
@@ -355,6 +362,15 @@ def main():
                                else "rtk::sweep_kernel<KIND,CORR,T,CPT,RING> (BE,CN,BE,BDF per step)"),
                     "algorithmic_bytes_per_unknown": bpu, "by_kind": by_kind}
     gpu_launches = int(tm.kernel_launches)
+    tupdate = None
+    if tm.tupdate_count > 0:
+        # material-temperature update (extension): device time per time step of its two parts, this rank
+        nt = int(tm.tupdate_count)
+        tupdate = {"updates": nt, "exchange_ms_per_step": tm.tupdate_ms / nt, "tables_ms_per_step": tm.tables_ms / nt,
+                   "sweep_ms_per_step": sum(tm.sweep_ms) / nt, "allreduce": "NCCL (torch.distributed) on the library's device buffer" if world > 1 else "none (all groups owned)",
+                   "allreduce_bytes_per_step": 3 * N * 8,
+                   "what": "exchange = moments + group sums A,E,D + all-reduce + T update; tables = Planck integrals of all G groups per cell "
+                           "+ per-cell correction terms at the new T"}
 
     # ------------------------------------------------------------- end to end through the public API (`e2e`)
     e2e = None
@@ -366,7 +382,8 @@ def main():
             if dist is not None:
                 dist.barrier()
             t0 = time.perf_counter()
-            s2 = rt.Solver(p, device=local_rank, group_begin=g0, group_count=gn, groups_per_batch=args.groups_per_batch, fetch_psi=False)
+            s2 = rt.Solver(p, device=local_rank, group_begin=g0, group_count=gn, groups_per_batch=args.groups_per_batch, fetch_psi=False,
+                           dist=dist)
             s2.set_step_output(pin, True)
             t_setup = time.perf_counter() - t0
             s2.solve()
@@ -391,10 +408,10 @@ def main():
                 "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "strong" if workload == "c5" else "weak",
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": workload, "M": M, "G": G, "N": N, "dt": args.dt, "ts_method": "BDF2 (BE,CN,BE,BDF)",
-                           "bc": [bcl, bcr], "V": args.V, "cell_fields": bool(args.cell_fields), "use_correction": True, "parallelism": f"groups sharded x{world}",
+                           "bc": [bcl, bcr], "V": args.V, "cell_fields": bool(args.cell_fields), "cv": args.cv, "use_correction": True, "parallelism": f"groups sharded x{world}",
                            "groups_per_rank": gn, "groups_per_batch": plan.groups_per_batch, "batches": plan.n_batches,
                            "l2": "inputs larger than L2 (each launch streams >= 10 GB)" if M * min(plan.groups_per_batch, gn) * N * 32 > 2e8 else "inputs smaller than L2"},
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": gpu_launches,
+                "roofline": roofline, "temperature_update": tupdate, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": gpu_launches,
                 "clocks": clk.summary(), "s_per_bdf2_step": ms_max / K * 1e-3,
                 "sweep_grid": plan.sweep_grid, "sweep_block": plan.sweep_block, "fused_step": bool(plan.fused),
                 "step_tile_cells": plan.step_tile_cells, "step_chain_warps": plan.step_chain}

@@ -26,95 +26,111 @@ __device__ __forceinline__ double rad_a_long()
 
 __device__ __forceinline__ double inv_h3c2() { return 1.0 / ((H_KEV_SH * H_KEV_SH * H_KEV_SH) * (C_LIGHT * C_LIGHT)); }
 
-// Planck function and its temperature derivative at one energy (Planck.h:86-125), k = 1.
-__device__ __forceinline__ double planck_B(double T, double E)
+// The group integrals follow Planck.cpp:85-229 with the pointwise functions of Planck.h:86-125 (k = 1):
+//   z2 <= 0.7: 12-point Gauss-Legendre of  B(E) = 2 E^3 / (h^3 c^2 (e^{E/T} - 1)),  dB/dT(E) = 2 E^4 e^{E/T} / (h^3 c^2 T^2 (e^{E/T} - 1)^2)
+//   z1 >= 0.5: 2 T^4 / (h^3 c^2) [S(z1) - S(z2)],  S(z) = sum_{n=N..1} e^{-nz}/n^4 P(nz) summed in DESCENDING n
+//              (P cubic for B, quartic and T^3 for dB/dT; Planck.cpp:94-120, 170-194); N starts at 32 and grows while the
+//              tail estimate exceeds 2.2e-16 relative to the first term
+//   otherwise: split at z = 0.6 (Gauss below, series above); the result times 4*pi (truncated pi).
+// ---- B and dB/dT of one group together.  Same operations, in the same order, as integrate_B and integrate_dBdT
+// evaluated one after the other; what they have in common is evaluated once: exp(-n z) of the series terms (each
+// sum keeps its own adaptive term count), the term weights 1/n^4, E/T and expm1(E/T) at the Gauss points.
+__device__ void planck_series_pair(double z1, double z2, double &outB, double &outD)
 {
-   return 2.0 * (E * E * E) * inv_h3c2() / expm1(E / T);
-}
-__device__ __forceinline__ double planck_dBdT(double T, double E)
-{
-   const double ex = exp(E / T), em = expm1(E / T);
-   const double E2 = E * E;
-   return 2.0 * inv_h3c2() * (E2 * E2) / (T * T) * ex / (em * em);
-}
-
-// S(z1) - S(z2), S(z) = sum_{n=N..1} e^{-nz}/n^4 * P(nz), summed in DESCENDING n like the reference
-// (Planck.cpp:94-120, 170-194).  DERIV selects P: cubic (B) or quartic (dB/dT).  N starts at 32 and
-// grows while the tail estimate exceeds 2.2e-16 relative to the first term.
-template <bool DERIV>
-__device__ double planck_series(double z1, double z2)
-{
-   auto poly = [](double x) {
-      return DERIV ? ((((x + 4.0) * x + 12.0) * x + 24.0) * x + 24.0) : (((x + 3.0) * x + 6.0) * x + 6.0);
-   };
+   auto polyB = [](double x) { return (((x + 3.0) * x + 6.0) * x + 6.0); };
+   auto polyD = [](double x) { return ((((x + 4.0) * x + 12.0) * x + 24.0) * x + 24.0); };
    const double eps = 2.220446049250313e-16;
-   int N = 32;
-   double first = exp(-z1) * poly(z1);
-   first = fmax(first, eps);
-   const double geo = 1.0 / (1.0 - exp(-z1));
+   const double ez1 = exp(-z1);
+   const double firstB = fmax(ez1 * polyB(z1), eps), firstD = fmax(ez1 * polyD(z1), eps);
+   const double geo = 1.0 / (1.0 - ez1);
+   int NB = 32, ND = 32;
    while (true)
    {
-      const double n1 = N + 1.0;
-      const double n2 = n1 * n1;
-      const double val = exp(-n1 * z1) * geo / (n2 * n2) * poly(n1 * z1) / first;
-      if (val > eps && N < (1 << 20)) ++N; else break;
+      const double n1 = NB + 1.0, n2 = n1 * n1;
+      const double val = exp(-n1 * z1) * geo / (n2 * n2) * polyB(n1 * z1) / firstB;
+      if (val > eps && NB < (1 << 20)) ++NB; else break;
    }
-   double s1 = 0.0, s2 = 0.0;
-   for (int n = N; n > 0; --n)
+   while (true)
+   {
+      const double n1 = ND + 1.0, n2 = n1 * n1;
+      const double val = exp(-n1 * z1) * geo / (n2 * n2) * polyD(n1 * z1) / firstD;
+      if (val > eps && ND < (1 << 20)) ++ND; else break;
+   }
+   double b1 = 0.0, b2 = 0.0, d1 = 0.0, d2 = 0.0;
+   for (int n = max(NB, ND); n > 0; --n)
    {
       const double dn = (double)n, n2 = dn * dn, in4 = 1.0 / (n2 * n2);
-      s1 += exp(-dn * z1) * in4 * poly(dn * z1);
-      s2 += exp(-dn * z2) * in4 * poly(dn * z2);
+      const double x1 = dn * z1, x2 = dn * z2;
+      const double t1 = exp(-x1) * in4, t2 = exp(-x2) * in4;
+      if (n <= NB) { b1 += t1 * polyB(x1); b2 += t2 * polyB(x2); }
+      if (n <= ND) { d1 += t1 * polyD(x1); d2 += t2 * polyD(x2); }
    }
-   return s1 - s2;
+   outB = b1 - b2;
+   outD = d1 - d2;
 }
 
-template <bool DERIV>
-__device__ double gauss12(double T, double lo, double hi)
+__device__ void gauss12_pair(double T, double lo, double hi, double &outB, double &outD)
 {
    const double mid = 0.5 * (hi + lo), map = 0.5 * (hi - lo);
-   double acc = 0.0;
+   double accB = 0.0, accD = 0.0;
 #pragma unroll
    for (int i = 0; i < 12; ++i)
    {
       const double E = mid + map * c_gauss_pt[i];
-      acc += map * c_gauss_w[i] * (DERIV ? planck_dBdT(T, E) : planck_B(T, E));
+      const double x = E / T, em = expm1(x), ex = exp(x), E2 = E * E;
+      const double mw = map * c_gauss_w[i];
+      accB += mw * (2.0 * (E * E * E) * inv_h3c2() / em);
+      accD += mw * (2.0 * inv_h3c2() * (E2 * E2) / (T * T) * ex / (em * em));
    }
-   return acc;
+   outB = accB;
+   outD = accD;
 }
 
-// One group integral in keV units, times 4*pi (Planck.cpp:85-154 / 161-229): 12-point Gauss for
-// z2 <= 0.7, series for z1 >= 0.5, split at z = 0.6 otherwise.
-template <bool DERIV>
-__device__ double planck_group_integral(double T, double E_min, double E_max)
+__device__ void planck_group_pair(double T, double E_min, double E_max, double &B, double &D)
 {
-   if (T == 0.0 || E_min == E_max) return 0.0;
+   B = 0.0; D = 0.0;
+   if (T == 0.0 || E_min == E_max) return;
    const double z1 = E_min / T, z2 = E_max / T;
    const double T2 = T * T;
-   const double pref = 2.0 * (DERIV ? T2 * T : T2 * T2) * inv_h3c2();
-   double v;
-   if (z2 <= 0.7) v = gauss12<DERIV>(T, E_min, E_max);
-   else if (z1 >= 0.5) v = pref * planck_series<DERIV>(z1, z2);
-   else v = gauss12<DERIV>(T, E_min, 0.6 * T) + pref * planck_series<DERIV>(0.6, z2);
-   return v * 4.0 * PI_TRUNC;
+   const double prefB = 2.0 * (T2 * T2) * inv_h3c2(), prefD = 2.0 * (T2 * T) * inv_h3c2();
+   double vB, vD;
+   if (z2 <= 0.7) gauss12_pair(T, E_min, E_max, vB, vD);
+   else if (z1 >= 0.5)
+   {
+      planck_series_pair(z1, z2, vB, vD);
+      vB *= prefB; vD *= prefD;
+   }
+   else
+   {
+      double sB, sD;
+      gauss12_pair(T, E_min, 0.6 * T, vB, vD);
+      planck_series_pair(0.6, z2, sB, sD);
+      vB = vB + prefB * sB; vD = vD + prefD * sD;
+   }
+   B = vB * 4.0 * PI_TRUNC;
+   D = vD * 4.0 * PI_TRUNC;
 }
 
-// raw[cell][g] for g < G-1 ; one thread per (cell, group) x {B, dBdT}
+// Tables are GROUP-MAJOR: B[g * ncell + c].  One thread per (group, cell), CELL fastest: the lanes of a warp integrate
+// the same group at neighbouring temperatures, so they take the same branch (Gauss / series / split) and run the same
+// number of series terms -- with the group fastest a warp executed ~10 of 32 lanes per instruction (ncu) -- and the
+// stores are coalesced.  g < G-1 only; the last group is the remainder (planck_finalize_kernel).
 __global__ void planck_integrals_kernel(int G, int ncell, const double *__restrict__ e_edge, const double *__restrict__ T,
                                         double *__restrict__ B, double *__restrict__ dBdT)
 {
    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
    const long long total = (long long)ncell * (G - 1);
    if (idx >= total) return;
-   const int c = (int)(idx / (G - 1)), g = (int)(idx % (G - 1));
-   const double t = T[c], lo = e_edge[g], hi = e_edge[g + 1];
-   if (blockIdx.y == 0) B[(size_t)c * G + g] = planck_group_integral<false>(t, lo, hi);
-   else dBdT[(size_t)c * G + g] = planck_group_integral<true>(t, lo, hi);
+   const int g = (int)(idx / ncell), c = (int)(idx - (long long)g * ncell);
+   double b, d;
+   planck_group_pair(T[c], e_edge[g], e_edge[g + 1], b, d);
+   B[idx] = b;
+   dBdT[idx] = d;
 }
 
 // Remainder of the grey totals into the last group (sequential ascending subtraction,
 // Planck.cpp:58-76: kept only if positive) and the keV -> jk unit change (correction.cpp:31-35).
-// One thread per cell.  keep_last: value the last group keeps when the remainder is not positive.
+// One thread per cell; group-major tables, so every step of the loop is a coalesced access.
 __global__ void planck_finalize_kernel(int G, int ncell, const double *__restrict__ T, double *__restrict__ B,
                                        double *__restrict__ dBdT)
 {
@@ -123,17 +139,19 @@ __global__ void planck_finalize_kernel(int G, int ncell, const double *__restric
    const double t = T[c];
    double bsum = rad_a_long() * C_LIGHT * (t * t) * (t * t);
    double dsum = 4.0 * rad_a_long() * C_LIGHT * (t * t) * t;
-   double *b = B + (size_t)c * G, *d = dBdT + (size_t)c * G;
+   double *b = B + c, *d = dBdT + c;
    for (int g = 0; g < G - 1; ++g)
    {
-      bsum -= b[g];
-      dsum -= d[g];
-      b[g] *= K_JPK;
-      d[g] *= K_JPK;
+      const size_t o = (size_t)g * ncell;
+      bsum -= b[o];
+      dsum -= d[o];
+      b[o] *= K_JPK;
+      d[o] *= K_JPK;
    }
    // last group: the remainder when positive, otherwise the stale previous value re-scaled (reference quirk)
-   b[G - 1] = K_JPK * (bsum > 0.0 ? bsum : b[G - 1]);
-   d[G - 1] = K_JPK * (dsum > 0.0 ? dsum : d[G - 1]);
+   const size_t o = (size_t)(G - 1) * ncell;
+   b[o] = K_JPK * (bsum > 0.0 ? bsum : b[o]);
+   d[o] = K_JPK * (dsum > 0.0 ? dsum : d[o]);
 }
 
 __device__ __forceinline__ double pf(double E, double T) // correction.cpp:11-22
@@ -264,8 +282,7 @@ int launch_planck(int G, int ncell, const double *d_e_edge, const double *d_T, d
    if (G > 1)
    {
       const long long total = (long long)ncell * (G - 1);
-      dim3 grid((unsigned)((total + 127) / 128), 2);
-      planck_integrals_kernel<<<grid, 128, 0, st>>>(G, ncell, d_e_edge, d_T, d_B, d_dBdT);
+      planck_integrals_kernel<<<(unsigned)((total + 127) / 128), 128, 0, st>>>(G, ncell, d_e_edge, d_T, d_B, d_dBdT);
       ++launches;
    }
    planck_finalize_kernel<<<(ncell + 127) / 128, 128, 0, st>>>(G, ncell, d_T, d_B, d_dBdT);

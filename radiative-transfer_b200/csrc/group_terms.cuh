@@ -20,7 +20,7 @@ struct GroupTermsArgs
 
 // 12-point Gauss-Legendre rule (computed on the host in long double like the reference, rounded to fp64)
 void upload_gauss_rule(const double *pt, const double *w);
-// B,dBdT: [ncell][G]; returns the number of kernels launched
+// B,dBdT: GROUP-MAJOR [G][ncell] (cell fastest; with ncell = 1 simply G long); returns the number of kernels launched
 int launch_planck(int G, int ncell, const double *d_e_edge, const double *d_T, double *d_B, double *d_dBdT, cudaStream_t st);
 int launch_group_terms(const GroupTermsArgs &a, cudaStream_t st);
 // correction.cpp:66-97; B in jk units (after launch_planck); all arrays G long

@@ -281,8 +281,8 @@ static int compute_var_tables(rt_solver *s, bool with_boundary)
    const rt_params &p = s->p;
    // the last group keeps "the previous value" when the grey remainder is not positive (Planck.cpp:73-76); the oracle
    // starts every evaluation from zeroed vectors
-   CK(cudaMemset2DAsync(s->d_B_c + (p.G - 1), (size_t)p.G * sizeof(double), 0, sizeof(double), p.N, s->st));
-   CK(cudaMemset2DAsync(s->d_dBdT_c + (p.G - 1), (size_t)p.G * sizeof(double), 0, sizeof(double), p.N, s->st));
+   CK(cudaMemsetAsync(s->d_B_c + (size_t)(p.G - 1) * p.N, 0, (size_t)p.N * sizeof(double), s->st));
+   CK(cudaMemsetAsync(s->d_dBdT_c + (size_t)(p.G - 1) * p.N, 0, (size_t)p.N * sizeof(double), s->st));
    s->tm.kernel_launches += launch_planck(p.G, p.N, s->d_e_edge, s->d_T_c, s->d_B_c, s->d_dBdT_c, s->st);
    CellTermsArgs ca;
    ca.G = p.G; ca.N = p.N; ca.G0 = p.group_begin; ca.groups = s->Gl;
@@ -295,6 +295,8 @@ static int compute_var_tables(rt_solver *s, bool with_boundary)
    s->tm.kernel_launches += 1;
    if (with_boundary)
    {
+      launch_boundary_state(ca, s->st);
+      s->tm.kernel_launches += 1;
       if (upload(s, s->d_psi_source, s->psi_source.data(), (size_t)p.M * p.G)) return 1; // the caller's sources, before the BC switch
       launch_boundary_table_var(p.M, p.G, p.bc_left, p.bc_right, p.use_mg_equilib, p.V, s->d_mu, s->d_edge_state[0], s->d_edge_state[1],
                                 s->d_edge_state[2], s->d_edge_state[3], s->d_psi_source, s->d_bdry, s->st);
@@ -465,8 +467,8 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       if (p->T_cell) std::copy(p->T_cell, p->T_cell + N, s->T_cell.begin());
       for (int c = 0; c < N; ++c)
          for (int g = 0; g < G; ++g)
-            s->kappa_cell[(size_t)g + (size_t)G * c] = p->kappa_cell ? p->kappa_cell[(size_t)g + (size_t)G * c] : p->kappa[g];
-      s->p.rho_cell = s->rho_cell.data(); s->p.T_cell = s->T_cell.data(); s->p.kappa_cell = s->kappa_cell.data();
+            s->kappa_cell[(size_t)g * N + c] = p->kappa_cell ? p->kappa_cell[(size_t)g + (size_t)G * c] : p->kappa[g]; // group-major on the device
+      s->p.rho_cell = s->rho_cell.data(); s->p.T_cell = s->T_cell.data(); s->p.kappa_cell = nullptr; // (the copy is transposed)
    }
    s->num_sms = prop.multiProcessorCount;
    s->Gl = p->group_count;
@@ -1247,13 +1249,13 @@ extern "C" int rt_planck_groups(int device, int G, const double *e_edge, int nce
    int ndev = 0;
    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail("rt_planck_groups: no CUDA device available");
    CK(cudaSetDevice(device));
-   double *d_e = nullptr, *d_T = nullptr, *d_B = nullptr, *d_dB = nullptr;
+   double *d_e = nullptr, *d_T = nullptr, *d_B = nullptr, *d_dB = nullptr, *d_tmp = nullptr;
    const size_t n = (size_t)ncell * G;
    int rc = 1;
    cudaEvent_t a = nullptr, b = nullptr;
    do
    {
-      if (dalloc(&d_e, G + 1) || dalloc(&d_T, ncell) || dalloc(&d_B, n) || dalloc(&d_dB, n)) break;
+      if (dalloc(&d_e, G + 1) || dalloc(&d_T, ncell) || dalloc(&d_B, n) || dalloc(&d_dB, n) || dalloc(&d_tmp, n)) break;
       if (cudaMemcpy(d_e, e_edge, (G + 1) * sizeof(double), cudaMemcpyHostToDevice) != cudaSuccess) { fail("rt_planck_groups: H2D failed"); break; }
       if (cudaMemcpy(d_T, T, ncell * sizeof(double), cudaMemcpyHostToDevice) != cudaSuccess) { fail("rt_planck_groups: H2D failed"); break; }
       cudaMemset(d_B, 0, n * sizeof(double));
@@ -1270,13 +1272,19 @@ extern "C" int rt_planck_groups(int device, int G, const double *e_edge, int nce
       float ms = 0.f;
       cudaEventElapsedTime(&ms, a, b);
       if (kernel_ms) *kernel_ms = ms;
-      if (cudaMemcpy(B, d_B, n * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) { fail("rt_planck_groups: D2H failed"); break; }
-      if (cudaMemcpy(dBdT, d_dB, n * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) { fail("rt_planck_groups: D2H failed"); break; }
+      // the device tables are group-major [G][ncell]; the caller gets [ncell][G] (layout conversion at the ABI edge only)
+      bool ok = true;
+      for (int k = 0; k < 2 && ok; ++k)
+      {
+         launch_transpose_gn(k ? d_dB : d_B, d_tmp, G, ncell, 0, ncell, 0);
+         ok = cudaMemcpy(k ? dBdT : B, d_tmp, n * sizeof(double), cudaMemcpyDeviceToHost) == cudaSuccess;
+      }
+      if (!ok) { fail("rt_planck_groups: D2H failed"); break; }
       rc = 0;
    } while (0);
    if (a) cudaEventDestroy(a);
    if (b) cudaEventDestroy(b);
-   cudaFree(d_e); cudaFree(d_T); cudaFree(d_B); cudaFree(d_dB);
+   cudaFree(d_e); cudaFree(d_T); cudaFree(d_B); cudaFree(d_dB); cudaFree(d_tmp);
    return rc;
 }
 

@@ -20,80 +20,92 @@ __device__ __forceinline__ double pf_cell(double E, double T) // correction.cpp:
    return K_JPK * (E * E * E) * inv_h3c2 / expm1(E / T);
 }
 
-// One block per cell: the reference's G-length Correction pipeline (correction.cpp:125-139 edge opacities, 162-249
-// edge stencils, 328-340 correction terms; same operations as group_terms_kernel) with the cell's rho, T, kappa.
+// The reference's G-length Correction pipeline (correction.cpp:125-139 edge opacities, 162-249 edge stencils, 328-340
+// correction terms; same operations as group_terms_kernel) with the cell's rho, T, kappa, for one (group, cell).  All
+// per-cell tables are group-major ([g][c], cell fastest): neighbouring lanes are neighbouring cells of one group.
+struct CellEval
+{
+   double sig, Bg, dEB, dsig, dkap;
+};
+
+__device__ __forceinline__ CellEval cell_terms_eval(const CellTermsArgs &a, int g, int c)
+{
+   const int G = a.G;
+   const size_t N = (size_t)a.N;
+   const double *e = a.e_edge;
+   const double T = a.T_cell[c], rho = a.rho_cell[c];
+   const double kg = a.kappa_cell[(size_t)g * N + c];
+   // opacity at the lower / upper edge of the group (linear interpolation between the group centres)
+   auto edge_opacity = [&](int ge, double k_below, double k_above) {
+      const double ea = 0.5 * (e[ge] + e[ge + 1]), eam = 0.5 * (e[ge - 1] + e[ge]);
+      const double wl = (ea - e[ge]) / (ea - eam), wr = (e[ge] - eam) / (ea - eam);
+      return k_below * wl + k_above * wr;
+   };
+   const double ke_lo = (g == 0) ? kg : edge_opacity(g, a.kappa_cell[(size_t)(g - 1) * N + c], kg);
+   const double ke_hi = (g == G - 1) ? kg : edge_opacity(g + 1, kg, a.kappa_cell[(size_t)(g + 1) * N + c]);
+   const double epf_lo = (g == 0) ? 0.0 : e[g] * pf_cell(e[g], T);
+   const double epf_hi = (g < G - 1 || g == 0) ? e[g + 1] * pf_cell(e[g + 1], T) : 0.0;
+   const double de = e[g + 1] - e[g];
+   CellEval r;
+   if (g == 0)
+   {
+      r.dEB = epf_hi;
+      r.dsig = ke_hi * e[1] / de;
+      r.dkap = ke_hi * epf_hi;
+   }
+   else if (g < G - 1)
+   {
+      r.dEB = epf_hi - epf_lo;
+      r.dsig = (ke_hi * e[g + 1] - ke_lo * e[g]) / de;
+      r.dkap = ke_hi * epf_hi - ke_lo * epf_lo;
+   }
+   else
+   {
+      r.dEB = -epf_lo;
+      r.dsig = 0.0; // set below
+      r.dkap = -ke_lo * epf_lo;
+   }
+   if (g == G - 1) r.dsig = -ke_hi * e[G] / de; // for G == 1 this overwrites entry 0, like the reference
+   r.sig = rho * kg;
+   r.Bg = a.B_cell[(size_t)g * N + c];
+   return r;
+}
+
+// one thread per (owned group, cell), cell fastest
 __global__ void cell_terms_kernel(CellTermsArgs a)
 {
-   extern __shared__ double s_edge[]; // [0, G]: kappa_edge ; [G+1, 2G+1]: E*pf(E,T) at the edges
-   const int G = a.G, c = blockIdx.x, tid = threadIdx.x, nt = blockDim.x;
-   double *kappa_edge = s_edge, *epf = s_edge + (G + 1);
-   const double *kap = a.kappa_cell + (size_t)G * c, *B = a.B_cell + (size_t)G * c;
-   const double T = a.T_cell[c], rho = a.rho_cell[c];
-   for (int g = tid; g <= G; g += nt)
-   {
-      double ke;
-      if (g == 0) ke = kap[0];
-      else if (g == G) ke = kap[G - 1];
-      else
-      {
-         const double ea = 0.5 * (a.e_edge[g] + a.e_edge[g + 1]), eam = 0.5 * (a.e_edge[g - 1] + a.e_edge[g]);
-         const double wl = (ea - a.e_edge[g]) / (ea - eam), wr = (a.e_edge[g] - eam) / (ea - eam);
-         ke = kap[g - 1] * wl + kap[g] * wr;
-      }
-      kappa_edge[g] = ke;
-      epf[g] = (g == 0) ? 0.0 : a.e_edge[g] * pf_cell(a.e_edge[g], T);
-   }
-   __syncthreads();
-   for (int g = tid; g < G; g += nt)
-   {
-      const double de = a.e_edge[g + 1] - a.e_edge[g];
-      double dEB, dsig, dkap;
-      if (g == 0)
-      {
-         dEB = epf[1];
-         dsig = kappa_edge[1] * a.e_edge[1] / de;
-         dkap = kappa_edge[1] * epf[1];
-      }
-      else if (g < G - 1)
-      {
-         dEB = epf[g + 1] - epf[g];
-         dsig = (kappa_edge[g + 1] * a.e_edge[g + 1] - kappa_edge[g] * a.e_edge[g]) / de;
-         dkap = kappa_edge[g + 1] * epf[g + 1] - kappa_edge[g] * epf[g];
-      }
-      else
-      {
-         dEB = -epf[G - 1];
-         dsig = 0.0; // set below
-         dkap = -kappa_edge[G - 1] * epf[G - 1];
-      }
-      if (g == G - 1) dsig = -kappa_edge[G] * a.e_edge[G] / de;
-      const double sig = rho * kap[g], Bg = B[g];
-      if (c == 0) { a.B_left[g] = Bg; a.dEB_left[g] = dEB; }
-      if (c == a.N - 1) { a.B_right[g] = Bg; a.dEB_right[g] = dEB; }
-      const int gl = g - a.G0;
-      if (gl >= 0 && gl < a.groups)
-      {
-         const size_t o = (size_t)gl * a.N + c;
-         a.sigma[o] = sig;
-         a.srcB[o] = sig * Bg;
-         a.cor1[o] = dsig;
-         a.cor2[o] = 3.0 * sig * Bg - dkap;
-         a.cor3[o] = dsig * (4.0 * Bg - dEB);
-         if (a.sdB) a.sdB[o] = sig * a.dBdT_cell[(size_t)G * c + g];
-      }
-   }
+   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+   if (idx >= (long long)a.groups * a.N) return;
+   const int gl = (int)(idx / a.N), c = (int)(idx - (long long)gl * a.N), g = a.G0 + gl;
+   const CellEval r = cell_terms_eval(a, g, c);
+   a.sigma[idx] = r.sig;
+   a.srcB[idx] = r.sig * r.Bg;
+   a.cor1[idx] = r.dsig;
+   a.cor2[idx] = 3.0 * r.sig * r.Bg - r.dkap;
+   a.cor3[idx] = r.dsig * (4.0 * r.Bg - r.dEB);
+   if (a.sdB) a.sdB[idx] = r.sig * a.dBdT_cell[(size_t)g * a.N + c];
+}
+
+// material state of the two boundary cells for ALL groups (the equilibrium boundary sources need them)
+__global__ void boundary_state_kernel(CellTermsArgs a)
+{
+   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+   if (idx >= 2 * a.G) return;
+   const int g = idx >> 1, right = idx & 1;
+   const CellEval r = cell_terms_eval(a, g, right ? a.N - 1 : 0);
+   if (right) { a.B_right[g] = r.Bg; a.dEB_right[g] = r.dEB; }
+   else { a.B_left[g] = r.Bg; a.dEB_left[g] = r.dEB; }
 }
 
 void launch_cell_terms(const CellTermsArgs &a, cudaStream_t st)
 {
-   const size_t smem = (size_t)2 * (a.G + 1) * sizeof(double);
-   static size_t granted = 48 * 1024;
-   if (smem > granted)
-   {
-      cudaFuncSetAttribute(cell_terms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      granted = smem;
-   }
-   cell_terms_kernel<<<a.N, 128, smem, st>>>(a);
+   const long long total = (long long)a.groups * a.N;
+   cell_terms_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(a);
+}
+
+void launch_boundary_state(const CellTermsArgs &a, cudaStream_t st)
+{
+   boundary_state_kernel<<<(2 * a.G + 127) / 128, 128, 0, st>>>(a);
 }
 
 __global__ void boundary_table_var_kernel(int M, int G, int bc_left, int bc_right, int use_mg_equilib, double V,
@@ -143,7 +155,7 @@ __global__ void init_state_var_kernel(double2 *__restrict__ buf, const double *_
    if (j < N)
    {
       const int cell = (i < (M >> 1)) ? (N - 1 - j) : j; // rows are stored in sweep order
-      v = B_cell[(size_t)(G0 + gl) + (size_t)G * cell];
+      v = B_cell[(size_t)(G0 + gl) * N + cell];
    }
    buf[idx] = make_double2(v, v);
 }

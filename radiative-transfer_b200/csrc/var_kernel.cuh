@@ -19,16 +19,17 @@ struct CellTermsArgs
 {
    int G, N, G0, groups;     // all groups enter the edge stencils; tables are written for the owned ones [G0, G0+groups)
    const double *e_edge;     // G+1
-   const double *kappa_cell; // g + G*c
+   const double *kappa_cell; // GROUP-MAJOR [g][c] (transposed from the caller's g + G*c at rt_create)
    const double *rho_cell;   // N
    const double *T_cell;     // N
-   const double *B_cell;     // g + G*c, jk units (planck kernels with ncell = N)
-   const double *dBdT_cell;  // g + G*c ; only read when sdB is wanted
+   const double *B_cell;     // [g][c], jk units (planck kernels with ncell = N)
+   const double *dBdT_cell;  // [g][c] ; only read when sdB is wanted
    double *sigma, *srcB, *cor1, *cor2, *cor3; // [gl][c]
    double *sdB;              // [gl][c] sigma_g dB_g/dT, or nullptr (material-temperature update only)
    double *B_left, *dEB_left, *B_right, *dEB_right; // G each: material state of cell 0 / cell N-1 (boundary sources)
 };
-void launch_cell_terms(const CellTermsArgs &a, cudaStream_t st);
+void launch_cell_terms(const CellTermsArgs &a, cudaStream_t st);      // tables of the owned groups
+void launch_boundary_state(const CellTermsArgs &a, cudaStream_t st);  // B_left .. dEB_right, all G groups
 
 // bdry(i,g) and, with use_mg_equilib, psi_source(i,g) from the boundary cells' state (mu>0: cell 0, mu<0: cell N-1)
 void launch_boundary_table_var(int M, int G, int bc_left, int bc_right, int use_mg_equilib, double V, const double *mu,
