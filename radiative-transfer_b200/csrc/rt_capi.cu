@@ -67,7 +67,11 @@ struct rt_solver
    bool var = false;
    std::vector<double> rho_cell, T_cell, kappa_cell;
    double *d_rho_c = nullptr, *d_T_c = nullptr, *d_kappa_c = nullptr, *d_B_c = nullptr, *d_dBdT_c = nullptr;
-   double *d_vt[5] = {nullptr, nullptr, nullptr, nullptr, nullptr}; // sigma, srcB, cor1, cor2, cor3
+   double *d_vt[5] = {nullptr, nullptr, nullptr, nullptr, nullptr}; // sigma, srcB, cor1, cor2, cor3: [sign][gl][vt_pitch] (var_kernel.cuh)
+   int vt_pitch = 0;               // N rounded up to 16
+   double *vt_fwd(int k) const { return d_vt[k] + (size_t)Gl * vt_pitch; } // the forward (mu > 0) copy
+   MatMaps mat_maps;
+   int var_threads = 64;           // CTA size of var_tile_kernel (x 4 cells per thread); RT_CUDA_VAR_THREADS=64|128, 0 = the chain-walk kernel
    double *d_edge_state[4] = {nullptr, nullptr, nullptr, nullptr};  // B_left, dEB_left, B_right, dEB_right (G each)
    // material-temperature update (extension; rt_params::cv > 0)
    bool tupdate = false, T_moved = false;
@@ -82,6 +86,7 @@ struct rt_solver
    size_t buf_elems = 0; // double2 elements per time-level buffer
    double2 *E[4] = {nullptr, nullptr, nullptr, nullptr};
    SweepMaps maps[3]; // per stage kind (tile shapes may differ): tensor maps of E[0..3]
+   SweepMaps maps_var; // tile shape of var_tile_kernel
    int i_ends = 0, i_prev = -1, i_half_neg = -1, i_half_pos = -1;
    int batch_start = 0, batch_groups = 0; // local group range of the batch currently on the device
    int stages_done = 0;
@@ -289,6 +294,7 @@ static int compute_var_tables(rt_solver *s, bool with_boundary)
    ca.e_edge = s->d_e_edge; ca.kappa_cell = s->d_kappa_c; ca.rho_cell = s->d_rho_c; ca.T_cell = s->d_T_c; ca.B_cell = s->d_B_c;
    ca.dBdT_cell = s->d_dBdT_c;
    ca.sigma = s->d_vt[0]; ca.srcB = s->d_vt[1]; ca.cor1 = s->d_vt[2]; ca.cor2 = s->d_vt[3]; ca.cor3 = s->d_vt[4];
+   ca.pitch = s->vt_pitch;
    ca.sdB = s->d_sdB;
    ca.B_left = s->d_edge_state[0]; ca.dEB_left = s->d_edge_state[1]; ca.B_right = s->d_edge_state[2]; ca.dEB_right = s->d_edge_state[3];
    launch_cell_terms(ca, s->st);
@@ -551,11 +557,22 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
    {
       CKD(dalloc(&s->d_rho_c, N)); CKD(dalloc(&s->d_T_c, N)); CKD(dalloc(&s->d_kappa_c, (size_t)G * N));
       CKD(dalloc(&s->d_B_c, (size_t)G * N)); CKD(dalloc(&s->d_dBdT_c, (size_t)G * N));
-      for (int k = 0; k < 5; ++k) CKD(dalloc(&s->d_vt[k], (size_t)s->Gl * N));
+      s->vt_pitch = (N + 15) & ~15;
+      for (int k = 0; k < 5; ++k)
+      {
+         const size_t n = (size_t)2 * s->Gl * s->vt_pitch;
+         CKD(dalloc(&s->d_vt[k], n));
+         CKC(cudaMemsetAsync(s->d_vt[k], 0, n * sizeof(double), s->st)); // the padding is read by TMA boxes (and masked)
+      }
+      if (const char *ve = getenv("RT_CUDA_VAR_THREADS"))
+      {
+         const int t = atoi(ve);
+         if (t == 0 || var_tile_shape_supported(t)) s->var_threads = t;
+      }
       for (int k = 0; k < 4; ++k) CKD(dalloc(&s->d_edge_state[k], G));
       if (s->tupdate)
       {
-         CKD(dalloc(&s->d_sdB, (size_t)s->Gl * N)); CKD(dalloc(&s->d_T_prev, N)); CKD(dalloc(&s->d_xsums, (size_t)3 * N));
+         CKD(dalloc(&s->d_sdB, (size_t)s->Gl * s->vt_pitch)); CKD(dalloc(&s->d_T_prev, N)); CKD(dalloc(&s->d_xsums, (size_t)3 * N));
          CKD(dalloc(&s->d_xpart, (size_t)exchange_chunks(s->Gl) * 3 * N));
          for (int m = 0; m < M; ++m) s->wsum += s->wt[m];
       }
@@ -604,7 +621,11 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       CKD(pool_alloc(s, &s->E[k], s->buf_elems));
       for (int kind = 0; kind < 3; ++kind) CKC(make_tile_map(&s->maps[kind].m[k], s->E[k], gb * M, s->Np, s->tile_cells[kind]));
       CKC(make_tile_map(&s->maps_step.m[k], s->E[k], gb * M, s->Np, s->step_box_cells));
+      if (s->var && s->var_threads > 0) CKC(make_tile_map(&s->maps_var.m[k], s->E[k], gb * M, s->Np, s->var_threads * 4));
    }
+   if (s->var && s->var_threads > 0)
+      for (int k = 0; k < 5; ++k) // a table row as pitch/2 16-byte "cells": the same 128-byte-swizzled box as a time-level tile
+         CKC(make_tile_map(&s->mat_maps.m[k], s->d_vt[k], 2 * s->Gl, s->vt_pitch / 2, s->var_threads * 2));
    const size_t ntiles = (size_t)gb * M * s->max_tiles_per_row;
    CKD(dalloc(&s->d_tile_status, ntiles));
    CKC(cudaMemsetAsync(s->d_tile_status, 0, ntiles * sizeof(double2), s->st));
@@ -681,17 +702,39 @@ static int launch_stage(rt_solver *s, int kind, int i1n, int i1p, int i2, int ic
    int grid = 0;
    if (s->var)
    {
-      // cell-dependent material fields (extension): one CTA per chain, no tickets, no look-back state
-      VarSweepArgs v;
-      v.x1[0] = s->E[i1n]; v.x1[1] = s->E[i1p]; v.x2 = a.x2; v.xc = a.xc; v.out = s->E[out];
-      v.t.sigma = s->d_vt[0]; v.t.srcB = s->d_vt[1]; v.t.cor1 = s->d_vt[2]; v.t.cor2 = s->d_vt[3]; v.t.cor3 = s->d_vt[4];
-      v.mu = s->d_mu; v.bdry = s->d_bdry;
-      v.M = p.M; v.N = p.N; v.Np = s->Np; v.G0 = p.group_begin; v.rows = a.rows; v.reflective_left = a.reflective_left;
-      v.dx = p.dx; v.tau = (p.ts_method == 3) ? p.dt / 2. : p.dt; v.dt = p.dt; v.beta = p.V / C_LIGHT;
-      CK(launch_var_sweep(kind, corr, v, s->st, &grid));
+      // cell-dependent material fields (extension)
+      const double tau = (p.ts_method == 3) ? p.dt / 2. : p.dt;
+      if (s->var_threads > 0)
+      {
+         // var_tile_kernel.cu: the uniform sweep's machinery (tickets, TMA tiles, look-back) with per-cell constants
+         const int tile = s->var_threads * 4;
+         VarTileArgs va;
+         va.s = a;
+         va.s.tiles_per_row = (p.N + tile - 1) / tile;
+         va.s.tiles_per_chain = a.reflective_left ? 2 * va.s.tiles_per_row : va.s.tiles_per_row;
+         va.s.lookback_walk = 0;
+         va.mu = s->d_mu; va.bdry = s->d_bdry; va.G0 = p.group_begin; va.Gl = s->Gl;
+         va.dx = p.dx; va.tau = tau; va.dt = p.dt; va.beta = p.V / C_LIGHT;
+         CK(launch_var_tile(kind, corr, s->var_threads, s->maps_var, s->mat_maps, va, s->num_sms, s->st, &grid));
+         const unsigned long long total_tiles = (unsigned long long)va.s.n_chains * va.s.tiles_per_chain;
+         s->ticket_base += (total_tiles + s->ticket_batch - 1) / s->ticket_batch + (unsigned long long)grid;
+         s->last_block = s->var_threads;
+      }
+      else
+      {
+         // var_kernel.cu, the first version kept as a cross-check: one CTA per chain walks its tiles in sequence
+         VarSweepArgs v;
+         v.x1[0] = s->E[i1n]; v.x1[1] = s->E[i1p]; v.x2 = a.x2; v.xc = a.xc; v.out = s->E[out];
+         v.t.sigma = s->vt_fwd(0); v.t.srcB = s->vt_fwd(1); v.t.cor1 = s->vt_fwd(2); v.t.cor2 = s->vt_fwd(3); v.t.cor3 = s->vt_fwd(4);
+         v.t.pitch = s->vt_pitch;
+         v.mu = s->d_mu; v.bdry = s->d_bdry;
+         v.M = p.M; v.N = p.N; v.Np = s->Np; v.G0 = p.group_begin; v.rows = a.rows; v.reflective_left = a.reflective_left;
+         v.dx = p.dx; v.tau = tau; v.dt = p.dt; v.beta = p.V / C_LIGHT;
+         CK(launch_var_sweep(kind, corr, v, s->st, &grid));
+         s->last_block = 128;
+      }
       if (counted && event_end(s, ep)) return 1;
       s->last_grid = grid;
-      s->last_block = 128;
       s->tm.kernel_launches++;
       if (counted)
       {
@@ -856,8 +899,8 @@ static int temperature_update(rt_solver *s)
    if (event_begin(s, 5, &ep)) return 1;
    launch_moments(s->E[s->i_ends], s->d_mu, s->d_wt, p.M, p.N, s->Np, s->batch_groups, s->d_phi, nullptr, nullptr, s->st);
    ExchangeArgs x;
-   x.N = p.N; x.groups = s->Gl; x.W = s->wsum;
-   x.sigma = s->d_vt[0]; x.srcB = s->d_vt[1]; x.sdB = s->d_sdB; x.phi = s->d_phi;
+   x.N = p.N; x.groups = s->Gl; x.pitch = s->vt_pitch; x.W = s->wsum;
+   x.sigma = s->vt_fwd(0); x.srcB = s->vt_fwd(1); x.sdB = s->d_sdB; x.phi = s->d_phi;
    x.partial = s->d_xpart; x.sums = s->d_xsums;
    s->tm.kernel_launches += 1 + launch_exchange_sums(x, s->st);
    CK(cudaGetLastError());
@@ -1003,7 +1046,7 @@ static int finish_batch(rt_solver *s)
    launch_moments(s->E[s->i_ends], s->d_mu, s->d_wt, p.M, p.N, s->Np, s->batch_groups, s->d_phi + off, s->d_phip + off,
                   s->d_F + off, s->st);
    if (s->var)
-      launch_diagnostics_var(s->E[s->i_ends], s->d_phi + off, s->d_mu, s->d_wt, s->d_vt[0], s->d_T_c, s->d_de_ave, p.M, p.N, s->Np,
+      launch_diagnostics_var(s->E[s->i_ends], s->d_phi + off, s->d_mu, s->d_wt, s->vt_fwd(0), s->vt_pitch, s->d_T_c, s->d_de_ave, p.M, p.N, s->Np,
                              p.group_begin + s->batch_start, s->batch_groups, p.dx, s->d_balance + s->batch_start,
                              s->d_left + s->batch_start, s->d_right + s->batch_start, s->st);
    else

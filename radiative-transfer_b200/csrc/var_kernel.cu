@@ -78,12 +78,15 @@ __global__ void cell_terms_kernel(CellTermsArgs a)
    if (idx >= (long long)a.groups * a.N) return;
    const int gl = (int)(idx / a.N), c = (int)(idx - (long long)gl * a.N), g = a.G0 + gl;
    const CellEval r = cell_terms_eval(a, g, c);
-   a.sigma[idx] = r.sig;
-   a.srcB[idx] = r.sig * r.Bg;
-   a.cor1[idx] = r.dsig;
-   a.cor2[idx] = 3.0 * r.sig * r.Bg - r.dkap;
-   a.cor3[idx] = r.dsig * (4.0 * r.Bg - r.dEB);
-   if (a.sdB) a.sdB[idx] = r.sig * a.dBdT_cell[(size_t)g * a.N + c];
+   // both sweep-ordered copies (CellTables): sign 1 (mu > 0) at j = c, sign 0 (mu < 0) at j = N-1-c
+   const size_t fwd = ((size_t)a.groups + gl) * a.pitch + c, rev = (size_t)gl * a.pitch + (a.N - 1 - c);
+   const double srcB = r.sig * r.Bg, c2 = 3.0 * r.sig * r.Bg - r.dkap, c3 = r.dsig * (4.0 * r.Bg - r.dEB);
+   a.sigma[fwd] = r.sig; a.sigma[rev] = r.sig;
+   a.srcB[fwd] = srcB;   a.srcB[rev] = srcB;
+   a.cor1[fwd] = r.dsig; a.cor1[rev] = r.dsig;
+   a.cor2[fwd] = c2;     a.cor2[rev] = c2;
+   a.cor3[fwd] = c3;     a.cor3[rev] = c3;
+   if (a.sdB) a.sdB[(size_t)gl * a.pitch + c] = r.sig * a.dBdT_cell[(size_t)g * a.N + c];
 }
 
 // material state of the two boundary cells for ALL groups (the equilibrium boundary sources need them)
@@ -196,7 +199,7 @@ __global__ void __launch_bounds__(VT) var_sweep_kernel(const VarSweepArgs a)
       const double2 *x2 = a.x2 ? a.x2 + (size_t)row * a.Np : nullptr;
       const double2 *xc = a.xc ? a.xc + (size_t)row * a.Np : nullptr;
       double2 *out = a.out + (size_t)row * a.Np;
-      const size_t trow = (size_t)gl * N;
+      const size_t trow = (size_t)gl * a.t.pitch;
       // inflow of the row's first cell: boundary value, or (reflective left) the mirrored row's last outflow node;
       // all three inflow carries equal it there (solver.cpp:695-697) -> factor kbc, no upstream old-level terms
       double tile_in = kbc * ((seg == 0) ? a.bdry[(size_t)i + (size_t)M * g] : s_carry);
@@ -317,8 +320,8 @@ __global__ void exchange_partial_kernel(ExchangeArgs a)
    double A = 0.0, E = 0.0, D = 0.0;
    for (int gl = g0; gl < g1; ++gl)
    {
-      const size_t o = (size_t)gl * a.N + c;
-      A += a.sigma[o] * a.phi[o];
+      const size_t o = (size_t)gl * a.pitch + c;
+      A += a.sigma[o] * a.phi[(size_t)gl * a.N + c];
       E += a.W * a.srcB[o];
       D += a.W * a.sdB[o];
    }
@@ -383,7 +386,7 @@ __device__ __forceinline__ double block_sum_var(double v, double *red)
 
 // One block per local group: diagnostics_kernel (moments.cu) with sigma and T taken per cell
 __global__ void diagnostics_var_kernel(const double2 *__restrict__ ends, const double *__restrict__ phi, const double *__restrict__ mu,
-                                       const double *__restrict__ wt, const double *__restrict__ sigma_cell,
+                                       const double *__restrict__ wt, const double *__restrict__ sigma_cell, int pitch,
                                        const double *__restrict__ T_cell, const double *__restrict__ de_ave, int M, int N, int Np,
                                        int G0, double dx, double *__restrict__ balance, double *__restrict__ left_ends,
                                        double *__restrict__ right_ends)
@@ -392,7 +395,7 @@ __global__ void diagnostics_var_kernel(const double2 *__restrict__ ends, const d
    const int gl = blockIdx.x, g = G0 + gl, half_m = M >> 1;
    const double ac = RAD_A * C_LIGHT;
    double part = 0.0, emit = 0.0;
-   const double *prow = phi + (size_t)gl * N, *srow = sigma_cell + (size_t)gl * N;
+   const double *prow = phi + (size_t)gl * N, *srow = sigma_cell + (size_t)gl * pitch;
    for (int c = threadIdx.x; c < N; c += blockDim.x)
    {
       const double T = T_cell[c];
@@ -431,10 +434,10 @@ __global__ void diagnostics_var_kernel(const double2 *__restrict__ ends, const d
 }
 
 void launch_diagnostics_var(const double2 *ends, const double *phi, const double *mu, const double *wt, const double *sigma_cell,
-                            const double *T_cell, const double *de_ave, int M, int N, int Np, int G0, int groups, double dx,
+                            int pitch, const double *T_cell, const double *de_ave, int M, int N, int Np, int G0, int groups, double dx,
                             double *balance, double *left_ends, double *right_ends, cudaStream_t st)
 {
-   diagnostics_var_kernel<<<groups, 1024, 0, st>>>(ends, phi, mu, wt, sigma_cell, T_cell, de_ave, M, N, Np, G0, dx, balance,
+   diagnostics_var_kernel<<<groups, 1024, 0, st>>>(ends, phi, mu, wt, sigma_cell, pitch, T_cell, de_ave, M, N, Np, G0, dx, balance,
                                                   left_ends, right_ends);
 }
 } // namespace rtk

@@ -9,11 +9,34 @@
 
 namespace rtk
 {
-// Per-cell tables of the owned groups, row layout [gl][c] (c contiguous): what the steppers need of the material state.
+// Per-cell tables of the owned groups: what the steppers need of the material state.  Every table is kept TWICE, once per
+// sweep direction: entry (sign, gl, j) at (sign*groups + gl)*pitch + j with j the storage index ALONG THE SWEEP (sign 1,
+// mu > 0: j = cell ; sign 0, mu < 0: j = N-1-cell), pitch = N rounded up to 16 -- so every row reads its tile of a
+// table as one aligned TMA box in its own order (var_tile_kernel.cu).  The forward copy (sign 1) serves everything else.
 struct CellTables
 {
-   const double *sigma, *srcB, *cor1, *cor2, *cor3; // rho*kappa_g, rho*kappa_g*B_g, correction terms (correction.cpp:328-340)
+   const double *sigma, *srcB, *cor1, *cor2, *cor3; // FORWARD copies: rho*kappa_g, rho*kappa_g*B_g, correction terms (correction.cpp:328-340)
+   int pitch;
 };
+
+// tensor maps of the five tables (rows = 2*groups, SWIZZLE_128B boxes of one tile) for var_tile_kernel
+struct alignas(64) MatMaps
+{
+   CUtensorMap m[5];
+};
+
+struct VarTileArgs
+{
+   SweepArgs s;        // time levels, look-back state, tickets (s.coef unused)
+   const double *mu;   // M
+   const double *bdry; // i + M*g (global group)
+   int G0, Gl;         // first owned group, owned groups (= rows of one table copy)
+   double dx, tau, dt, beta;
+};
+bool var_tile_shape_supported(int threads);
+// persistent CTAs of `threads` x 4 cells; the caller advances its ticket base like after launch_sweep
+cudaError_t launch_var_tile(int kind, bool corr, int threads, const SweepMaps &maps, const MatMaps &mats, const VarTileArgs &va,
+                            int num_sms, cudaStream_t st, int *grid_out);
 
 struct CellTermsArgs
 {
@@ -24,8 +47,9 @@ struct CellTermsArgs
    const double *T_cell;     // N
    const double *B_cell;     // [g][c], jk units (planck kernels with ncell = N)
    const double *dBdT_cell;  // [g][c] ; only read when sdB is wanted
-   double *sigma, *srcB, *cor1, *cor2, *cor3; // [gl][c]
-   double *sdB;              // [gl][c] sigma_g dB_g/dT, or nullptr (material-temperature update only)
+   double *sigma, *srcB, *cor1, *cor2, *cor3; // both sweep-ordered copies, see CellTables (base of the sign-0 copy)
+   int pitch;                // N rounded up to 16
+   double *sdB;              // [gl][pitch] forward only: sigma_g dB_g/dT, or nullptr (material-temperature update only)
    double *B_left, *dEB_left, *B_right, *dEB_right; // G each: material state of cell 0 / cell N-1 (boundary sources)
 };
 void launch_cell_terms(const CellTermsArgs &a, cudaStream_t st);      // tables of the owned groups
@@ -58,7 +82,7 @@ cudaError_t launch_var_sweep(int kind, bool corr, const VarSweepArgs &a, cudaStr
 // definition is oracle/rt_oracle.cpp rto_temperature_update.
 struct ExchangeArgs
 {
-   int N, groups;            // owned groups; tables and phi are [gl][c]
+   int N, groups, pitch;     // owned groups; phi is [gl][N], the tables [gl][pitch] (forward copies)
    double W;                 // sum of the quadrature weights
    const double *sigma, *srcB, *sdB, *phi;
    double *partial;          // [chunk][3][N] scratch, chunk = EXCHANGE_GROUPS_PER_CHUNK groups
@@ -74,6 +98,6 @@ void launch_temperature_update(int N, bool bdf2, double dt, double cv, const dou
 
 // balance (solver.cpp:240-284) with per-cell sigma and T, group-end spectra (826-850)
 void launch_diagnostics_var(const double2 *ends, const double *phi, const double *mu, const double *wt, const double *sigma_cell,
-                            const double *T_cell, const double *de_ave, int M, int N, int Np, int G0, int groups, double dx,
+                            int pitch, const double *T_cell, const double *de_ave, int M, int N, int Np, int G0, int groups, double dx,
                             double *balance, double *left_ends, double *right_ends, cudaStream_t st);
 } // namespace rtk
