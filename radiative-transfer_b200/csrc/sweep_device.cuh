@@ -186,6 +186,7 @@ struct TileDesc
    long long row_off;    // element offset of the tile's first cell in a time-level buffer
    long long status_idx; // index of the tile's look-back word
    int row, p, sgn, tile_start, valid, junction;
+   int gl, dir;          // local group and direction of the row (row = gl*M + dir)
 };
 
 // ticket -> (tile position p, chain) -> (row, tile in row); p-major so that all chains advance together.
@@ -234,6 +235,8 @@ __device__ __forceinline__ TileDesc decode_ticket(const Args &a, TicketCursor &c
    ti.valid = min(tile_cells, a.N - ti.tile_start);
    ti.row_off = (long long)ti.row * a.Np + ti.tile_start;
    ti.status_idx = (long long)cu.chain * a.tiles_per_chain + cu.p;
+   ti.gl = cu.gl;
+   ti.dir = ti.row - cu.gl * a.M;
    return ti;
 }
 

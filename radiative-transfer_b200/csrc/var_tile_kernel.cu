@@ -96,8 +96,23 @@ struct RowConst
    }
 };
 
+// dynamic shared memory of one CTA: 3 X1/result slots, 2 each for X2 / XC, ONE slot of material tables (+ alignment slack)
 template <int KIND, bool CORR, int THREADS, int CPT>
-__global__ void __launch_bounds__(THREADS) var_tile_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ MatMaps mats,
+constexpr int var_smem_bytes()
+{
+   const int narr = 1 + (KIND != KIND_BE ? 1 : 0) + ((KIND == KIND_BDF && CORR) ? 1 : 0);
+   return (3 + 2 * (narr - 1)) * THREADS * CPT * 16 + (CORR ? 5 : 2) * THREADS * CPT * 8 + 1024;
+}
+// resident CTAs per SM the register allocation aims for: what shared memory allows, at most 16 warps
+template <int KIND, bool CORR, int THREADS, int CPT>
+constexpr int var_min_blocks()
+{
+   const int by_smem = (227 * 1024) / (var_smem_bytes<KIND, CORR, THREADS, CPT>() + 1024), by_warps = 512 / THREADS;
+   return by_smem < by_warps ? by_smem : by_warps;
+}
+
+template <int KIND, bool CORR, int THREADS, int CPT>
+__global__ void __launch_bounds__(THREADS, var_min_blocks<KIND, CORR, THREADS, CPT>()) var_tile_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ MatMaps mats,
                                                            const VarTileArgs va)
 {
    using TS = TileShape<THREADS, CPT>;
@@ -117,7 +132,9 @@ __global__ void __launch_bounds__(THREADS) var_tile_kernel(const __grid_constant
    auto x1_slot = [&](int r) { return tiles + r * TILE_BYTES; };
    auto x2_slot = [&](int b) { return tiles + (RING + b) * TILE_BYTES; };
    auto xc_slot = [&](int b) { return tiles + (RING + (NEED_X2 ? 2 : 0) + b) * TILE_BYTES; };
-   auto mat_slot = [&](int b) { return tiles + (RING + 2 * (NARR - 1)) * TILE_BYTES + b * NT * MAT_BYTES; };
+   // ONE slot for the material tables: they are consumed by pass 1, so the next tile's boxes are issued right after the
+   // barrier that ends pass 1 (half a tile of lead time) -- a second slot would cost resident CTAs
+   unsigned char *const mat = tiles + (RING + 2 * (NARR - 1)) * TILE_BYTES;
 
    __shared__ __align__(16) double2 s_halo[2][2]; // [buffer][0: X1, 1: X2]: the cell upstream of the tile
    __shared__ __align__(8) unsigned long long s_full[2];
@@ -140,14 +157,18 @@ __global__ void __launch_bounds__(THREADS) var_tile_kernel(const __grid_constant
       tma_load_3d(x1_slot(r), &maps.m[a.ix1[ti.sgn]], 0, chunk0, ti.row, &s_full[b]);
       if (NEED_X2) tma_load_3d(x2_slot(b), &maps.m[a.ix2], 0, chunk0, ti.row, &s_full[b]);
       if (NEED_XC) tma_load_3d(xc_slot(b), &maps.m[a.ixc], 0, chunk0, ti.row, &s_full[b]);
-      const int trow = ti.sgn * va.Gl + ti.row / a.M; // the table copy in this row's sweep order
-#pragma unroll
-      for (int t = 0; t < NT; ++t) tma_load_3d(mat_slot(b) + t * MAT_BYTES, &mats.m[t], 0, ti.tile_start >> 4, trow, &s_full[b]);
       if (halo)
       {
          bulk_load(&s_halo[b][1], a.x2 + ti.row_off - 1, 16u, &s_full[b]);
          if (KIND == KIND_BDF) bulk_load(&s_halo[b][0], a.x1[ti.sgn] + ti.row_off - 1, 16u, &s_full[b]);
       }
+   };
+
+   // thread 0 only: the tile's boxes of the material tables (counted in the expect_tx of issue_loads)
+   auto issue_mat = [&](const TileDesc &ti, int b) {
+      const int trow = ti.sgn * va.Gl + ti.gl; // the table copy in this row's sweep order
+#pragma unroll
+      for (int t = 0; t < NT; ++t) tma_load_3d(mat + t * MAT_BYTES, &mats.m[t], 0, ti.tile_start >> 4, trow, &s_full[b]);
    };
 
    TicketQueue tq;
@@ -166,6 +187,7 @@ __global__ void __launch_bounds__(THREADS) var_tile_kernel(const __grid_constant
       {
          s_desc[0] = decode_ticket(a, cursor, t0, TILE);
          issue_loads(s_desc[0], 0, 0);
+         issue_mat(s_desc[0], 0);
       }
       if (t1 < total_tiles) s_desc[1] = decode_ticket(a, cursor, t1, TILE);
       ahead = tq.take(a, total_tiles);
@@ -197,9 +219,9 @@ __global__ void __launch_bounds__(THREADS) var_tile_kernel(const __grid_constant
       unsigned char *const s1 = x1_slot(ring);
       unsigned char *const s2 = x2_slot(buf);
       unsigned char *const sc = xc_slot(buf);
-      const unsigned char *const sm = mat_slot(buf);
+      const unsigned char *const sm = mat;
       double2 *status = a.tile_status + ti.status_idx;
-      const int i_dir = ti.row % a.M;
+      const int i_dir = ti.dir;
       const double mu = va.mu[i_dir];
 
       // early look-back probe / the chain head's boundary inflow
@@ -208,7 +230,7 @@ __global__ void __launch_bounds__(THREADS) var_tile_kernel(const __grid_constant
       if (tid == 0)
       {
          if (ti.p > 0) early = ld_status(status - 1);
-         else inflow0 = kbc * va.bdry[(size_t)i_dir + (size_t)a.M * (va.G0 + ti.row / a.M)];
+         else inflow0 = kbc * va.bdry[(size_t)i_dir + (size_t)a.M * (va.G0 + ti.gl)];
       }
 
       mbar_wait(&s_full[buf], (phase >> buf) & 1u);
@@ -293,7 +315,8 @@ __global__ void __launch_bounds__(THREADS) var_tile_kernel(const __grid_constant
       double Ae = __shfl_up_sync(0xffffffffu, Ai, 1), We = __shfl_up_sync(0xffffffffu, Wi, 1);
       if (lane == 0) { Ae = 1.0; We = 0.0; }
       if (lane == 31) { s_wA[warp] = Ai; s_wW[warp] = Wi; }
-      __syncthreads(); // (C)
+      __syncthreads(); // (C) warp totals visible; nobody reads the material tables of this tile any more
+      if (tid == 0 && nxt < total_tiles) issue_mat(s_desc[slot_next], buf ^ 1);
       double Ap = 1.0, Wp = 0.0; // composition of the warps before this one
       for (int w2 = 0; w2 < warp; ++w2)
       {
@@ -364,20 +387,12 @@ __global__ void __launch_bounds__(THREADS) var_tile_kernel(const __grid_constant
 
 // ------------------------------------------------------------------------------------------ host side
 template <int KIND, bool CORR, int THREADS, int CPT>
-static size_t var_smem_bytes()
-{
-   const int narr = 1 + (KIND != KIND_BE ? 1 : 0) + ((KIND == KIND_BDF && CORR) ? 1 : 0);
-   const int nt = CORR ? 5 : 2;
-   return (size_t)(3 + 2 * (narr - 1)) * TileShape<THREADS, CPT>::TILE_BYTES + (size_t)2 * nt * TileShape<THREADS, CPT>::TILE * 8 + 1024;
-}
-
-template <int KIND, bool CORR, int THREADS, int CPT>
 static cudaError_t var_launch_one(const SweepMaps &maps, const MatMaps &mats, const VarTileArgs &va, int num_sms, cudaStream_t st,
                                   int *grid_out)
 {
    static int ctas_per_sm = -1;
    auto k = var_tile_kernel<KIND, CORR, THREADS, CPT>;
-   const size_t sm = var_smem_bytes<KIND, CORR, THREADS, CPT>();
+   const size_t sm = (size_t)var_smem_bytes<KIND, CORR, THREADS, CPT>();
    if (ctas_per_sm < 0)
    {
       cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
