@@ -151,7 +151,9 @@ int rt_validate(rt_solver *s, double *sums3, int *ok);
  * rt_set_allreduce: `fn(buf, count, stream, user)` must sum the `count` fp64 values at DEVICE pointer `buf` element-wise
  * over all handles that share the problem (in place, result on every rank) and order that work after what `stream`
  * (a cudaStream_t) holds and before what is submitted to it next; non-zero return aborts the solve.  NULL = the handle
- * owns every group.  The library itself does not link NCCL: the Python host passes torch.distributed's all_reduce, a
+ * owns every group.  A group shard calls it TWICE per time step: 3*N values (the group sums A, E, D) before the update and
+ * 2*N values after it (per-cell sums of the shard's Planck integrals at T': the last group is the grey remainder over all
+ * groups, Planck.cpp:58-76, so the integrals are sharded like the sweeps and only these sums travel).  The library itself does not link NCCL: the Python host passes torch.distributed's all_reduce, a
  * C++ host its ncclAllReduce. */
 typedef int (*rt_allreduce_fn)(void *device_buf, size_t count, void *cuda_stream, void *user);
 int rt_set_allreduce(rt_solver *s, rt_allreduce_fn fn, void *user);

@@ -115,17 +115,51 @@ __device__ void planck_group_pair(double T, double E_min, double E_max, double &
 // the same group at neighbouring temperatures, so they take the same branch (Gauss / series / split) and run the same
 // number of series terms -- with the group fastest a warp executed ~10 of 32 lanes per instruction (ncu) -- and the
 // stores are coalesced.  g < G-1 only; the last group is the remainder (planck_finalize_kernel).
-__global__ void planck_integrals_kernel(int G, int ncell, const double *__restrict__ e_edge, const double *__restrict__ T,
-                                        double *__restrict__ B, double *__restrict__ dBdT)
+__global__ void planck_integrals_kernel(int G, int ncell, int g0, int ng, const double *__restrict__ e_edge,
+                                        const double *__restrict__ T, double *__restrict__ B, double *__restrict__ dBdT)
 {
    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-   const long long total = (long long)ncell * (G - 1);
-   if (idx >= total) return;
-   const int g = (int)(idx / ncell), c = (int)(idx - (long long)g * ncell);
+   if (idx >= (long long)ncell * ng) return;
+   const int g = g0 + (int)(idx / ncell), c = (int)(idx % ncell);
    double b, d;
    planck_group_pair(T[c], e_edge[g], e_edge[g + 1], b, d);
-   B[idx] = b;
-   dBdT[idx] = d;
+   B[(size_t)g * ncell + c] = b;
+   dBdT[(size_t)g * ncell + c] = d;
+}
+
+// ---- group-sharded evaluation (material-temperature update on a group shard, rt_capi.cu): a rank integrates only the
+// groups it owns; the last group's remainder needs the sum over ALL other groups, so every rank forms its partial sums
+// per cell (ascending over its groups), the caller all-reduces them, and the owner of the last group takes the remainder.
+// The sum is then (total - sum_g B_g) instead of the reference's sequential subtraction: same value to rounding.
+__global__ void planck_partial_kernel(int ncell, int g0, int ng, double *__restrict__ B, double *__restrict__ dBdT,
+                                      double *__restrict__ part)
+{
+   const int c = blockIdx.x * blockDim.x + threadIdx.x;
+   if (c >= ncell) return;
+   double bs = 0.0, ds = 0.0;
+   for (int g = g0; g < g0 + ng; ++g)
+   {
+      const size_t o = (size_t)g * ncell + c;
+      bs += B[o];
+      ds += dBdT[o];
+      B[o] *= K_JPK;
+      dBdT[o] *= K_JPK;
+   }
+   part[c] = bs;
+   part[ncell + c] = ds;
+}
+
+__global__ void planck_last_kernel(int G, int ncell, const double *__restrict__ T, const double *__restrict__ part,
+                                   double *__restrict__ B, double *__restrict__ dBdT)
+{
+   const int c = blockIdx.x * blockDim.x + threadIdx.x;
+   if (c >= ncell) return;
+   const double t = T[c];
+   const double bsum = rad_a_long() * C_LIGHT * (t * t) * (t * t) - part[c];
+   const double dsum = 4.0 * rad_a_long() * C_LIGHT * (t * t) * t - part[ncell + c];
+   const size_t o = (size_t)(G - 1) * ncell + c;
+   B[o] = K_JPK * (bsum > 0.0 ? bsum : 0.0);
+   dBdT[o] = K_JPK * (dsum > 0.0 ? dsum : 0.0);
 }
 
 // Remainder of the grey totals into the last group (sequential ascending subtraction,
@@ -282,11 +316,30 @@ int launch_planck(int G, int ncell, const double *d_e_edge, const double *d_T, d
    if (G > 1)
    {
       const long long total = (long long)ncell * (G - 1);
-      planck_integrals_kernel<<<(unsigned)((total + 127) / 128), 128, 0, st>>>(G, ncell, d_e_edge, d_T, d_B, d_dBdT);
+      planck_integrals_kernel<<<(unsigned)((total + 127) / 128), 128, 0, st>>>(G, ncell, 0, G - 1, d_e_edge, d_T, d_B, d_dBdT);
       ++launches;
    }
    planck_finalize_kernel<<<(ncell + 127) / 128, 128, 0, st>>>(G, ncell, d_T, d_B, d_dBdT);
    return launches + 1;
+}
+
+int launch_planck_shard_begin(int G, int ncell, int g0, int ng, const double *d_e_edge, const double *d_T, double *d_B,
+                              double *d_dBdT, double *d_part, cudaStream_t st)
+{
+   const int n = min(g0 + ng, G - 1) - g0; // owned groups other than the last one
+   if (n > 0)
+   {
+      const long long total = (long long)ncell * n;
+      planck_integrals_kernel<<<(unsigned)((total + 127) / 128), 128, 0, st>>>(G, ncell, g0, n, d_e_edge, d_T, d_B, d_dBdT);
+   }
+   planck_partial_kernel<<<(ncell + 127) / 128, 128, 0, st>>>(ncell, g0, n > 0 ? n : 0, d_B, d_dBdT, d_part);
+   return n > 0 ? 2 : 1;
+}
+
+int launch_planck_shard_finish(int G, int ncell, const double *d_T, const double *d_part, double *d_B, double *d_dBdT, cudaStream_t st)
+{
+   planck_last_kernel<<<(ncell + 127) / 128, 128, 0, st>>>(G, ncell, d_T, d_part, d_B, d_dBdT);
+   return 1;
 }
 
 int launch_group_terms(const GroupTermsArgs &a, cudaStream_t st)

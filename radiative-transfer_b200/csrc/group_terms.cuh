@@ -22,6 +22,12 @@ struct GroupTermsArgs
 void upload_gauss_rule(const double *pt, const double *w);
 // B,dBdT: GROUP-MAJOR [G][ncell] (cell fastest; with ncell = 1 simply G long); returns the number of kernels launched
 int launch_planck(int G, int ncell, const double *d_e_edge, const double *d_T, double *d_B, double *d_dBdT, cudaStream_t st);
+// group-sharded evaluation for the owned groups [g0, g0+ng): integrals + per-cell partial sums of the raw (keV) values into
+// d_part[2*ncell] (B sums, then dB/dT sums); after the caller has summed d_part over the ranks, the owner of group G-1
+// takes the grey remainder with launch_planck_shard_finish.  Same tables ([G][ncell]), only owned rows are touched.
+int launch_planck_shard_begin(int G, int ncell, int g0, int ng, const double *d_e_edge, const double *d_T, double *d_B,
+                              double *d_dBdT, double *d_part, cudaStream_t st);
+int launch_planck_shard_finish(int G, int ncell, const double *d_T, const double *d_part, double *d_B, double *d_dBdT, cudaStream_t st);
 int launch_group_terms(const GroupTermsArgs &a, cudaStream_t st);
 // correction.cpp:66-97; B in jk units (after launch_planck); all arrays G long
 int launch_multigroup_opacities(int G, double T, double kappa_grey, const double *d_e_edge, const double *d_B, double *d_kappa,

@@ -78,6 +78,7 @@ struct rt_solver
    double wsum = 0.0;              // sum of the quadrature weights, ascending
    double *d_sdB = nullptr;        // [gl][c] sigma_g dB_g/dT
    double *d_T_prev = nullptr, *d_xsums = nullptr, *d_xpart = nullptr; // N ; 3N (A, E, D) ; chunks*3N
+   double *d_ppart = nullptr;      // 2N: per-cell partial sums of the raw Planck integrals (sharded evaluation)
    long long tsteps_done = 0;      // temperature updates since the state was initialised
    rt_allreduce_fn allreduce = nullptr;
    void *allreduce_user = nullptr;
@@ -281,14 +282,29 @@ static int event_end(rt_solver *s, EventPair *ep)
 // extension: Planck integrals per (cell, group) and the Correction pipeline per cell at the current T(c); with
 // `with_boundary` also the boundary sources from the boundary cells (they overwrite the uniform boundary table and are
 // built ONCE: a temperature update leaves the incoming boundary intensities alone, like the oracle)
-static int compute_var_tables(rt_solver *s, bool with_boundary)
+static int compute_var_tables(rt_solver *s, bool with_boundary, bool sharded = false)
 {
    const rt_params &p = s->p;
+   if (sharded)
+   {
+      // a group shard inside a temperature-coupled solve: integrate the owned groups only; the last group's grey
+      // remainder needs the sum over all groups -> second (2N) all-reduce of the step
+      s->tm.kernel_launches += launch_planck_shard_begin(p.G, p.N, p.group_begin, s->Gl, s->d_e_edge, s->d_T_c, s->d_B_c, s->d_dBdT_c,
+                                                         s->d_ppart, s->st);
+      CK(cudaGetLastError());
+      const int rc = s->allreduce(s->d_ppart, (size_t)2 * p.N, (void *)s->st, s->allreduce_user);
+      if (rc) return fail("rt: the all-reduce hook failed with code %d in the Planck remainder after stage %d", rc, s->stages_done);
+      if (p.group_begin + s->Gl == p.G)
+         s->tm.kernel_launches += launch_planck_shard_finish(p.G, p.N, s->d_T_c, s->d_ppart, s->d_B_c, s->d_dBdT_c, s->st);
+   }
+   else
+   {
    // the last group keeps "the previous value" when the grey remainder is not positive (Planck.cpp:73-76); the oracle
    // starts every evaluation from zeroed vectors
    CK(cudaMemsetAsync(s->d_B_c + (size_t)(p.G - 1) * p.N, 0, (size_t)p.N * sizeof(double), s->st));
    CK(cudaMemsetAsync(s->d_dBdT_c + (size_t)(p.G - 1) * p.N, 0, (size_t)p.N * sizeof(double), s->st));
    s->tm.kernel_launches += launch_planck(p.G, p.N, s->d_e_edge, s->d_T_c, s->d_B_c, s->d_dBdT_c, s->st);
+   }
    CellTermsArgs ca;
    ca.G = p.G; ca.N = p.N; ca.G0 = p.group_begin; ca.groups = s->Gl;
    ca.e_edge = s->d_e_edge; ca.kappa_cell = s->d_kappa_c; ca.rho_cell = s->d_rho_c; ca.T_cell = s->d_T_c; ca.B_cell = s->d_B_c;
@@ -396,7 +412,7 @@ extern "C" int rt_destroy(rt_solver *s)
    for (double *t : tabs) if (t) cudaFree(t);
    double *vtabs[] = {s->d_rho_c, s->d_T_c, s->d_kappa_c, s->d_B_c, s->d_dBdT_c, s->d_vt[0], s->d_vt[1], s->d_vt[2], s->d_vt[3],
                       s->d_vt[4], s->d_edge_state[0], s->d_edge_state[1], s->d_edge_state[2], s->d_edge_state[3],
-                      s->d_sdB, s->d_T_prev, s->d_xsums, s->d_xpart};
+                      s->d_sdB, s->d_T_prev, s->d_xsums, s->d_xpart, s->d_ppart};
    for (double *t : vtabs) if (t) cudaFree(t);
    for (int k = 0; k < 4; ++k) if (s->E[k]) cudaFreeAsync(s->E[k], s->st);
    if (s->st) cudaStreamSynchronize(s->st);
@@ -572,7 +588,7 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       for (int k = 0; k < 4; ++k) CKD(dalloc(&s->d_edge_state[k], G));
       if (s->tupdate)
       {
-         CKD(dalloc(&s->d_sdB, (size_t)s->Gl * s->vt_pitch)); CKD(dalloc(&s->d_T_prev, N)); CKD(dalloc(&s->d_xsums, (size_t)3 * N));
+         CKD(dalloc(&s->d_sdB, (size_t)s->Gl * s->vt_pitch)); CKD(dalloc(&s->d_T_prev, N)); CKD(dalloc(&s->d_xsums, (size_t)3 * N)); CKD(dalloc(&s->d_ppart, (size_t)2 * N));
          CKD(dalloc(&s->d_xpart, (size_t)exchange_chunks(s->Gl) * 3 * N));
          for (int m = 0; m < M; ++m) s->wsum += s->wt[m];
       }
@@ -913,7 +929,8 @@ static int temperature_update(rt_solver *s)
    s->tm.kernel_launches += 1;
    if (event_end(s, ep)) return 1;
    if (event_begin(s, 6, &ep)) return 1;
-   if (compute_var_tables(s, false)) return 1;
+   // on a group shard (hook set) the Planck integrals are sharded too; a handle that owns every group integrates them all
+   if (compute_var_tables(s, false, s->allreduce != nullptr && s->Gl < p.G)) return 1;
    if (event_end(s, ep)) return 1;
    s->tsteps_done++;
    s->tm.tupdate_count++;
