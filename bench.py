@@ -318,8 +318,9 @@ def main():
     if args.V == 0.0:
         bpu["BDF"] = 48  # no correction source: the BDF stage does not read the stage-2 result
     if args.cell_fields:
-        # + the per-(group, cell) tables every row of the group reads: sigma, srcB (+ cor1..3 with the correction) / M rows
-        extra = (40.0 if args.V != 0.0 else 16.0) / M
+        # + the per-(group, cell) tables: sigma, srcB (+ cor1..3 with the correction), kept once per sweep direction and read
+        # from DRAM once per direction sign (the M/2 rows of a sign share them through L2): 2 x 40 B / M rows
+        extra = 2 * (40.0 if args.V != 0.0 else 16.0) / M
         bpu = {k: v + extra for k, v in bpu.items()}
     if tm.step_launches > 0:
         # fused BDF2-step kernel: one pass over the state per time step -- reads ends^n (16 B), writes ends^(n+1) (16 B)
@@ -358,7 +359,7 @@ def main():
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
                     "traffic": traffic, "algorithmic_bytes_per_launch": (alg_bytes / n_launches) if n_launches else None,
                     "avg_launch_ms": (sweep_ms / n_launches) if n_launches else None, "peak_source": peak_src,
-                    "kernel": ("rtk::var_sweep_kernel<KIND,CORR> (cell-dependent material fields; BE,CN,BE,BDF per step)" if args.cell_fields
+                    "kernel": ("rtk::var_tile_kernel<KIND,CORR,THREADS,4> (cell-dependent material fields, TMA-staged material tables, pair scan; BE,CN,BE,BDF per step)" if args.cell_fields
                                else "rtk::sweep_kernel<KIND,CORR,T,CPT,RING> (BE,CN,BE,BDF per step)"),
                     "algorithmic_bytes_per_unknown": bpu, "by_kind": by_kind}
     gpu_launches = int(tm.kernel_launches)

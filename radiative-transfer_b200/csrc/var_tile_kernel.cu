@@ -144,11 +144,14 @@ __global__ void __launch_bounds__(THREADS, var_min_blocks<KIND, CORR, THREADS, C
    __shared__ double s_ctile;
 
    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+   // two single-thread roles in DIFFERENT warps, so that neither warp carries all the serial work: thread 0 looks back and
+   // publishes; the first lane of the last warp (PROD) draws and decodes tickets and issues every TMA load and store
+   constexpr int PROD = THREADS - 32;
    const unsigned flag_incl = a.epoch * 2u + 2u;
    const long long total_tiles = (long long)a.n_chains * a.tiles_per_chain;
    const double kbc = (KIND == KIND_BE) ? 1.0 : (KIND == KIND_CN ? 2.0 : 6.0);
 
-   // ---- thread 0 only: TMA / bulk loads of one tile into pipeline buffer b (X1 into ring slot r)
+   // ---- PROD only: TMA / bulk loads of one tile into pipeline buffer b (X1 into ring slot r)
    auto issue_loads = [&](const TileDesc &ti, int b, int r) {
       const bool halo = NEED_X2 && ti.tile_start > 0;
       const unsigned bytes = (unsigned)(NARR * TILE_BYTES + NT * MAT_BYTES) + (halo ? (KIND == KIND_BDF ? 32u : 16u) : 0u);
@@ -164,7 +167,7 @@ __global__ void __launch_bounds__(THREADS, var_min_blocks<KIND, CORR, THREADS, C
       }
    };
 
-   // thread 0 only: the tile's boxes of the material tables (counted in the expect_tx of issue_loads)
+   // PROD only: the tile's boxes of the material tables (counted in the expect_tx of issue_loads)
    auto issue_mat = [&](const TileDesc &ti, int b) {
       const int trow = ti.sgn * va.Gl + ti.gl; // the table copy in this row's sweep order
 #pragma unroll
@@ -175,7 +178,7 @@ __global__ void __launch_bounds__(THREADS, var_min_blocks<KIND, CORR, THREADS, C
    TicketCursor cursor;
    cursor.ticket = -2;
    long long ahead = 0;
-   if (tid == 0)
+   if (tid == PROD)
    {
       mbar_init(&s_full[0], 1);
       mbar_init(&s_full[1], 1);
@@ -202,7 +205,7 @@ __global__ void __launch_bounds__(THREADS, var_min_blocks<KIND, CORR, THREADS, C
       const int ring_next = (ring == RING - 1) ? 0 : ring + 1;
       const int slot_next = (slot == 2) ? 0 : slot + 1, slot_ahead = (slot_next == 2) ? 0 : slot_next + 1;
       const long long nxt = s_ticket[slot_next];
-      if (tid == 0)
+      if (tid == PROD)
       {
          if (nxt < total_tiles)
          {
@@ -316,7 +319,7 @@ __global__ void __launch_bounds__(THREADS, var_min_blocks<KIND, CORR, THREADS, C
       if (lane == 0) { Ae = 1.0; We = 0.0; }
       if (lane == 31) { s_wA[warp] = Ai; s_wW[warp] = Wi; }
       __syncthreads(); // (C) warp totals visible; nobody reads the material tables of this tile any more
-      if (tid == 0 && nxt < total_tiles) issue_mat(s_desc[slot_next], buf ^ 1);
+      if (tid == PROD && nxt < total_tiles) issue_mat(s_desc[slot_next], buf ^ 1);
       double Ap = 1.0, Wp = 0.0; // composition of the warps before this one
       for (int w2 = 0; w2 < warp; ++w2)
       {
@@ -368,7 +371,7 @@ __global__ void __launch_bounds__(THREADS, var_min_blocks<KIND, CORR, THREADS, C
       fence_proxy_async();
       __syncthreads(); // (F)
 
-      if (tid == 0)
+      if (tid == PROD)
       {
          tma_store_3d(&maps.m[a.iout], 0, ti.tile_start >> 3, ti.row, s1); // rows that end inside the tile are clipped
          bulk_commit();
@@ -378,7 +381,7 @@ __global__ void __launch_bounds__(THREADS, var_min_blocks<KIND, CORR, THREADS, C
       ring = ring_next;
       slot = slot_next;
    }
-   if (tid == 0)
+   if (tid == PROD)
    {
       bulk_wait_read<0>();
       tq.finish(a, total_tiles);
