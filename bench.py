@@ -318,9 +318,10 @@ def main():
     if args.V == 0.0:
         bpu["BDF"] = 48  # no correction source: the BDF stage does not read the stage-2 result
     if args.cell_fields:
-        # + the per-(group, cell) tables: sigma, srcB (+ cor1..3 with the correction), kept once per sweep direction and read
-        # from DRAM once per direction sign (the M/2 rows of a sign share them through L2): 2 x 40 B / M rows
-        extra = 2 * (40.0 if args.V != 0.0 else 16.0) / M
+        # + the per-(group, cell) tables every row of the group reads: sigma, srcB (+ cor1..3 with the correction) / M rows.
+        # (The kernel keeps them once per sweep direction, so DRAM sees up to twice that -- counted as traffic, not as
+        # algorithmic bytes.)
+        extra = (40.0 if args.V != 0.0 else 16.0) / M
         bpu = {k: v + extra for k, v in bpu.items()}
     if tm.step_launches > 0:
         # fused BDF2-step kernel: one pass over the state per time step -- reads ends^n (16 B), writes ends^(n+1) (16 B)
