@@ -104,3 +104,26 @@ def test_validation_is_refused_with_cell_fields(rt):
     p.T_cell = np.full(p.N, 1.0)
     with pytest.raises(rt.capi.RtError):
         rt.Solver(p)
+
+
+@pytest.mark.parametrize("var_threads", ["64", "128", "0"])
+@pytest.mark.parametrize("ts,bcl,bcr", [(3, 2, 1), (2, 1, 1)])
+def test_every_cell_dependent_kernel_variant(rt, oracle, monkeypatch, var_threads, ts, bcl, bcr):
+    """the tile kernel in both shapes (64 / 128 threads x 4 cells: var_tile_kernel.cu) and the chain-walk cross-check
+    kernel (RT_CUDA_VAR_THREADS=0: var_kernel.cu) against the oracle, rows longer than several tiles and ending inside one"""
+    monkeypatch.setenv("RT_CUDA_VAR_THREADS", var_threads)
+    p = synthetic_parameters(rt, M=8, G=5, N=2 * 512 + 77, dt=1e-3, V=1.0, steps=2, bc_left=bcl, bc_right=bcr, ts_method=ts)
+    _fields(p)
+    _compare(rt, oracle, p, 2 * (4 if ts == 3 else 1))
+
+
+def test_tile_kernel_is_bitwise_reproducible(rt):
+    """the look-back always takes the predecessor's inclusive value, so two runs agree bit for bit"""
+    p = synthetic_parameters(rt, M=8, G=6, N=5000, dt=1e-3, V=1.0, steps=2, bc_left=2, bc_right=1)
+    _fields(p)
+    runs = []
+    for _ in range(2):
+        with rt.Solver(p) as s:
+            s.solve()
+            runs.append(s.ends(0).copy(order="F"))
+    assert np.array_equal(runs[0], runs[1])
