@@ -71,7 +71,7 @@ struct rt_solver
    int vt_pitch = 0;               // N rounded up to 16
    double *vt_fwd(int k) const { return d_vt[k] + (size_t)Gl * vt_pitch; } // the forward (mu > 0) copy
    MatMaps mat_maps;
-   int var_threads = 64;           // CTA size of var_tile_kernel (x 4 cells per thread); RT_CUDA_VAR_THREADS=64|128, 0 = the chain-walk kernel
+   int var_threads = 64, var_cpt = 4; // tile shape of var_tile_kernel: RT_CUDA_VAR_THREADS=64|128 (0 = the chain-walk kernel), RT_CUDA_VAR_CPT=4|8
    double *d_edge_state[4] = {nullptr, nullptr, nullptr, nullptr};  // B_left, dEB_left, B_right, dEB_right (G each)
    // material-temperature update (extension; rt_params::cv > 0)
    bool tupdate = false, T_moved = false;
@@ -583,8 +583,10 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       if (const char *ve = getenv("RT_CUDA_VAR_THREADS"))
       {
          const int t = atoi(ve);
-         if (t == 0 || var_tile_shape_supported(t)) s->var_threads = t;
+         if (t == 0 || var_tile_shape_supported(t, 4)) s->var_threads = t;
       }
+      if (const char *ce = getenv("RT_CUDA_VAR_CPT"))
+         if (s->var_threads > 0 && var_tile_shape_supported(s->var_threads, atoi(ce))) s->var_cpt = atoi(ce);
       for (int k = 0; k < 4; ++k) CKD(dalloc(&s->d_edge_state[k], G));
       if (s->tupdate)
       {
@@ -637,11 +639,11 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       CKD(pool_alloc(s, &s->E[k], s->buf_elems));
       for (int kind = 0; kind < 3; ++kind) CKC(make_tile_map(&s->maps[kind].m[k], s->E[k], gb * M, s->Np, s->tile_cells[kind]));
       CKC(make_tile_map(&s->maps_step.m[k], s->E[k], gb * M, s->Np, s->step_box_cells));
-      if (s->var && s->var_threads > 0) CKC(make_tile_map(&s->maps_var.m[k], s->E[k], gb * M, s->Np, s->var_threads * 4));
+      if (s->var && s->var_threads > 0) CKC(make_tile_map(&s->maps_var.m[k], s->E[k], gb * M, s->Np, s->var_threads * s->var_cpt));
    }
    if (s->var && s->var_threads > 0)
       for (int k = 0; k < 5; ++k) // a table row as pitch/2 16-byte "cells": the same 128-byte-swizzled box as a time-level tile
-         CKC(make_tile_map(&s->mat_maps.m[k], s->d_vt[k], 2 * s->Gl, s->vt_pitch / 2, s->var_threads * 2));
+         CKC(make_tile_map(&s->mat_maps.m[k], s->d_vt[k], 2 * s->Gl, s->vt_pitch / 2, s->var_threads * s->var_cpt / 2));
    const size_t ntiles = (size_t)gb * M * s->max_tiles_per_row;
    CKD(dalloc(&s->d_tile_status, ntiles));
    CKC(cudaMemsetAsync(s->d_tile_status, 0, ntiles * sizeof(double2), s->st));
@@ -723,7 +725,7 @@ static int launch_stage(rt_solver *s, int kind, int i1n, int i1p, int i2, int ic
       if (s->var_threads > 0)
       {
          // var_tile_kernel.cu: the uniform sweep's machinery (tickets, TMA tiles, look-back) with per-cell constants
-         const int tile = s->var_threads * 4;
+         const int tile = s->var_threads * s->var_cpt;
          VarTileArgs va;
          va.s = a;
          va.s.tiles_per_row = (p.N + tile - 1) / tile;
@@ -731,7 +733,7 @@ static int launch_stage(rt_solver *s, int kind, int i1n, int i1p, int i2, int ic
          va.s.lookback_walk = 0;
          va.mu = s->d_mu; va.bdry = s->d_bdry; va.G0 = p.group_begin; va.Gl = s->Gl;
          va.dx = p.dx; va.tau = tau; va.dt = p.dt; va.beta = p.V / C_LIGHT;
-         CK(launch_var_tile(kind, corr, s->var_threads, s->maps_var, s->mat_maps, va, s->num_sms, s->st, &grid));
+         CK(launch_var_tile(kind, corr, s->var_threads, s->var_cpt, s->maps_var, s->mat_maps, va, s->num_sms, s->st, &grid));
          const unsigned long long total_tiles = (unsigned long long)va.s.n_chains * va.s.tiles_per_chain;
          s->ticket_base += (total_tiles + s->ticket_batch - 1) / s->ticket_batch + (unsigned long long)grid;
          s->last_block = s->var_threads;

@@ -33,9 +33,9 @@ struct VarTileArgs
    int G0, Gl;         // first owned group, owned groups (= rows of one table copy)
    double dx, tau, dt, beta;
 };
-bool var_tile_shape_supported(int threads);
-// persistent CTAs of `threads` x 4 cells; the caller advances its ticket base like after launch_sweep
-cudaError_t launch_var_tile(int kind, bool corr, int threads, const SweepMaps &maps, const MatMaps &mats, const VarTileArgs &va,
+bool var_tile_shape_supported(int threads, int cpt); // 64 x 4, 64 x 8, 128 x 4
+// persistent CTAs of `threads` x `cpt` cells; the caller advances its ticket base like after launch_sweep
+cudaError_t launch_var_tile(int kind, bool corr, int threads, int cpt, const SweepMaps &maps, const MatMaps &mats, const VarTileArgs &va,
                             int num_sms, cudaStream_t st, int *grid_out);
 
 struct CellTermsArgs

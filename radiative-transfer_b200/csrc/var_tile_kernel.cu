@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(THREADS, var_min_blocks<KIND, CORR, THREADS, C
    constexpr int NT = CORR ? 5 : 2;        // material tables staged per tile
    constexpr int MAT_BYTES = TILE * 8;     // one table tile: TILE doubles = TILE/2 "double2 cells" of the tensor map
    constexpr int RING = 3;
-   static_assert(CPT == 4, "a thread reads its 4 table entries as two 16-byte pairs");
+   static_assert(CPT == 4 || CPT == 8, "a thread reads its table entries as 16-byte pairs; the swizzled images are conflict-free for 4 and 8");
    static_assert(MAT_BYTES % 1024 == 0, "SWIZZLE_128B images must be 1024-byte aligned");
 
    const SweepArgs &a = va.s;
@@ -254,21 +254,13 @@ __global__ void __launch_bounds__(THREADS, var_min_blocks<KIND, CORR, THREADS, C
             if (KIND == KIND_BDF) up1 = reinterpret_cast<const double2 *>(s1 + swz(j0 - 1))->y;
             if (NEED_X2) up2 = reinterpret_cast<const double2 *>(s2 + swz(j0 - 1))->y;
          }
-         // the thread's 4 entries of every table: two 16-byte pairs of the swizzled image
-         double mt[NT][CPT];
-#pragma unroll
-         for (int t = 0; t < NT; ++t)
-         {
-            const double2 p0 = *reinterpret_cast<const double2 *>(sm + t * MAT_BYTES + swz(j0 >> 1));
-            const double2 p1 = *reinterpret_cast<const double2 *>(sm + t * MAT_BYTES + swz((j0 >> 1) + 1));
-            mt[t][0] = p0.x; mt[t][1] = p0.y; mt[t][2] = p1.x; mt[t][3] = p1.y;
-         }
+         // the thread's CPT entries of every table are CPT/2 16-byte pairs of the swizzled image (conflict-free for 4 and 8)
+         auto mat_pair = [&](int t, int pp) { return *reinterpret_cast<const double2 *>(sm + t * MAT_BYTES + swz((j0 >> 1) + pp)); };
          const RowConst<KIND, CORR> rc(mu, va.dx, va.tau, va.dt, va.beta);
          const bool row_head = ti.tile_start == 0 && tid == 0;
-         auto cell = [&](int jj, bool masked) {
+         auto cell = [&](int jj, bool masked, double sig, double srcB, double cor1, double cor2, double cor3) {
             const int j = j0 + jj;
-            const RowCoef c = rc.cell(mt[0][jj], mt[1][jj], CORR ? mt[CORR ? 2 : 0][jj] : 0.0, CORR ? mt[CORR ? 3 : 0][jj] : 0.0,
-                                      CORR ? mt[CORR ? 4 : 0][jj] : 0.0);
+            const RowCoef c = rc.cell(sig, srcB, cor1, cor2, cor3);
             const int o = swz(j);
             double2 X1[1], X2[1];
             double xs[1], wl[1], Uc[1];
@@ -291,16 +283,19 @@ __global__ void __launch_bounds__(THREADS, var_min_blocks<KIND, CORR, THREADS, C
             if (KIND == KIND_BDF) up1 = X1[0].y;
             if (NEED_X2) up2 = X2[0].y;
          };
-         if (ti.valid == TILE)
-         {
+         auto run = [&](bool masked) {
 #pragma unroll
-            for (int jj = 0; jj < CPT; ++jj) cell(jj, false);
-         }
-         else
-         {
+            for (int pp = 0; pp < CPT / 2; ++pp)
+            {
+               double2 m[5];
 #pragma unroll
-            for (int jj = 0; jj < CPT; ++jj) cell(jj, true);
-         }
+               for (int t = 0; t < 5; ++t) m[t] = (t < NT) ? mat_pair(t, pp) : make_double2(0.0, 0.0);
+               cell(2 * pp, masked, m[0].x, m[1].x, m[2].x, m[3].x, m[4].x);
+               cell(2 * pp + 1, masked, m[0].y, m[1].y, m[2].y, m[3].y, m[4].y);
+            }
+         };
+         if (ti.valid == TILE) run(false);
+         else run(true);
       }
 
       // ---- block scan of the pairs
@@ -430,13 +425,14 @@ static cudaError_t var_launch_shape(int kind, bool corr, const SweepMaps &maps, 
    return cudaErrorInvalidValue;
 }
 
-bool var_tile_shape_supported(int threads) { return threads == 64 || threads == 128; }
+bool var_tile_shape_supported(int threads, int cpt) { return (threads == 64 && (cpt == 4 || cpt == 8)) || (threads == 128 && cpt == 4); }
 
-cudaError_t launch_var_tile(int kind, bool corr, int threads, const SweepMaps &maps, const MatMaps &mats, const VarTileArgs &va,
+cudaError_t launch_var_tile(int kind, bool corr, int threads, int cpt, const SweepMaps &maps, const MatMaps &mats, const VarTileArgs &va,
                             int num_sms, cudaStream_t st, int *grid_out)
 {
-   if (threads == 64) return var_launch_shape<64, 4>(kind, corr, maps, mats, va, num_sms, st, grid_out);
-   if (threads == 128) return var_launch_shape<128, 4>(kind, corr, maps, mats, va, num_sms, st, grid_out);
+   if (threads == 64 && cpt == 4) return var_launch_shape<64, 4>(kind, corr, maps, mats, va, num_sms, st, grid_out);
+   if (threads == 64 && cpt == 8) return var_launch_shape<64, 8>(kind, corr, maps, mats, va, num_sms, st, grid_out);
+   if (threads == 128 && cpt == 4) return var_launch_shape<128, 4>(kind, corr, maps, mats, va, num_sms, st, grid_out);
    return cudaErrorInvalidValue;
 }
 } // namespace rtk

@@ -169,3 +169,16 @@ def test_group_shards_coupled_through_the_allreduce_hook(rt, oracle):
             assert not errs, errs
             _check_step(a, ref[k], B, slice(0, 4))
             _check_step(b, ref[k], B, slice(4, 9))
+
+
+def test_grey_single_group_with_temperature_update(rt, oracle):
+    """G = 1 (the shape of prm/single_group.prm): the last-group remainder IS the group, the edge stencils take their
+    G = 1 branch (correction.cpp:206-211 overwrite), the group sum has one term"""
+    p = synthetic_parameters(rt, M=2, G=1, N=400, dt=1e-3, V=1.0, steps=3, bc_left=2, bc_right=2)
+    p.T_cell = 0.9 + 0.2 * np.sin(np.arange(p.N) / 23.0) ** 2
+    p.cv = 0.6
+    ref, B = _oracle_steps(oracle, rt, p, 3, 4, threads=1)
+    with rt.Solver(p) as s:
+        for k in range(3):
+            s.run_stages(4)
+            _check_step(s, ref[k], B)
