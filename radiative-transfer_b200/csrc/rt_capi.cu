@@ -119,7 +119,7 @@ struct rt_solver
    size_t ev_used = 0;
    bool timing_on = true;
    // fused BDF2-step kernel (step_kernel.cu): RT_CUDA_FUSED=0 runs every step stage by stage
-   bool fused = true, half_stale = false;
+   bool fused = true, fused_var = false, half_stale = false;
    int step_threads = 32, step_cpt = 8, step_chain = 4, step_box_cells = 256, step_tile_cells = 1024, step_tiles_per_row = 0;
    SweepMaps maps_step;
    int ticket_batch = 8;       // tickets per atomic draw (RT_CUDA_TICKET_BATCH)
@@ -528,8 +528,12 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       s->step_tile_cells = s->step_box_cells * s->step_chain;     // cells per ticket
       s->step_tiles_per_row = (N + s->step_tile_cells - 1) / s->step_tile_cells;
       s->max_tiles_per_row = std::max(s->max_tiles_per_row, 4 * s->step_tiles_per_row); // 4 look-back words per tile
+      if (s->var) s->max_tiles_per_row = std::max(s->max_tiles_per_row, 4 * ((N + 255) / 256)); // fused cell-dependent step, 256-cell tiles
       const char *fe = getenv("RT_CUDA_FUSED");
-      s->fused = !(fe && fe[0] == '0') && !s->var; // the cell-dependent kernels are per-stage only
+      s->fused = !(fe && fe[0] == '0') && !s->var;
+      // cell-dependent fields: the fused step of var_step_kernel.cu (RT_CUDA_FUSED=0 or RT_CUDA_VAR_FUSED=0: stage by stage)
+      const char *vfe = getenv("RT_CUDA_VAR_FUSED");
+      s->fused_var = s->var && !(fe && fe[0] == '0') && !(vfe && vfe[0] == '0');
    }
    const char *tenv = getenv("RT_CUDA_TIMING");
    s->timing_on = !(tenv && tenv[0] == '0');
@@ -587,6 +591,7 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       }
       if (const char *ce = getenv("RT_CUDA_VAR_CPT"))
          if (s->var_threads > 0 && var_tile_shape_supported(s->var_threads, atoi(ce))) s->var_cpt = atoi(ce);
+      if (!(s->var_threads > 0 && var_step_shape_supported(s->var_threads, s->var_cpt))) s->fused_var = false;
       for (int k = 0; k < 4; ++k) CKD(dalloc(&s->d_edge_state[k], G));
       if (s->tupdate)
       {
@@ -670,10 +675,10 @@ extern "C" int rt_get_plan(const rt_solver *s, rt_plan *plan)
    plan->tiles_per_row = s->tiles_per_row[KIND_BE];
    plan->sweep_grid = s->last_grid;
    plan->sweep_block = s->last_block ? s->last_block : s->threads[KIND_BE];
-   plan->fused = (s->fused && s->p.ts_method == 3) ? 1 : 0;
-   plan->step_tile_cells = s->step_tile_cells;
-   plan->step_block = s->step_threads * s->step_chain;
-   plan->step_chain = s->step_chain;
+   plan->fused = ((s->fused || s->fused_var) && s->p.ts_method == 3) ? 1 : 0;
+   plan->step_tile_cells = s->var ? s->var_threads * s->var_cpt : s->step_tile_cells;
+   plan->step_block = s->var ? s->var_threads : s->step_threads * s->step_chain;
+   plan->step_chain = s->var ? 1 : s->step_chain;
    plan->bytes_per_group = (size_t)4 * s->p.M * s->Np * sizeof(double2);
    plan->state_bytes = 4 * s->buf_elems * sizeof(double2);
    cudaSetDevice(s->p.device);
@@ -843,8 +848,11 @@ static int run_one_stage(rt_solver *s)
 
 // One whole BDF2 step (4 stage sweeps) in a single pass over the state (step_kernel.cu), out of place: afterwards
 // prev_ends is the old buffer; half_ends is not stored (rt_get_ends re-materialises it on demand).
+static int run_fused_step_var(rt_solver *s);
+
 static int run_fused_step(rt_solver *s)
 {
+   if (s->var) return run_fused_step_var(s);
    const rt_params &p = s->p;
    const int in = s->i_ends, out = pick_free(in, -1, -1, -1);
    StepArgs a;
@@ -874,6 +882,53 @@ static int run_fused_step(rt_solver *s)
    s->ticket_base += (total_tiles + tb - 1) / tb + (unsigned long long)grid;
    s->last_grid = grid;
    s->last_block = s->step_threads * s->step_chain;
+   s->i_prev = in;
+   s->i_ends = out;
+   s->i_half_neg = s->i_half_pos = -1;
+   s->half_stale = true;
+   s->stages_done += 4;
+   s->tm.step_launches++;
+   s->tm.kernel_launches++;
+   s->tm.stages += 4;
+   s->tm.unknown_stages += 4ll * a.rows * p.N;
+   s->results_valid = false;
+   return 0;
+}
+
+// the same with cell-dependent material fields (var_step_kernel.cu)
+static int run_fused_step_var(rt_solver *s)
+{
+   const rt_params &p = s->p;
+   const int in = s->i_ends, out = pick_free(in, -1, -1, -1);
+   const int tile = s->var_threads * s->var_cpt;
+   VarStepArgs va;
+   StepArgs &a = va.s;
+   a.x = s->E[in];
+   a.ix = in; a.iout = out;
+   for (int k = 0; k < 3; ++k) a.coef[k] = nullptr;
+   a.coef_step = nullptr;
+   a.tile_status = s->d_tile_status;
+   a.ticket = s->d_ticket; a.ticket_base = s->ticket_base; a.ticket_batch = s->ticket_batch;
+   a.epoch = ++s->epoch;
+   a.M = p.M; a.N = p.N; a.Np = s->Np;
+   a.rows = s->batch_groups * p.M;
+   a.tiles_per_row = (p.N + tile - 1) / tile;
+   a.reflective_left = (p.bc_left == 2) ? 1 : 0;
+   a.n_chains = a.reflective_left ? a.rows / 2 : a.rows;
+   a.tiles_per_chain = a.reflective_left ? 2 * a.tiles_per_row : a.tiles_per_row;
+   a.l2_prefetch = 0;
+   va.mu = s->d_mu; va.bdry = s->d_bdry; va.G0 = p.group_begin; va.Gl = s->Gl;
+   va.dx = p.dx; va.tau = p.dt / 2.; va.dt = p.dt; va.beta = p.V / C_LIGHT;
+   const bool corr = p.use_correction && p.V != 0.0;
+   EventPair *ep;
+   if (event_begin(s, 4, &ep)) return 1;
+   int grid = 0;
+   CK(launch_var_step(corr, s->var_threads, s->var_cpt, s->maps_var, s->mat_maps, va, s->num_sms, s->st, &grid));
+   if (event_end(s, ep)) return 1;
+   const unsigned long long total_tiles = (unsigned long long)a.n_chains * a.tiles_per_chain;
+   s->ticket_base += (total_tiles + s->ticket_batch - 1) / s->ticket_batch + (unsigned long long)grid;
+   s->last_grid = grid;
+   s->last_block = s->var_threads;
    s->i_prev = in;
    s->i_ends = out;
    s->i_half_neg = s->i_half_pos = -1;
@@ -947,7 +1002,7 @@ static int run_stages(rt_solver *s, int n)
    {
       // whole BDF2 steps go through the fused step kernel; anything else (BE / CN time stepping, a partial step
       // requested through rt_run_stages) stage by stage
-      if (s->fused && s->p.ts_method == 3 && s->stages_done % 4 == 0 && n - k >= 4)
+      if ((s->fused || s->fused_var) && s->p.ts_method == 3 && s->stages_done % 4 == 0 && n - k >= 4)
       {
          if (run_fused_step(s)) return 1;
          k += 4;

@@ -6,6 +6,7 @@
 // oracle/rt_oracle.cpp, which is bit-identical to the reference-pinned uniform oracle for uniform arrays.
 #pragma once
 #include "rt_common.cuh"
+#include "step_kernel.cuh"
 
 namespace rtk
 {
@@ -33,6 +34,19 @@ struct VarTileArgs
    int G0, Gl;         // first owned group, owned groups (= rows of one table copy)
    double dx, tau, dt, beta;
 };
+// fused BDF2 step with cell-dependent fields (var_step_kernel.cu): all four stage sweeps in one pass per tile
+struct VarStepArgs
+{
+   StepArgs s;         // ends^n / ends^(n+1), FOUR look-back words per tile, tickets (s.coef / s.coef_step unused)
+   const double *mu;   // M
+   const double *bdry; // i + M*g (global group)
+   int G0, Gl;
+   double dx, tau, dt, beta; // tau = dt/2
+};
+bool var_step_shape_supported(int threads, int cpt); // 64 x 4, 128 x 4
+cudaError_t launch_var_step(bool corr, int threads, int cpt, const SweepMaps &maps, const MatMaps &mats, const VarStepArgs &va,
+                            int num_sms, cudaStream_t st, int *grid_out);
+
 bool var_tile_shape_supported(int threads, int cpt); // 64 x 4, 64 x 8, 128 x 4
 // persistent CTAs of `threads` x `cpt` cells; the caller advances its ticket base like after launch_sweep
 cudaError_t launch_var_tile(int kind, bool corr, int threads, int cpt, const SweepMaps &maps, const MatMaps &mats, const VarTileArgs &va,

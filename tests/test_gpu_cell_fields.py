@@ -4,6 +4,8 @@ The reference's slab is uniform (solver.cpp:150-157 TODO), so: (1) with UNIFORM 
 kernels must agree with the uniform kernels and with the reference-pinned oracle; (2) with varying fields they are
 checked against the oracle's cell-dependent restatement (tests/test_oracle_cell_fields.py pins that one to the uniform
 oracle bit for bit for uniform arrays) at the same 1e-9 tolerance, every time-stepping method and boundary condition."""
+import os
+
 import numpy as np
 import pytest
 
@@ -30,7 +32,10 @@ def _compare(rt, oracle, p, stages, threads=4):
     o.close()
     with rt.Solver(p) as s:
         s.run_stages(stages)
-        assert s.timing().step_launches == 0  # per-stage launches only
+        # whole BDF2 steps run as ONE fused launch each (var_step_kernel.cu) unless RT_CUDA_VAR_FUSED=0 / the chain-walk kernel
+        fused = p.ts_method == 3 and os.environ.get("RT_CUDA_VAR_FUSED", "1") != "0" and os.environ.get("RT_CUDA_VAR_THREADS", "64") != "0" \
+            and os.environ.get("RT_CUDA_VAR_CPT", "4") == "4" and os.environ.get("RT_CUDA_FUSED", "1") != "0"
+        assert s.timing().step_launches == (stages // 4 if fused else 0)
         worst = 0.0
         for got, want in ((s.psi_mat_ref, ref["psi"]), (s.ends(0), ref["ends"]), (s.ends(1), ref["prev"]), (s.ends(2), ref["half"])):
             ok, w, _ = state_ok(got, want, B)
@@ -127,3 +132,28 @@ def test_tile_kernel_is_bitwise_reproducible(rt):
             s.solve()
             runs.append(s.ends(0).copy(order="F"))
     assert np.array_equal(runs[0], runs[1])
+
+
+@pytest.mark.parametrize("bcl,bcr,V", [(2, 1, 1.0), (1, 1, 1.0), (0, 0, 0.0)])
+def test_fused_step_equals_the_staged_step(rt, oracle, monkeypatch, bcl, bcr, V):
+    """cell-dependent fields: the fused BDF2 step (var_step_kernel.cu) against the same steps run stage by stage
+    (var_tile_kernel.cu) -- same stage algebra, same per-cell constants, so they agree to rounding -- after whole steps,
+    after a partial step on top (stage-by-stage continuation from a fused state), and prev_ends / half_ends after a fused step"""
+    p = synthetic_parameters(rt, M=8, G=4, N=3 * 256 + 100, dt=1e-3, V=V, steps=3, bc_left=bcl, bc_right=bcr)
+    _fields(p)
+    out = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("RT_CUDA_VAR_FUSED", mode)
+        with rt.Solver(p) as s:
+            s.run_stages(8)
+            assert s.timing().step_launches == (2 if mode == "1" else 0)
+            a = dict(ends=s.ends(0), prev=s.ends(1), half=s.ends(2))
+            s.run_stages(2)  # a partial step continues stage by stage
+            a["partial"] = s.ends(0)
+            s.run_stages(2)
+            a["final"] = s.ends(0)
+            out[mode] = a
+    for k in out["1"]:
+        ref = out["0"][k]
+        scale = np.abs(ref).max()
+        assert np.max(np.abs(out["1"][k] - ref)) <= 1e-12 * scale, k
