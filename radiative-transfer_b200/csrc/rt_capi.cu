@@ -71,6 +71,7 @@ struct rt_solver
    int vt_pitch = 0;               // N rounded up to 16
    double *vt_fwd(int k) const { return d_vt[k] + (size_t)Gl * vt_pitch; } // the forward (mu > 0) copy
    MatMaps mat_maps;
+   int var_step_mat_slots = 1;     // RT_CUDA_VAR_STEP_MATBUF=1|2 (fused cell-dependent step; 1 = one more resident CTA, measured +10 %)
    int var_threads = 64, var_cpt = 4; // tile shape of var_tile_kernel: RT_CUDA_VAR_THREADS=64|128 (0 = the chain-walk kernel), RT_CUDA_VAR_CPT=4|8
    double *d_edge_state[4] = {nullptr, nullptr, nullptr, nullptr};  // B_left, dEB_left, B_right, dEB_right (G each)
    // material-temperature update (extension; rt_params::cv > 0)
@@ -592,6 +593,8 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       if (const char *ce = getenv("RT_CUDA_VAR_CPT"))
          if (s->var_threads > 0 && var_tile_shape_supported(s->var_threads, atoi(ce))) s->var_cpt = atoi(ce);
       if (!(s->var_threads > 0 && var_step_shape_supported(s->var_threads, s->var_cpt))) s->fused_var = false;
+      if (const char *me = getenv("RT_CUDA_VAR_STEP_MATBUF"))
+         if (atoi(me) == 1 || atoi(me) == 2) s->var_step_mat_slots = atoi(me);
       for (int k = 0; k < 4; ++k) CKD(dalloc(&s->d_edge_state[k], G));
       if (s->tupdate)
       {
@@ -923,7 +926,7 @@ static int run_fused_step_var(rt_solver *s)
    EventPair *ep;
    if (event_begin(s, 4, &ep)) return 1;
    int grid = 0;
-   CK(launch_var_step(corr, s->var_threads, s->var_cpt, s->maps_var, s->mat_maps, va, s->num_sms, s->st, &grid));
+   CK(launch_var_step(corr, s->var_threads, s->var_cpt, s->var_threads == 64 ? s->var_step_mat_slots : 2, s->maps_var, s->mat_maps, va, s->num_sms, s->st, &grid));
    if (event_end(s, ep)) return 1;
    const unsigned long long total_tiles = (unsigned long long)a.n_chains * a.tiles_per_chain;
    s->ticket_base += (total_tiles + s->ticket_batch - 1) / s->ticket_batch + (unsigned long long)grid;

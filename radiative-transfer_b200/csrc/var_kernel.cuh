@@ -44,8 +44,9 @@ struct VarStepArgs
    double dx, tau, dt, beta; // tau = dt/2
 };
 bool var_step_shape_supported(int threads, int cpt); // 64 x 4, 128 x 4
-cudaError_t launch_var_step(bool corr, int threads, int cpt, const SweepMaps &maps, const MatMaps &mats, const VarStepArgs &va,
-                            int num_sms, cudaStream_t st, int *grid_out);
+// mat_slots: shared-memory slots of material tables, 2 or (64 x 4 only) 1
+cudaError_t launch_var_step(bool corr, int threads, int cpt, int mat_slots, const SweepMaps &maps, const MatMaps &mats,
+                            const VarStepArgs &va, int num_sms, cudaStream_t st, int *grid_out);
 
 bool var_tile_shape_supported(int threads, int cpt); // 64 x 4, 64 x 8, 128 x 4
 // persistent CTAs of `threads` x `cpt` cells; the caller advances its ticket base like after launch_sweep

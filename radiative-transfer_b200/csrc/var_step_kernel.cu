@@ -26,20 +26,22 @@
 
 namespace rtk
 {
-template <bool CORR, int THREADS, int CPT>
+// MB = slots of material tables: 2 (loaded with X, a full tile ahead) or 1 (the next tile's boxes are issued after pass 1
+// of stage 3, the last reader: less lead time, one more resident CTA)
+template <bool CORR, int THREADS, int CPT, int MB>
 constexpr int var_step_smem_bytes()
 {
-   return 4 * THREADS * CPT * 16 + 2 * (CORR ? 5 : 2) * THREADS * CPT * 8 + 1024; // 2 X + S0 + S1 + 2 x tables + slack
+   return 4 * THREADS * CPT * 16 + MB * (CORR ? 5 : 2) * THREADS * CPT * 8 + 1024; // 2 X + S0 + S1 + MB x tables + slack
 }
-template <bool CORR, int THREADS, int CPT>
+template <bool CORR, int THREADS, int CPT, int MB>
 constexpr int var_step_min_blocks()
 {
-   const int by_smem = (227 * 1024) / (var_step_smem_bytes<CORR, THREADS, CPT>() + 1024), by_regs = 65536 / (THREADS * 168);
+   const int by_smem = (227 * 1024) / (var_step_smem_bytes<CORR, THREADS, CPT, MB>() + 1024), by_regs = 65536 / (THREADS * 168);
    return by_smem < by_regs ? by_smem : by_regs;
 }
 
-template <bool CORR, int THREADS, int CPT>
-__global__ void __launch_bounds__(THREADS, var_step_min_blocks<CORR, THREADS, CPT>())
+template <bool CORR, int THREADS, int CPT, int MB>
+__global__ void __launch_bounds__(THREADS, var_step_min_blocks<CORR, THREADS, CPT, MB>())
 var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ MatMaps mats, const VarStepArgs va)
 {
    using TS = TileShape<THREADS, CPT>;
@@ -54,7 +56,7 @@ var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
    auto x_slot = [&](int b) { return tiles + b * TILE_BYTES; };
    unsigned char *const t0 = tiles + 2 * TILE_BYTES;
    unsigned char *const t1 = tiles + 3 * TILE_BYTES;
-   auto mat_slot = [&](int b) { return tiles + 4 * TILE_BYTES + b * NT * MAT_BYTES; };
+   auto mat_slot = [&](int b) { return tiles + 4 * TILE_BYTES + (MB == 2 ? b : 0) * NT * MAT_BYTES; };
 
    __shared__ __align__(16) double2 s_halo[2];
    __shared__ __align__(8) unsigned long long s_full[2];
@@ -72,10 +74,13 @@ var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
       const bool halo = ti.tile_start > 0;
       mbar_expect_tx(&s_full[b], (unsigned)(TILE_BYTES + NT * MAT_BYTES) + (halo ? 16u : 0u));
       tma_load_3d(x_slot(b), &maps.m[a.ix], 0, ti.tile_start >> 3, ti.row, &s_full[b]);
+      if (halo) bulk_load(&s_halo[b], a.x + ti.row_off - 1, 16u, &s_full[b]);
+   };
+   // PROD only: the tile's boxes of the material tables (counted in the expect_tx of issue_loads)
+   auto issue_mat = [&](const TileDesc &ti, int b) {
       const int trow = ti.sgn * va.Gl + ti.gl; // the table copy in this row's sweep order
 #pragma unroll
       for (int t = 0; t < NT; ++t) tma_load_3d(mat_slot(b) + t * MAT_BYTES, &mats.m[t], 0, ti.tile_start >> 4, trow, &s_full[b]);
-      if (halo) bulk_load(&s_halo[b], a.x + ti.row_off - 1, 16u, &s_full[b]);
    };
 
    TicketQueue tq;
@@ -94,6 +99,7 @@ var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
       {
          s_desc[0] = decode_ticket(a, cursor, q0, TILE);
          issue_loads(s_desc[0], 0);
+         issue_mat(s_desc[0], 0);
       }
       if (q1 < total_tiles) s_desc[1] = decode_ticket(a, cursor, q1, TILE);
       ahead = tq.take(a, total_tiles);
@@ -118,6 +124,7 @@ var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
          {
             const TileDesc dn = s_desc[slot_next];
             issue_loads(dn, buf ^ 1); // buffer buf^1 was last read in the previous tile
+            if (MB == 2) issue_mat(dn, buf ^ 1);
          }
          s_ticket[slot_ahead] = ahead;
          if (ahead < total_tiles) s_desc[slot_ahead] = decode_ticket(a, cursor, ahead, TILE);
@@ -149,9 +156,10 @@ var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
       // ---- pass 1 of one stage: per-cell constants from the staged tables, right-hand sides, thread-local pair (A, W).
       // x1 / x2 / xs as in stage_pass1 (sweep_device.cuh); cells past the end of the row are the identity element.
       double alpha[CPT], gamma[CPT], beta[CPT], U[CPT];
-      auto pass1 = [&](auto kindc, const double2 (&x1)[CPT], const double2 (&x2)[CPT], const double (&xs)[CPT], double up1, double up2,
-                       double &A, double &W) {
+      auto pass1m = [&](auto kindc, auto maskc, const double2 (&x1)[CPT], const double2 (&x2)[CPT], const double (&xs)[CPT], double up1,
+                        double up2, double &A, double &W) {
          constexpr int KIND = decltype(kindc)::value;
+         constexpr bool MASKED = decltype(maskc)::value;
          const RowConst<KIND, CORR> rc(mu, va.dx, va.tau, va.dt, va.beta);
          A = 1.0; W = 0.0;
 #pragma unroll
@@ -169,7 +177,7 @@ var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
                double2 X1[1] = {x1[jj]}, X2[1] = {x2[jj]};
                double XS[1] = {xs[jj]}, wl[1], Uc[1];
                stage_pass1<KIND, CORR, 1>(c, X1, X2, XS, up1, up2, row_first && jj == 0, wl, Uc);
-               const bool ok = full || (j0 + jj) < ti.valid;
+               const bool ok = !MASKED || (j0 + jj) < ti.valid;
                alpha[jj] = ok ? c.alpha : 1.0;
                gamma[jj] = ok ? c.gamma : 0.0;
                beta[jj] = ok ? wl[0] : 0.0;
@@ -180,6 +188,13 @@ var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
                if (KIND != KIND_BE) up2 = x2[jj].y;
             }
          }
+      };
+
+      // full tiles (all but the last tile of a row) take the copy without the identity selects
+      auto pass1 = [&](auto kindc, const double2 (&x1)[CPT], const double2 (&x2)[CPT], const double (&xs)[CPT], double up1, double up2,
+                       double &A, double &W) {
+         if (full) pass1m(kindc, std::false_type{}, x1, x2, xs, up1, up2, A, W);
+         else pass1m(kindc, std::true_type{}, x1, x2, xs, up1, up2, A, W);
       };
 
       // ---- block scan of the pairs + look-back chain k: returns the true inflow of this thread's chunk
@@ -200,6 +215,7 @@ var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
          if (lane == 0) { Ae = 1.0; We = 0.0; }
          if (lane == 31) { s_wA[warp] = Ai; s_wW[warp] = Wi; }
          __syncthreads(); // (C)
+         if (MB == 1 && k == 3 && tid == PROD && nxt < total_tiles) issue_mat(s_desc[slot_next], buf ^ 1); // no reader of the tables left
          double Ap = 1.0, Wp = 0.0;
          for (int w2 = 0; w2 < warp; ++w2)
          {
@@ -323,13 +339,13 @@ var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
 }
 
 // ------------------------------------------------------------------------------------------ host side
-template <bool CORR, int THREADS, int CPT>
+template <bool CORR, int THREADS, int CPT, int MB>
 static cudaError_t var_step_launch_one(const SweepMaps &maps, const MatMaps &mats, const VarStepArgs &va, int num_sms, cudaStream_t st,
                                        int *grid_out)
 {
    static int ctas_per_sm = -1;
-   auto kern = var_step_kernel<CORR, THREADS, CPT>;
-   const size_t smem = (size_t)var_step_smem_bytes<CORR, THREADS, CPT>();
+   auto kern = var_step_kernel<CORR, THREADS, CPT, MB>;
+   const size_t smem = (size_t)var_step_smem_bytes<CORR, THREADS, CPT, MB>();
    if (ctas_per_sm < 0)
    {
       cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -350,14 +366,16 @@ static cudaError_t var_step_launch_one(const SweepMaps &maps, const MatMaps &mat
 
 bool var_step_shape_supported(int threads, int cpt) { return (threads == 64 || threads == 128) && cpt == 4; }
 
-cudaError_t launch_var_step(bool corr, int threads, int cpt, const SweepMaps &maps, const MatMaps &mats, const VarStepArgs &va,
+cudaError_t launch_var_step(bool corr, int threads, int cpt, int mat_slots, const SweepMaps &maps, const MatMaps &mats, const VarStepArgs &va,
                             int num_sms, cudaStream_t st, int *grid_out)
 {
    if (cpt != 4) return cudaErrorInvalidValue;
-   if (threads == 64) return corr ? var_step_launch_one<true, 64, 4>(maps, mats, va, num_sms, st, grid_out)
-                                  : var_step_launch_one<false, 64, 4>(maps, mats, va, num_sms, st, grid_out);
-   if (threads == 128) return corr ? var_step_launch_one<true, 128, 4>(maps, mats, va, num_sms, st, grid_out)
-                                   : var_step_launch_one<false, 128, 4>(maps, mats, va, num_sms, st, grid_out);
+   if (threads == 64 && mat_slots == 1) return corr ? var_step_launch_one<true, 64, 4, 1>(maps, mats, va, num_sms, st, grid_out)
+                                                    : var_step_launch_one<false, 64, 4, 1>(maps, mats, va, num_sms, st, grid_out);
+   if (threads == 64) return corr ? var_step_launch_one<true, 64, 4, 2>(maps, mats, va, num_sms, st, grid_out)
+                                  : var_step_launch_one<false, 64, 4, 2>(maps, mats, va, num_sms, st, grid_out);
+   if (threads == 128) return corr ? var_step_launch_one<true, 128, 4, 2>(maps, mats, va, num_sms, st, grid_out)
+                                   : var_step_launch_one<false, 128, 4, 2>(maps, mats, va, num_sms, st, grid_out);
    return cudaErrorInvalidValue;
 }
 } // namespace rtk
