@@ -384,7 +384,7 @@ def main():
         # material-temperature update (extension): device time per time step of its two parts, this rank
         nt = int(tm.tupdate_count)
         tupdate = {"updates": nt, "exchange_ms_per_step": tm.tupdate_ms / nt, "tables_ms_per_step": tm.tables_ms / nt,
-                   "sweep_ms_per_step": sum(tm.sweep_ms) / nt, "allreduce": "NCCL (torch.distributed) on the library's device buffer" if world > 1 else "none (all groups owned)",
+                   "sweep_ms_per_step": (sum(tm.sweep_ms) + tm.step_ms) / nt, "allreduce": "NCCL (torch.distributed) on the library's device buffer" if world > 1 else "none (all groups owned)",
                    "allreduce_bytes_per_step": 3 * N * 8,
                    "what": "exchange = moments + group sums A,E,D + all-reduce + T update; tables = Planck integrals of all G groups per cell "
                            "+ per-cell correction terms at the new T"}

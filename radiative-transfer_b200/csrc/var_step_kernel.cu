@@ -26,6 +26,9 @@
 
 namespace rtk
 {
+#ifndef VAR_STEP_REGS
+#define VAR_STEP_REGS 168 // register budget per thread the resident-CTA target is derived from (A/B: -DVAR_STEP_REGS=128)
+#endif
 // MB = slots of material tables: 2 (loaded with X, a full tile ahead) or 1 (the next tile's boxes are issued after pass 1
 // of stage 3, the last reader: less lead time, one more resident CTA)
 template <bool CORR, int THREADS, int CPT, int MB>
@@ -36,7 +39,7 @@ constexpr int var_step_smem_bytes()
 template <bool CORR, int THREADS, int CPT, int MB>
 constexpr int var_step_min_blocks()
 {
-   const int by_smem = (227 * 1024) / (var_step_smem_bytes<CORR, THREADS, CPT, MB>() + 1024), by_regs = 65536 / (THREADS * 168);
+   const int by_smem = (227 * 1024) / (var_step_smem_bytes<CORR, THREADS, CPT, MB>() + 1024), by_regs = 65536 / (THREADS * VAR_STEP_REGS);
    return by_smem < by_regs ? by_smem : by_regs;
 }
 
