@@ -35,6 +35,12 @@ __device__ __forceinline__ double inv_h3c2() { return 1.0 / ((H_KEV_SH * H_KEV_S
 // ---- B and dB/dT of one group together.  Same operations, in the same order, as integrate_B and integrate_dBdT
 // evaluated one after the other; what they have in common is evaluated once: exp(-n z) of the series terms (each
 // sum keeps its own adaptive term count), the term weights 1/n^4, E/T and expm1(E/T) at the Gauss points.
+// TRIM (per-cell tables only; the reference's own G-length evaluation, ncell = 1, keeps every term): the series terms are
+// summed in descending n from N >= 32 whatever z is, but term_n / term_1 <= e^{-(n-1) z} (the polynomial ratio is at most
+// n^4, cancelled by the 1/n^4 weight), so every term with (n-1) z > 46 is below e^-46 = 2^-66 of the leading term and all of
+// them together below 2^-65 of the sum: they cannot move the fp64 result beyond a last-bit rounding flip.  Those terms are
+// not evaluated: for z = 5 that leaves 11 of 32 terms, for z = 30 three.
+template <bool TRIM>
 __device__ void planck_series_pair(double z1, double z2, double &outB, double &outD)
 {
    auto polyB = [](double x) { return (((x + 3.0) * x + 6.0) * x + 6.0); };
@@ -57,13 +63,25 @@ __device__ void planck_series_pair(double z1, double z2, double &outB, double &o
       if (val > eps && ND < (1 << 20)) ++ND; else break;
    }
    double b1 = 0.0, b2 = 0.0, d1 = 0.0, d2 = 0.0;
-   for (int n = max(NB, ND); n > 0; --n)
+   int n_top = max(NB, ND), n_top2 = n_top;
+   if (TRIM)
+   {
+      n_top = min(n_top, 2 + (int)(46.0 / z1));  // (n-1) z1 <= 46 (+1 for the truncation)
+      n_top2 = min(n_top, 2 + (int)(46.0 / z2)); // z2 > z1: the upper edge's terms die out sooner
+   }
+   for (int n = n_top; n > 0; --n)
    {
       const double dn = (double)n, n2 = dn * dn, in4 = 1.0 / (n2 * n2);
       const double x1 = dn * z1, x2 = dn * z2;
-      const double t1 = exp(-x1) * in4, t2 = exp(-x2) * in4;
-      if (n <= NB) { b1 += t1 * polyB(x1); b2 += t2 * polyB(x2); }
-      if (n <= ND) { d1 += t1 * polyD(x1); d2 += t2 * polyD(x2); }
+      const double t1 = exp(-x1) * in4;
+      if (n <= NB) b1 += t1 * polyB(x1);
+      if (n <= ND) d1 += t1 * polyD(x1);
+      if (!TRIM || n <= n_top2)
+      {
+         const double t2 = exp(-x2) * in4;
+         if (n <= NB) b2 += t2 * polyB(x2);
+         if (n <= ND) d2 += t2 * polyD(x2);
+      }
    }
    outB = b1 - b2;
    outD = d1 - d2;
@@ -86,6 +104,7 @@ __device__ void gauss12_pair(double T, double lo, double hi, double &outB, doubl
    outD = accD;
 }
 
+template <bool TRIM>
 __device__ void planck_group_pair(double T, double E_min, double E_max, double &B, double &D)
 {
    B = 0.0; D = 0.0;
@@ -97,14 +116,14 @@ __device__ void planck_group_pair(double T, double E_min, double E_max, double &
    if (z2 <= 0.7) gauss12_pair(T, E_min, E_max, vB, vD);
    else if (z1 >= 0.5)
    {
-      planck_series_pair(z1, z2, vB, vD);
+      planck_series_pair<TRIM>(z1, z2, vB, vD);
       vB *= prefB; vD *= prefD;
    }
    else
    {
       double sB, sD;
       gauss12_pair(T, E_min, 0.6 * T, vB, vD);
-      planck_series_pair(0.6, z2, sB, sD);
+      planck_series_pair<TRIM>(0.6, z2, sB, sD);
       vB = vB + prefB * sB; vD = vD + prefD * sD;
    }
    B = vB * 4.0 * PI_TRUNC;
@@ -115,6 +134,7 @@ __device__ void planck_group_pair(double T, double E_min, double E_max, double &
 // the same group at neighbouring temperatures, so they take the same branch (Gauss / series / split) and run the same
 // number of series terms -- with the group fastest a warp executed ~10 of 32 lanes per instruction (ncu) -- and the
 // stores are coalesced.  g < G-1 only; the last group is the remainder (planck_finalize_kernel).
+template <bool TRIM>
 __global__ void planck_integrals_kernel(int G, int ncell, int g0, int ng, const double *__restrict__ e_edge,
                                         const double *__restrict__ T, double *__restrict__ B, double *__restrict__ dBdT)
 {
@@ -122,7 +142,7 @@ __global__ void planck_integrals_kernel(int G, int ncell, int g0, int ng, const 
    if (idx >= (long long)ncell * ng) return;
    const int g = g0 + (int)(idx / ncell), c = (int)(idx % ncell);
    double b, d;
-   planck_group_pair(T[c], e_edge[g], e_edge[g + 1], b, d);
+   planck_group_pair<TRIM>(T[c], e_edge[g], e_edge[g + 1], b, d);
    B[(size_t)g * ncell + c] = b;
    dBdT[(size_t)g * ncell + c] = d;
 }
@@ -316,7 +336,9 @@ int launch_planck(int G, int ncell, const double *d_e_edge, const double *d_T, d
    if (G > 1)
    {
       const long long total = (long long)ncell * (G - 1);
-      planck_integrals_kernel<<<(unsigned)((total + 127) / 128), 128, 0, st>>>(G, ncell, 0, G - 1, d_e_edge, d_T, d_B, d_dBdT);
+      // ncell == 1 is the reference's own evaluation (one T, G groups): every term; per-cell tables: trimmed series
+      if (ncell == 1) planck_integrals_kernel<false><<<(unsigned)((total + 127) / 128), 128, 0, st>>>(G, ncell, 0, G - 1, d_e_edge, d_T, d_B, d_dBdT);
+      else planck_integrals_kernel<true><<<(unsigned)((total + 127) / 128), 128, 0, st>>>(G, ncell, 0, G - 1, d_e_edge, d_T, d_B, d_dBdT);
       ++launches;
    }
    planck_finalize_kernel<<<(ncell + 127) / 128, 128, 0, st>>>(G, ncell, d_T, d_B, d_dBdT);
@@ -330,7 +352,7 @@ int launch_planck_shard_begin(int G, int ncell, int g0, int ng, const double *d_
    if (n > 0)
    {
       const long long total = (long long)ncell * n;
-      planck_integrals_kernel<<<(unsigned)((total + 127) / 128), 128, 0, st>>>(G, ncell, g0, n, d_e_edge, d_T, d_B, d_dBdT);
+      planck_integrals_kernel<true><<<(unsigned)((total + 127) / 128), 128, 0, st>>>(G, ncell, g0, n, d_e_edge, d_T, d_B, d_dBdT);
    }
    planck_partial_kernel<<<(ncell + 127) / 128, 128, 0, st>>>(ncell, g0, n > 0 ? n : 0, d_B, d_dBdT, d_part);
    return n > 0 ? 2 : 1;
