@@ -27,6 +27,10 @@
 #include "step_kernel.cuh"
 #include "sweep_device.cuh"
 
+#ifndef STEP_SPIN_SLEEP
+#define STEP_SPIN_SLEEP 0 // nanoseconds a warp sleeps between two polls of the previous warp's carry word (A/B knob)
+#endif
+
 namespace rtk
 {
 // packed per-row constants of a BDF2 step: 64 doubles.  The per-cell right-hand sides are FOLDED: with
@@ -342,6 +346,9 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
             double2 w = lds_word(src);
             while ((int)__double_as_longlong(w.y) != seq + 1)
             {
+#if STEP_SPIN_SLEEP > 0
+               __nanosleep(STEP_SPIN_SLEEP); // a polling warp competes for issue slots with the warps that do the work
+#endif
                w = lds_word(src);
                if (++spins > SPIN_LIMIT) __trap();
             }
