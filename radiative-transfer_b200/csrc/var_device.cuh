@@ -48,6 +48,43 @@ struct RowConst
       o2 = o * o;
    }
 
+   // the source terms q = qa + qb (u+v) of a cell: they depend on tau, mu, beta and the material only, NOT on the stage
+   // kind -- all four stages of a BDF2 step (tau = dt/2) share them
+   __device__ __forceinline__ void source_terms(double srcB, double cor1, double cor2, double cor3, double &qa, double &qb) const
+   {
+      qa = hq * srcB;
+      qb = 0.0;
+      if (CORR)
+      {
+         qa = fma(qc2, cor2, fma(qc3, cor3, qa));
+         qb = qb1 * cor1;
+      }
+   }
+
+   // stepper constants of a cell from sigma and its (precomputed) source terms
+   __device__ __forceinline__ RowCoef cell_q(double sig, double qa, double qb) const
+   {
+      RowCoef c;
+      const double d = fma(d1, sig, d0);
+      const double inv = __drcp_rn(fma(d, d, o2));
+      c.id = d * inv;
+      c.io = o * inv;
+      c.alpha = c.io * k;
+      c.gamma = c.id * k;
+      c.qa = qa;
+      c.qb = CORR ? qb : 0.0;
+      c.c_uu = (KIND == KIND_BE) ? cu0 : fma(cu1, sig, cu0);
+      c.c_vv = c.c_uu;
+      c.c_uv = c_uv; c.c_vu = -c_uv;
+      c.p_uu = (KIND == KIND_BDF) ? fma(pu1, sig, pu0) : 0.0;
+      c.p_vv = c.p_uu;
+      c.p_uv = p_uv; c.p_vu = -p_uv;
+      c.up1 = up1; c.up2 = up2;
+      c.kbc = (KIND == KIND_BE) ? 1.0 : (KIND == KIND_CN ? 2.0 : 6.0);
+      c.inflow0 = 0.0;
+      return c;
+   }
+
    __device__ __forceinline__ RowCoef cell(double sig, double srcB, double cor1, double cor2, double cor3) const
    {
       RowCoef c;

@@ -29,8 +29,8 @@ namespace rtk
 #ifndef VAR_STEP_REGS
 #define VAR_STEP_REGS 168 // register budget per thread the resident-CTA target is derived from (A/B: -DVAR_STEP_REGS=128)
 #endif
-// MB = slots of material tables: 2 (loaded with X, a full tile ahead) or 1 (the next tile's boxes are issued after pass 1
-// of stage 3, the last reader: less lead time, one more resident CTA)
+// MB = slots of material tables: 2 (loaded with X) or 1 (the tables are read once, at the start of a tile, so the next
+// tile's boxes are issued after the tile's first barrier: almost a full tile of lead time and one more resident CTA)
 template <bool CORR, int THREADS, int CPT, int MB>
 constexpr int var_step_smem_bytes()
 {
@@ -156,7 +156,25 @@ var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
       if (tid == 0) { if (ti.tile_start > 0) up_x = s_halo[buf].y; }
       else up_x = reinterpret_cast<const double2 *>(sx + swz(j0 - 1))->y;
 
-      // ---- pass 1 of one stage: per-cell constants from the staged tables, right-hand sides, thread-local pair (A, W).
+      // the cell's material enters every stage through sigma and the source terms qa, qb only, and the source terms do not
+      // depend on the stage kind (same tau = dt/2): read the staged tables ONCE per tile, keep 3 values per cell
+      double sigc[CPT], qac[CPT], qbc[CPT];
+      {
+         const RowConst<KIND_BE, CORR> rq(mu, va.dx, va.tau, va.dt, va.beta);
+#pragma unroll
+         for (int pp = 0; pp < CPT / 2; ++pp)
+         {
+            double2 m[5];
+#pragma unroll
+            for (int t = 0; t < 5; ++t)
+               m[t] = (t < NT) ? *reinterpret_cast<const double2 *>(sm + t * MAT_BYTES + swz((j0 >> 1) + pp)) : make_double2(0.0, 0.0);
+            sigc[2 * pp] = m[0].x; sigc[2 * pp + 1] = m[0].y;
+            rq.source_terms(m[1].x, m[2].x, m[3].x, m[4].x, qac[2 * pp], qbc[2 * pp]);
+            rq.source_terms(m[1].y, m[2].y, m[3].y, m[4].y, qac[2 * pp + 1], qbc[2 * pp + 1]);
+         }
+      }
+
+      // ---- pass 1 of one stage: per-cell constants, right-hand sides, thread-local pair (A, W).
       // x1 / x2 / xs as in stage_pass1 (sweep_device.cuh); cells past the end of the row are the identity element.
       double alpha[CPT], gamma[CPT], beta[CPT], U[CPT];
       auto pass1m = [&](auto kindc, auto maskc, const double2 (&x1)[CPT], const double2 (&x2)[CPT], const double (&xs)[CPT], double up1,
@@ -166,30 +184,21 @@ var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
          const RowConst<KIND, CORR> rc(mu, va.dx, va.tau, va.dt, va.beta);
          A = 1.0; W = 0.0;
 #pragma unroll
-         for (int pp = 0; pp < CPT / 2; ++pp)
+         for (int jj = 0; jj < CPT; ++jj)
          {
-            double2 m[5];
-#pragma unroll
-            for (int t = 0; t < 5; ++t)
-               m[t] = (t < NT) ? *reinterpret_cast<const double2 *>(sm + t * MAT_BYTES + swz((j0 >> 1) + pp)) : make_double2(0.0, 0.0);
-#pragma unroll
-            for (int h = 0; h < 2; ++h)
-            {
-               const int jj = 2 * pp + h;
-               const RowCoef c = h ? rc.cell(m[0].y, m[1].y, m[2].y, m[3].y, m[4].y) : rc.cell(m[0].x, m[1].x, m[2].x, m[3].x, m[4].x);
-               double2 X1[1] = {x1[jj]}, X2[1] = {x2[jj]};
-               double XS[1] = {xs[jj]}, wl[1], Uc[1];
-               stage_pass1<KIND, CORR, 1>(c, X1, X2, XS, up1, up2, row_first && jj == 0, wl, Uc);
-               const bool ok = !MASKED || (j0 + jj) < ti.valid;
-               alpha[jj] = ok ? c.alpha : 1.0;
-               gamma[jj] = ok ? c.gamma : 0.0;
-               beta[jj] = ok ? wl[0] : 0.0;
-               U[jj] = ok ? Uc[0] : 0.0;
-               W = fma(alpha[jj], W, beta[jj]);
-               A *= alpha[jj];
-               if (KIND == KIND_BDF) up1 = x1[jj].y;
-               if (KIND != KIND_BE) up2 = x2[jj].y;
-            }
+            const RowCoef c = rc.cell_q(sigc[jj], qac[jj], qbc[jj]);
+            double2 X1[1] = {x1[jj]}, X2[1] = {x2[jj]};
+            double XS[1] = {xs[jj]}, wl[1], Uc[1];
+            stage_pass1<KIND, CORR, 1>(c, X1, X2, XS, up1, up2, row_first && jj == 0, wl, Uc);
+            const bool ok = !MASKED || (j0 + jj) < ti.valid;
+            alpha[jj] = ok ? c.alpha : 1.0;
+            gamma[jj] = ok ? c.gamma : 0.0;
+            beta[jj] = ok ? wl[0] : 0.0;
+            U[jj] = ok ? Uc[0] : 0.0;
+            W = fma(alpha[jj], W, beta[jj]);
+            A *= alpha[jj];
+            if (KIND == KIND_BDF) up1 = x1[jj].y;
+            if (KIND != KIND_BE) up2 = x2[jj].y;
          }
       };
 
@@ -218,7 +227,7 @@ var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
          if (lane == 0) { Ae = 1.0; We = 0.0; }
          if (lane == 31) { s_wA[warp] = Ai; s_wW[warp] = Wi; }
          __syncthreads(); // (C)
-         if (MB == 1 && k == 3 && tid == PROD && nxt < total_tiles) issue_mat(s_desc[slot_next], buf ^ 1); // no reader of the tables left
+         if (MB == 1 && k == 0 && tid == PROD && nxt < total_tiles) issue_mat(s_desc[slot_next], buf ^ 1); // the tables were read at the tile's start
          double Ap = 1.0, Wp = 0.0;
          for (int w2 = 0; w2 < warp; ++w2)
          {
