@@ -330,13 +330,16 @@ def main():
         step_bpu = STEP_BYTES_PER_UNKNOWN + (40.0 if args.V != 0.0 else 16.0) / M
         alg = step_bpu * unknowns_per_launch
         achieved = alg / (avg_ms * 1e-3) / 1e9
-        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        vpu = tr.get("var_step_dram_bytes_per_unknown")
+        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                    "traffic": vpu * unknowns_per_launch if vpu else None,
                     "algorithmic_bytes_per_launch": alg, "avg_launch_ms": avg_ms, "peak_source": peak_src,
+                    "fp64_pipe_pct": tr.get("var_step_fp64_pipe_pct"), "issue_active_pct": tr.get("var_step_issue_active_pct"),
                     "kernel": "rtk::var_step_kernel<CORR,THREADS,4,MB> (cell-dependent fields; BE,CN,BE,BDF fused: one launch per BDF2 step)",
                     "algorithmic_bytes_per_unknown_step": step_bpu,
                     "note": "HBM is the roofline reported against, but at 32 B per unknown-step this kernel is bound by instruction issue "
-                            "and fp64 latency (~420 thread-instructions per cell and step: per-cell stepper constants with one reciprocal "
-                            "per stage, four pair scans); run stage by stage the same step moves 176 B per unknown at 0.7-0.8 of the HBM peak",
+                            "and fp64 latency (~330 thread-instructions per cell and step: per-cell stepper constants with one reciprocal "
+                            "per stage, four pair scans; profiles/r01_v9_var_step_ncu_digest.txt); run stage by stage the same step moves 176 B per unknown at 0.7-0.8 of the HBM peak",
                     "staged_equivalent_GBps": sum(bpu[k] * (2 if k == "BE" else 1) for k in kinds) * unknowns_per_launch / (avg_ms * 1e-3) / 1e9}
     elif tm.step_launches > 0:
         # fused BDF2-step kernel: one pass over the state per time step -- reads ends^n (16 B), writes ends^(n+1) (16 B)
