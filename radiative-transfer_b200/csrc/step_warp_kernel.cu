@@ -31,8 +31,39 @@
 #define STEP_SPIN_SLEEP 0 // nanoseconds a warp sleeps between two polls of the previous warp's carry word (A/B knob)
 #endif
 
+// Polling loops and warp convergence.  This kernel has no CTA barrier in its tile loop, and ptxas is told that the warp
+// index is warp-uniform (see the kernel's first lines), so it treats the whole tile loop as convergent: no BRA.DIV check
+// and no BSSY/BSYNC pair around the shuffles -- and none after the polling loops either, because a load of ONE address
+// by all lanes counts as a uniform value.  For the 16-byte status words that is not true on the hardware: a 128-bit
+// load of a warp is served in several passes, a store of the producer can land between two of them, and then some
+// lanes leave the loop one iteration before the others and the warp never reconverges (found the hard way: the launch
+// ran into the spin limit).  Polls of 16-byte words therefore take their exit condition through a warp vote -- all lanes
+// leave in the same iteration, every lane has seen the complete word.  RT_VOTE_POLLS selects the loops (bit 1: mbarrier
+// wait, 2: look-back word in global memory, 4: carry word in shared memory, 8: the 32-bit ring counters); measured on C4:
+// 4 alone +1.6 %, all four +0.4 % against the build with divergence checks.  Default: all four (the build the GPU suite
+// was run on); 1|2|4 leaves out the 32-bit counters, whose load is a single broadcast access.
+#ifndef RT_VOTE_POLLS
+#define RT_VOTE_POLLS 15
+#endif
+#ifndef RT_SPIN_SHIFT
+#define RT_SPIN_SHIFT 22 // log2 of the spin limit of the loops below (a diagnostic build with 40 hangs instead of trapping)
+#endif
+
 namespace rtk
 {
+template <int BIT>
+__device__ __forceinline__ bool poll_again(bool c)
+{
+   if (RT_VOTE_POLLS & BIT) return __any_sync(0xffffffffu, c);
+   return c;
+}
+constexpr long long SPIN_LIMIT_W = 1ll << RT_SPIN_SHIFT;
+__device__ __forceinline__ void mbar_wait_w(unsigned long long *bar, unsigned parity)
+{
+   long long spins = 0;
+   while (poll_again<1>(!mbar_try_wait(bar, parity)))
+      if (++spins > SPIN_LIMIT_W) __trap();
+}
 // packed per-row constants of a BDF2 step: 64 doubles.  The per-cell right-hand sides are FOLDED: with
 //   ru = q + c_uu x + c_uv y + p_uu X + p_uv Y + up1c up1 + up2c up2 ,  rv = q - c_uv x + c_uu y - p_uv X + p_uu Y ,
 //   beta = io ru + id rv ,  U = id ru - io rv      (x, y = X1 nodes ; X, Y = X2 nodes ; q = qa + qb (u+v))
@@ -162,7 +193,10 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
    __shared__ int s_decoded; // ring entries decoded by warp 0 so far
    __shared__ int s_done;    // tiles the last warp has finished
 
-   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+   // The warp index goes through a shuffle so that ptxas KNOWS it is warp-uniform: with `threadIdx.x >> 5` every branch on
+   // it counts as divergent, each shuffle below gets a BRA.DIV check with an out-of-line WARPSYNC.COLLECTIVE path, and the
+   // register constraints of those paths cost two moves per 64-bit shuffle in the main path (-30 % instructions, SASS).
+   const int lane = threadIdx.x & 31, warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
    const unsigned flag_incl = a.epoch * 2u + 2u;
    const long long total_tiles = (long long)a.n_chains * a.tiles_per_chain;
    const int half_m = a.M >> 1, dm = a.reflective_left ? half_m : a.M;
@@ -262,15 +296,15 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
          {
             // back-pressure: at most two tiles ahead of the last warp (bounds the carry and descriptor rings)
             long long spins = 0;
-            while (ld_flag(&s_done) < seq - 2)
-               if (++spins > SPIN_LIMIT) __trap();
+            while (poll_again<8>(ld_flag(&s_done) < seq - 2))
+               if (++spins > SPIN_LIMIT_W) __trap();
          }
       }
       else
       {
          long long spins = 0;
-         while ((avail = ld_flag(&s_decoded)) <= seq)
-            if (++spins > SPIN_LIMIT) __trap();
+         while (poll_again<8>((avail = ld_flag(&s_decoded)) <= seq))
+            if (++spins > SPIN_LIMIT_W) __trap();
          __threadfence_block();
       }
       const WarpTile ti = s_desc[seq & 15];
@@ -308,7 +342,7 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
          const bool first_sub = (warp == 0);                  // carry from the previous CTA tile / the boundary
          double2 *const carry_slot = &s_carry[seq & 3][0][0];
 
-         mbar_wait(&s_full[warp][buf], (phase >> buf) & 1u); // sub-tile, constants and halo cell have landed
+         mbar_wait_w(&s_full[warp][buf], (phase >> buf) & 1u); // sub-tile, constants and halo cell have landed
          phase ^= 1u << buf;
 
          const unsigned char *const sx = wt + buf * WT_BYTES;
@@ -333,10 +367,10 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
                w.y = __shfl_sync(0xffffffffu, wpre.y, k);
                if (ti.p == 0) return inflow0;
                long long spins = 0;
-               while ((int)(status_flag(w) - flag_incl) < 0)
+               while (poll_again<2>((int)(status_flag(w) - flag_incl) < 0))
                {
                   w = ld_status(status - 4 + k);
-                  if (++spins > SPIN_LIMIT) __trap();
+                  if (++spins > SPIN_LIMIT_W) __trap();
                }
                return junction ? kbc * w.x : w.x;
             }
@@ -344,13 +378,13 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
             const double2 *src = carry_slot + k * NW + (warp - 1);
             long long spins = 0;
             double2 w = lds_word(src);
-            while ((int)__double_as_longlong(w.y) != seq + 1)
+            while (poll_again<4>((int)__double_as_longlong(w.y) != seq + 1))
             {
 #if STEP_SPIN_SLEEP > 0
                __nanosleep(STEP_SPIN_SLEEP); // a polling warp competes for issue slots with the warps that do the work
 #endif
                w = lds_word(src);
-               if (++spins > SPIN_LIMIT) __trap();
+               if (++spins > SPIN_LIMIT_W) __trap();
             }
             return w.x;
          };
@@ -533,12 +567,14 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
                tma_store_3d(&maps.m[a.iout], 0, sub_start >> 3, ti.row, th); // cells past the row's end are clipped
                bulk_commit();
             }
+            __syncwarp(); // as below: no single-lane block at the end of a region
          }
       }
       if (NW > 1 && warp == NW - 1)
       {
          __syncwarp();
          if (lane == 0) st_flag(&s_done, seq + 1);
+         __syncwarp(); // reconverge BEFORE the back edge (a single-lane block that ends the loop body makes the whole loop divergent for ptxas)
       }
    }
    if (lane == 0) bulk_wait_read<0>();
