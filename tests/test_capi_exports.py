@@ -42,6 +42,24 @@ def test_library_is_sm100a_only(rt):
     assert archs == {"100a"}, archs
 
 
+def test_sweep_kernels_have_no_divergence_fallbacks(rt):
+    """The scans of the sweep kernels are warp shuffles in loops without a CTA barrier.  When ptxas cannot prove the
+    warp converged it wraps every shuffle in a BRA.DIV check with an out-of-line WARPSYNC.COLLECTIVE path (and pays two
+    register moves per 64-bit shuffle in the main path).  None of the library's kernels may contain one."""
+    out = subprocess.run(["cuobjdump", "-sass", rt.capi.LIB_PATH], capture_output=True, text=True)
+    if out.returncode != 0:
+        pytest.skip("cuobjdump not available")
+    per_kernel, name = {}, None
+    for ln in out.stdout.splitlines():
+        m = re.search(r"Function : (\S+)", ln)
+        if m:
+            name = m.group(1)
+        elif "BRA.DIV" in ln and name:
+            per_kernel[name] = per_kernel.get(name, 0) + 1
+    hot = {k: v for k, v in per_kernel.items() if re.search(r"(sweep|step|var_tile)_?\w*kernel", k)}
+    assert not hot, hot
+
+
 def test_struct_layout_matches_header(rt, tmp_path):
     """compile a C program against include/rt_cuda.h that prints sizeof/offsetof; compare with the ctypes mirrors"""
     prog = tmp_path / "layout.c"
