@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 3
+#define RT_ABI_VERSION 4
 
 typedef struct rt_params
 {
@@ -106,6 +106,8 @@ typedef struct rt_plan
    int step_tile_cells;  /* cells per ticket of the fused step kernel (sub-tile x chained warps)                 */
    int step_block;       /* threads per CTA of the fused step kernel                                             */
    int step_chain;       /* warps chained per CTA tile (1 for the CTA-wide tile shapes)                          */
+   int time_levels;      /* time-level buffers allocated: 2 for the fused step, 4 once a step has run stage by stage (ABI 4) */
+   int step_kernel;      /* fused step: 4 = one 4-vector scan per sub-tile (step4_kernel.cu), 1 = four scalar scans       */
 } rt_plan;
 
 const char *rt_last_error(void);

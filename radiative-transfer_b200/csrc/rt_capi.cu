@@ -62,6 +62,7 @@ struct rt_solver
    double *d_psi_source = nullptr, *d_bdry = nullptr;
    double *d_coef[3] = {nullptr, nullptr, nullptr}; // per stage kind: Gl*M entries of COEF_ENTRY_DOUBLES doubles
    double *d_coef_step = nullptr;                   // the three kinds packed per row (STEP_COEF_DOUBLES each)
+   double *d_coef4 = nullptr;                       // the same + chunk transfer matrices and responses (STEP4_COEF_DOUBLES each, step4_kernel.cu)
    double sums[3] = {0, 0, 0};
    // cell-dependent material fields (extension, var_kernel.cu): inputs, Planck per cell, per-cell tables [gl][c]
    bool var = false;
@@ -87,6 +88,8 @@ struct rt_solver
    int Gl = 0, Gb = 0, n_batches = 0, Np = 0;
    size_t buf_elems = 0; // double2 elements per time-level buffer
    double2 *E[4] = {nullptr, nullptr, nullptr, nullptr};
+   int plan_levels = 4;  // levels the batch size was planned for
+   int levels = 0;       // time-level buffers allocated so far: 2 for the fused step / BE / CN time stepping, the other two on demand
    SweepMaps maps[3]; // per stage kind (tile shapes may differ): tensor maps of E[0..3]
    SweepMaps maps_var; // tile shape of var_tile_kernel
    int i_ends = 0, i_prev = -1, i_half_neg = -1, i_half_pos = -1;
@@ -114,6 +117,11 @@ struct rt_solver
    double *d_step_phi[2] = {nullptr, nullptr};
    cudaEvent_t step_ev[2] = {nullptr, nullptr};
    int step_parity = 0;
+   // scalar intensity of every step from the fused step kernel itself (step4_kernel.cu, PHI): partial sums per run of rows
+   double *d_phi_part = nullptr;
+   long long phi_pitch = 0;   // cells per partial row (whole tiles)
+   int phi_run = 1;           // rows per run = tickets per draw: the largest divisor of M/2 that is <= 8
+   bool step_phi_fused = false; // the step just completed has left its partial sums in d_phi_part
    // timing
    rt_timing tm;
    std::vector<EventPair> ev_pool;
@@ -121,6 +129,7 @@ struct rt_solver
    bool timing_on = true;
    // fused BDF2-step kernel (step_kernel.cu): RT_CUDA_FUSED=0 runs every step stage by stage
    bool fused = true, fused_var = false, half_stale = false;
+   int step_kernel = 4;        // 4: one 4-vector scan per sub-tile (step4_kernel.cu, default) ; 1: four scalar scans (RT_CUDA_STEP_KERNEL=1)
    int step_threads = 32, step_cpt = 8, step_chain = 4, step_box_cells = 256, step_tile_cells = 1024, step_tiles_per_row = 0;
    SweepMaps maps_step;
    int ticket_batch = 8;       // tickets per atomic draw (RT_CUDA_TICKET_BATCH)
@@ -358,7 +367,8 @@ static int compute_group_tables(rt_solver *s)
       s->tm.kernel_launches++;
    }
    launch_pack_step_coef(s->d_coef[0], s->d_coef[1], s->d_coef[2], s->d_coef_step, s->Gl * p.M, corr, s->st);
-   s->tm.kernel_launches++;
+   launch_pack_step4_coef(s->d_coef[0], s->d_coef[1], s->d_coef[2], s->d_wt, s->d_coef4, s->Gl * p.M, p.M, corr, s->st);
+   s->tm.kernel_launches += 2;
    CK(cudaGetLastError());
    if (s->var && compute_var_tables(s, true)) return 1;
    return 0;
@@ -400,6 +410,23 @@ static int load_batch(rt_solver *s, int start)
    return 0;
 }
 
+// time-level buffers are allocated on demand: two for the fused step, four when a step runs stage by stage
+static int ensure_levels(rt_solver *s, int n)
+{
+   for (int k = s->levels; k < n; ++k)
+   {
+      if (pool_alloc(s, &s->E[k], s->buf_elems))
+         return fail("%s (time-level buffer %d of %d: %zu bytes -- half_ends / a stage-by-stage step need four levels; create the solver with "
+                     "RT_CUDA_LEVELS=4 or fewer groups per batch)", g_err.c_str(), k + 1, n, s->buf_elems * sizeof(double2));
+      const int rows = s->Gb * s->p.M;
+      for (int kind = 0; kind < 3; ++kind) CK(make_tile_map(&s->maps[kind].m[k], s->E[k], rows, s->Np, s->tile_cells[kind]));
+      CK(make_tile_map(&s->maps_step.m[k], s->E[k], rows, s->Np, s->step_box_cells));
+      if (s->var && s->var_threads > 0) CK(make_tile_map(&s->maps_var.m[k], s->E[k], rows, s->Np, s->var_threads * s->var_cpt));
+      s->levels = k + 1;
+   }
+   return 0;
+}
+
 extern "C" int rt_destroy(rt_solver *s)
 {
    if (!s) return 0;
@@ -409,7 +436,7 @@ extern "C" int rt_destroy(rt_solver *s)
                      s->d_dEB, s->d_dsig, s->d_dkap, s->d_cor1, s->d_cor2, s->d_cor3, s->d_sigma, s->d_srcB, s->d_de_ave,
                      s->d_sums, s->d_psi_source, s->d_bdry, s->d_phi, s->d_phip, s->d_F,
                      s->d_balance, s->d_left, s->d_right, s->d_stage, s->d_step_phi[0], s->d_step_phi[1],
-                     s->d_coef[0], s->d_coef[1], s->d_coef[2], s->d_coef_step};
+                     s->d_coef[0], s->d_coef[1], s->d_coef[2], s->d_coef_step, s->d_coef4, s->d_phi_part};
    for (double *t : tabs) if (t) cudaFree(t);
    double *vtabs[] = {s->d_rho_c, s->d_T_c, s->d_kappa_c, s->d_B_c, s->d_dBdT_c, s->d_vt[0], s->d_vt[1], s->d_vt[2], s->d_vt[3],
                       s->d_vt[4], s->d_edge_state[0], s->d_edge_state[1], s->d_edge_state[2], s->d_edge_state[3],
@@ -530,6 +557,10 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       s->step_tiles_per_row = (N + s->step_tile_cells - 1) / s->step_tile_cells;
       s->max_tiles_per_row = std::max(s->max_tiles_per_row, 4 * s->step_tiles_per_row); // 4 look-back words per tile
       if (s->var) s->max_tiles_per_row = std::max(s->max_tiles_per_row, 4 * ((N + 255) / 256)); // fused cell-dependent step, 256-cell tiles
+      if (const char *ke = getenv("RT_CUDA_STEP_KERNEL")) s->step_kernel = (atoi(ke) == 1) ? 1 : 4;
+      if (s->step_threads != 32 || s->step_cpt != 8 || !step4_chain_supported(s->step_chain)) s->step_kernel = 1;
+      for (int r = 1; r <= 8; ++r)
+         if ((M / 2) % r == 0) s->phi_run = r;
       const char *fe = getenv("RT_CUDA_FUSED");
       s->fused = !(fe && fe[0] == '0') && !s->var;
       // cell-dependent fields: the fused step of var_step_kernel.cu (RT_CUDA_FUSED=0 or RT_CUDA_VAR_FUSED=0: stage by stage)
@@ -562,6 +593,7 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
    CKD(dalloc(&s->d_balance, s->Gl)); CKD(dalloc(&s->d_left, s->Gl)); CKD(dalloc(&s->d_right, s->Gl));
    for (int k = 0; k < 3; ++k) CKD(dalloc(&s->d_coef[k], (size_t)s->Gl * M * COEF_ENTRY_DOUBLES));
    CKD(dalloc(&s->d_coef_step, (size_t)s->Gl * M * STEP_COEF_DOUBLES));
+   CKD(dalloc(&s->d_coef4, (size_t)s->Gl * M * STEP4_COEF_DOUBLES));
    CKD(dalloc(&s->d_ticket, 1));
    CKC(cudaMemsetAsync(s->d_ticket, 0, sizeof(unsigned long long), s->st));
    CKC(cudaMemsetAsync(s->d_B, 0, G * sizeof(double), s->st));
@@ -608,24 +640,31 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       CKD(upload(s, s->d_kappa_c, s->kappa_cell.data(), (size_t)G * N));
    }
 
-   // ---- memory plan: 4 time-level buffers of (u,v) per unknown + look-back state
+   // ---- memory plan: time-level buffers of (u,v) per unknown + look-back state + result / per-step output arrays.
+   // The fused BDF2 step reads ends^n and writes ends^(n+1): TWO levels (BE / CN time stepping likewise); the other two
+   // (half_ends, the stage-2 result) exist only when a step runs stage by stage -- RT_CUDA_FUSED=0, a partial step through
+   // rt_run_stages, rt_get_ends(which = 2) -- and are allocated on demand (ensure_levels).  C4 (2^20 x S16 x 256 groups)
+   // is 137 GB at two levels: one resident batch on a B200 instead of two.
    size_t free_b = 0, total_b = 0;
    CKC(cudaMemGetInfo(&free_b, &total_b));
    CKD(pool_setup(p->device));
    free_b += pool_idle_bytes(p->device);
-   const size_t per_group = (size_t)4 * M * s->Np * sizeof(double2) + (size_t)M * s->max_tiles_per_row * 20;
-   const size_t reserve = (size_t)1 << 30; // results staging, allocator slack
+   int plan_levels = (p->ts_method != 3 || s->fused || s->fused_var) ? 2 : 4;
+   if (const char *le = getenv("RT_CUDA_LEVELS"))
+      if (atoi(le) == 4) plan_levels = 4;
+   s->plan_levels = plan_levels;
+   s->phi_pitch = (long long)s->step_tiles_per_row * s->step_tile_cells;
+   const size_t phi_slots = (size_t)(M / 2) / s->phi_run;
+   // per resident group: state, look-back words, per-step output staging (2 x phi) and its partial sums
+   const size_t per_group = (size_t)plan_levels * M * s->Np * sizeof(double2) + (size_t)M * s->max_tiles_per_row * 20 +
+                            (size_t)2 * N * sizeof(double) + 2 * phi_slots * (size_t)s->phi_pitch * sizeof(double);
+   const size_t keep = (size_t)3 * s->Gl * N * sizeof(double); // phi / phi_plus / F of every owned group
+   const size_t reserve = (size_t)1 << 30; // layout-conversion staging, allocator slack
    int gb = p->groups_per_batch;
    if (gb <= 0)
    {
-      const size_t usable = free_b > reserve ? free_b - reserve : free_b / 2;
-      size_t fit = usable / per_group;
-      // when the groups do not all fit, phi/phi_plus/F of every owned group are retained on the device as well
-      if (fit < (size_t)s->Gl)
-      {
-         const size_t keep = (size_t)3 * s->Gl * N * sizeof(double);
-         fit = usable > keep ? (usable - keep) / per_group : 0;
-      }
+      const size_t usable = free_b > reserve + keep ? free_b - reserve - keep : free_b / 2;
+      const size_t fit = usable / per_group;
       gb = (int)std::min<size_t>(fit, (size_t)s->Gl);
       if (gb < 1) { fail("rt_create: not even one group (%zu bytes) fits in %zu free bytes", per_group, free_b); rt_destroy(s); return 1; }
       // balance the batches: same number of batches, equal sizes
@@ -642,13 +681,7 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
    s->Gb = gb;
    s->n_batches = (s->Gl + gb - 1) / gb;
    s->buf_elems = (size_t)gb * M * s->Np;
-   for (int k = 0; k < 4; ++k)
-   {
-      CKD(pool_alloc(s, &s->E[k], s->buf_elems));
-      for (int kind = 0; kind < 3; ++kind) CKC(make_tile_map(&s->maps[kind].m[k], s->E[k], gb * M, s->Np, s->tile_cells[kind]));
-      CKC(make_tile_map(&s->maps_step.m[k], s->E[k], gb * M, s->Np, s->step_box_cells));
-      if (s->var && s->var_threads > 0) CKC(make_tile_map(&s->maps_var.m[k], s->E[k], gb * M, s->Np, s->var_threads * s->var_cpt));
-   }
+   CKD(ensure_levels(s, plan_levels));
    if (s->var && s->var_threads > 0)
       for (int k = 0; k < 5; ++k) // a table row as pitch/2 16-byte "cells": the same 128-byte-swizzled box as a time-level tile
          CKC(make_tile_map(&s->mat_maps.m[k], s->d_vt[k], 2 * s->Gl, s->vt_pitch / 2, s->var_threads * s->var_cpt / 2));
@@ -682,8 +715,10 @@ extern "C" int rt_get_plan(const rt_solver *s, rt_plan *plan)
    plan->step_tile_cells = s->var ? s->var_threads * s->var_cpt : s->step_tile_cells;
    plan->step_block = s->var ? s->var_threads : s->step_threads * s->step_chain;
    plan->step_chain = s->var ? 1 : s->step_chain;
-   plan->bytes_per_group = (size_t)4 * s->p.M * s->Np * sizeof(double2);
-   plan->state_bytes = 4 * s->buf_elems * sizeof(double2);
+   plan->bytes_per_group = (size_t)s->plan_levels * s->p.M * s->Np * sizeof(double2);
+   plan->state_bytes = (size_t)s->levels * s->buf_elems * sizeof(double2);
+   plan->time_levels = s->levels;
+   plan->step_kernel = s->step_kernel;
    cudaSetDevice(s->p.device);
    cudaMemGetInfo(&plan->free_bytes, &plan->total_bytes);
    return 0;
@@ -786,11 +821,14 @@ static int launch_stage(rt_solver *s, int kind, int i1n, int i1p, int i2, int ic
    return 0;
 }
 
+static int materialize_half(rt_solver *s);
+
 // one stage sweep of the batch currently on the device
 static int run_one_stage(rt_solver *s)
 {
    const rt_params &p = s->p;
    const int it = s->stages_done;
+   if (ensure_levels(s, p.ts_method == 3 ? 4 : 2)) return 1;
    int kind, out;
    int i1n, i1p, i2 = -1, ic = -1; // buffer indices: X1 for mu<0 / mu>0 rows, X2, XC
    if (p.ts_method == 1)
@@ -812,6 +850,9 @@ static int run_one_stage(rt_solver *s)
       switch (it % 4)
       {
       case 0: // BE predictor; prev_ends = ends
+         // after a fused step half_ends exists only on demand; the reference keeps step n's half_ends until stage 1 of step
+         // n+1 overwrites it, so it has to be materialised now, while prev_ends^n (its input) is still intact
+         if (s->half_stale && materialize_half(s)) return 1;
          kind = KIND_BE;
          out = pick_free(s->i_ends, s->i_half_neg, s->i_half_pos, -1);
          i1n = i1p = s->i_ends;
@@ -845,6 +886,7 @@ static int run_one_stage(rt_solver *s)
    if (launch_stage(s, kind, i1n, i1p, i2, ic, out, true)) return 1;
    s->i_ends = out;
    s->stages_done++;
+   s->step_phi_fused = false;
    s->results_valid = false;
    return 0;
 }
@@ -857,15 +899,24 @@ static int run_fused_step(rt_solver *s)
 {
    if (s->var) return run_fused_step_var(s);
    const rt_params &p = s->p;
+   if (ensure_levels(s, 2)) return 1;
    const int in = s->i_ends, out = pick_free(in, -1, -1, -1);
+   // the per-step scalar intensity rides along in the one-scan kernel: partial sums of w_m psi per run of rows
+   const bool v4 = s->step_kernel == 4;
+   const bool phi = v4 && s->step_phi_host && s->step_group_major && s->d_phi_part;
    StepArgs a;
    a.x = s->E[in];
    a.ix = in; a.iout = out;
    for (int k = 0; k < 3; ++k)
       a.coef[k] = reinterpret_cast<const double2 *>(s->d_coef[k] + (size_t)s->batch_start * p.M * COEF_ENTRY_DOUBLES);
    a.coef_step = s->d_coef_step + (size_t)s->batch_start * p.M * STEP_COEF_DOUBLES;
+   a.coef4 = s->d_coef4 + (size_t)s->batch_start * p.M * STEP4_COEF_DOUBLES;
+   a.phi_part = phi ? s->d_phi_part : nullptr;
+   a.phi_pitch = s->phi_pitch;
+   a.phi_slots = (p.M / 2) / s->phi_run;
    a.tile_status = s->d_tile_status;
-   const int tb = std::min(s->ticket_batch, 8); // the warp-tile kernel decodes a batch with 8 lanes at most
+   // tickets per draw: the warp-tile kernels decode a batch with 8 lanes at most; with PHI a draw is one run of rows
+   const int tb = phi ? s->phi_run : std::min(s->ticket_batch, 8);
    a.ticket = s->d_ticket; a.ticket_base = s->ticket_base; a.ticket_batch = tb;
    a.epoch = ++s->epoch;
    a.M = p.M; a.N = p.N; a.Np = s->Np;
@@ -879,7 +930,8 @@ static int run_fused_step(rt_solver *s)
    EventPair *ep;
    if (event_begin(s, 4, &ep)) return 1;
    int grid = 0;
-   CK(launch_step(corr, s->step_threads, s->step_cpt, s->step_chain, s->maps_step, a, s->num_sms, s->st, &grid));
+   if (v4) CK(launch_step4(corr, phi, s->step_chain, s->maps_step, a, s->num_sms, s->st, &grid));
+   else CK(launch_step(corr, s->step_threads, s->step_cpt, s->step_chain, s->maps_step, a, s->num_sms, s->st, &grid));
    if (event_end(s, ep)) return 1;
    const unsigned long long total_tiles = (unsigned long long)a.n_chains * a.tiles_per_chain;
    s->ticket_base += (total_tiles + tb - 1) / tb + (unsigned long long)grid;
@@ -889,6 +941,7 @@ static int run_fused_step(rt_solver *s)
    s->i_ends = out;
    s->i_half_neg = s->i_half_pos = -1;
    s->half_stale = true;
+   s->step_phi_fused = phi;
    s->stages_done += 4;
    s->tm.step_launches++;
    s->tm.kernel_launches++;
@@ -950,6 +1003,7 @@ static int run_fused_step_var(rt_solver *s)
 static int materialize_half(rt_solver *s)
 {
    if (!s->half_stale) return 0;
+   if (ensure_levels(s, 4)) return 1;
    const int A = s->i_prev, C = pick_free(s->i_ends, A, -1, -1), D = pick_free(s->i_ends, A, C, -1);
    if (A < 0 || C < 0 || D < 0) return fail("internal: cannot re-materialise half_ends");
    if (launch_stage(s, KIND_BE, A, A, -1, -1, C, false)) return 1;
@@ -970,6 +1024,10 @@ static int ensure_result_arrays(rt_solver *s);
 static int temperature_update(rt_solver *s)
 {
    const rt_params &p = s->p;
+   if (s->Gl < p.G && !s->allreduce)
+      return fail("rt: this handle owns groups [%d,%d) of %d and the material-temperature update (cv > 0) sums absorption and emission "
+                  "over ALL groups: set the exchange with rt_set_allreduce (or create the handle with device_count > 1) -- refusing to "
+                  "update T from a partial sum", p.group_begin, p.group_begin + s->Gl, p.G);
    if (ensure_result_arrays(s)) return 1;
    EventPair *ep;
    if (event_begin(s, 5, &ep)) return 1;
@@ -1305,6 +1363,13 @@ extern "C" int rt_set_step_output(rt_solver *s, double *phi_host, int group_majo
          if (!s->d_step_phi[k]) { if (dalloc(&s->d_step_phi[k], n)) return 1; }
          if (!s->step_ev[k]) CK(cudaEventCreateWithFlags(&s->step_ev[k], cudaEventDisableTiming));
       }
+      // the one-scan step kernel adds up w_m psi itself (RT_CUDA_STEP_PHI=0: separate moments pass over the state)
+      const char *pe = getenv("RT_CUDA_STEP_PHI");
+      if (group_major && s->fused && s->step_kernel == 4 && s->p.ts_method == 3 && !(pe && pe[0] == '0') && !s->d_phi_part)
+      {
+         const size_t np = (size_t)s->Gb * 2 * ((size_t)(s->p.M / 2) / s->phi_run) * (size_t)s->phi_pitch;
+         if (dalloc(&s->d_phi_part, np)) return 1;
+      }
    }
    return 0;
 }
@@ -1321,7 +1386,11 @@ static int step_output(rt_solver *s)
       CK(cudaStreamWaitEvent(s->st, s->step_ev[k], 0));
       EventPair *ep;
       if (event_begin(s, 3, &ep)) return 1;
-      launch_moments(s->E[s->i_ends], s->d_mu, s->d_wt, p.M, p.N, s->Np, s->batch_groups, s->d_step_phi[k], nullptr, nullptr, s->st);
+      if (s->step_phi_fused)
+         launch_phi_combine(s->d_phi_part, s->phi_pitch, (p.M / 2) / s->phi_run, p.N, s->batch_groups, s->d_step_phi[k], s->st);
+      else
+         launch_moments(s->E[s->i_ends], s->d_mu, s->d_wt, p.M, p.N, s->Np, s->batch_groups, s->d_step_phi[k], nullptr, nullptr, s->st);
+      s->step_phi_fused = false;
       if (event_end(s, ep)) return 1;
       s->tm.kernel_launches++;
       cudaEvent_t done;

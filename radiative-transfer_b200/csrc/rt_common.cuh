@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+
 namespace rtk
 {
 // Physical constants, bit-identical to the reference's (include/Constants.h:9-23).
@@ -31,6 +33,23 @@ constexpr double VALIDATION_TOL = 1.e-6;
 
 
 enum StageKind : int { KIND_BE = 0, KIND_CN = 1, KIND_BDF = 2 };
+
+constexpr int RT_MAX_DEVICES = 64;    // per-device launch configuration caches (shared-memory opt-in, occupancy)
+// Launch plans (shared-memory opt-in, resident CTAs per SM) are cached PER DEVICE: cudaFuncAttributeMaxDynamicSharedMemorySize
+// is a per-device attribute, and one process may own handles on several GPUs (rt_params::device, device_count).
+struct DevicePlanCache
+{
+   std::atomic<int> v[RT_MAX_DEVICES]; // 0 = not planned on that device yet (static storage: zero-initialised)
+};
+inline cudaError_t device_plan_slot(DevicePlanCache &c, std::atomic<int> **slot)
+{
+   int dev = 0;
+   const cudaError_t e = cudaGetDevice(&dev);
+   if (e != cudaSuccess) return e;
+   if (dev < 0 || dev >= RT_MAX_DEVICES) return cudaErrorInvalidDevice;
+   *slot = &c.v[dev];
+   return cudaSuccess;
+}
 
 constexpr int COEF_ENTRY_DOUBLES = 18; // sizeof(RowCoef) / 8 (sweep_kernel.cu)
 

@@ -327,10 +327,13 @@ __global__ void __launch_bounds__(THREADS, (THREADS * CPT == 512) ? 384 / THREAD
 template <bool CORR, int THREADS, int CPT>
 static cudaError_t launch_one(const SweepMaps &maps, const StepArgs &a, int num_sms, cudaStream_t st, int *grid_out)
 {
-   static int ctas_per_sm = -1;
+   static DevicePlanCache plans;
+   std::atomic<int> *plan_slot = nullptr;
+   if (cudaError_t e0 = device_plan_slot(plans, &plan_slot)) return e0;
+   int ctas_per_sm = plan_slot->load(std::memory_order_acquire);
    auto kern = step_kernel<CORR, THREADS, CPT>;
    const size_t smem = (size_t)4 * TileShape<THREADS, CPT>::TILE_BYTES + 1024; // 2 X + S0 + S1 + alignment slack
-   if (ctas_per_sm < 0)
+   if (ctas_per_sm <= 0)
    {
       cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (e != cudaSuccess) return e;
@@ -338,6 +341,7 @@ static cudaError_t launch_one(const SweepMaps &maps, const StepArgs &a, int num_
       e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, THREADS, smem);
       if (e != cudaSuccess) return e;
       ctas_per_sm = occ > 0 ? occ : 1;
+      plan_slot->store(ctas_per_sm, std::memory_order_release);
    }
    const long long total = (long long)a.n_chains * a.tiles_per_chain;
    long long grid = (long long)num_sms * ctas_per_sm;

@@ -22,9 +22,15 @@ struct StepArgs
    int reflective_left;
    int n_chains, tiles_per_chain;
    int l2_prefetch;
+   // one-scan kernel (step4_kernel.cu)
+   const double *coef4;  // packed row constants, STEP4_COEF_DOUBLES each: stage constants, T^(2^s), response R
+   double *phi_part;     // PHI: partial sums of w_m psi per run of rows [(gl*2 + sign)*phi_slots + slot][phi_pitch], sweep order
+   long long phi_pitch;  // cells per partial row: whole tiles (tiles_per_row * tile cells)
+   int phi_slots;        // runs per (group, sign): (M/2) / ticket_batch
 };
 
 constexpr int STEP_COEF_DOUBLES = 64; // packed BE + CN + BDF constants of one row (step_warp_kernel.cu)
+constexpr int STEP4_COEF_DOUBLES = 160; // the same + chunk transfer matrices + stage-3 response (step4_kernel.cu)
 
 // threads = 32: one warp per tile (step_warp_kernel.cu, the default); 64 / 128: CTA-wide tiles (step_kernel.cu)
 bool step_shape_supported(int threads, int cpt);
@@ -36,4 +42,14 @@ cudaError_t launch_step_warp(bool corr, int cpt, int chain_warps, const SweepMap
 // chain_warps only matters for threads = 32.
 cudaError_t launch_step(bool corr, int threads, int cpt, int chain_warps, const SweepMaps &maps, const StepArgs &a, int num_sms,
                         cudaStream_t st, int *grid_out);
+
+// ---- step4_kernel.cu: the fused step with ONE 4-vector scan per sub-tile (default)
+bool step4_chain_supported(int chain_warps); // 2, 4 or 8 warps (consecutive 256-cell sub-tiles) per CTA tile
+void launch_pack_step4_coef(const double *be, const double *cn, const double *bdf, const double *wt, double *out, int rows, int M, bool corr,
+                            cudaStream_t st);
+// phi: accumulate w_m psi of the step's result per run of a.ticket_batch rows into a.phi_part (a.ticket_batch must divide M/2)
+cudaError_t launch_step4(bool corr, bool phi, int chain_warps, const SweepMaps &maps, const StepArgs &a, int num_sms, cudaStream_t st,
+                         int *grid_out);
+// phi[gl][c] from the partial sums of one step4 launch
+void launch_phi_combine(const double *part, long long pitch, int slots, int N, int groups, double *phi, cudaStream_t st);
 } // namespace rtk

@@ -58,6 +58,7 @@ __device__ __forceinline__ bool poll_again(bool c)
    return c;
 }
 constexpr long long SPIN_LIMIT_W = 1ll << RT_SPIN_SHIFT;
+constexpr long long SPIN_LIMIT_S = 1ll << (RT_SPIN_SHIFT + 3); // shared-memory polls turn around ~8x quicker than global ones
 __device__ __forceinline__ void mbar_wait_w(unsigned long long *bar, unsigned parity)
 {
    long long spins = 0;
@@ -191,7 +192,7 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
    __shared__ __align__(16) WarpTile s_desc[16];
    __shared__ __align__(8) unsigned long long s_full[NW][2];
    __shared__ int s_decoded; // ring entries decoded by warp 0 so far
-   __shared__ int s_done;    // tiles the last warp has finished
+   __shared__ int s_done[NW]; // tiles each warp has finished or sat out (a row may end before a warp's sub-tile)
 
    // The warp index goes through a shuffle so that ptxas KNOWS it is warp-uniform: with `threadIdx.x >> 5` every branch on
    // it counts as divergent, each shuffle below gets a BRA.DIV check with an out-of-line WARPSYNC.COLLECTIVE path, and the
@@ -278,7 +279,8 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
    if (NW > 1)
    {
       for (int i = threadIdx.x; i < 4 * 4 * NW; i += 32 * NW) (&s_carry[0][0][0])[i] = make_double2(0.0, 0.0);
-      if (threadIdx.x == 0) { s_decoded = 0; s_done = 0; }
+      if (threadIdx.x == 0) s_decoded = 0;
+      if (threadIdx.x < NW) s_done[threadIdx.x] = 0;
       __syncthreads(); // the only CTA-wide barrier
    }
    else __syncwarp();
@@ -294,17 +296,19 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
          avail = dec;
          if (NW > 1)
          {
-            // back-pressure: at most two tiles ahead of the last warp (bounds the carry and descriptor rings)
+            // back-pressure: at most two tiles ahead of the SLOWEST warp (bounds the carry and descriptor rings).  Every warp
+            // counts its own tiles: with one counter written by the last warp, a tile that warp sits out (row ends earlier)
+            // let warp 0 run ahead of the warps that were still working and overwrite their carry slots.
             long long spins = 0;
-            while (poll_again<8>(ld_flag(&s_done) < seq - 2))
-               if (++spins > SPIN_LIMIT_W) __trap();
+            while (__any_sync(0xffffffffu, ld_flag(&s_done[lane % NW]) < seq - 2))
+               if (++spins > SPIN_LIMIT_S) __trap();
          }
       }
       else
       {
          long long spins = 0;
          while (poll_again<8>((avail = ld_flag(&s_decoded)) <= seq))
-            if (++spins > SPIN_LIMIT_W) __trap();
+            if (++spins > SPIN_LIMIT_S) __trap();
          __threadfence_block();
       }
       const WarpTile ti = s_desc[seq & 15];
@@ -384,7 +388,7 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
                __nanosleep(STEP_SPIN_SLEEP); // a polling warp competes for issue slots with the warps that do the work
 #endif
                w = lds_word(src);
-               if (++spins > SPIN_LIMIT_W) __trap();
+               if (++spins > SPIN_LIMIT_S) __trap();
             }
             return w.x;
          };
@@ -570,10 +574,10 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
             __syncwarp(); // as below: no single-lane block at the end of a region
          }
       }
-      if (NW > 1 && warp == NW - 1)
+      if (NW > 1)
       {
          __syncwarp();
-         if (lane == 0) st_flag(&s_done, seq + 1);
+         if (lane == 0) st_flag(&s_done[warp], seq + 1);
          __syncwarp(); // reconverge BEFORE the back edge (a single-lane block that ends the loop body makes the whole loop divergent for ptxas)
       }
    }
@@ -584,10 +588,13 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
 template <bool CORR, int CPT, int NW>
 static cudaError_t launch_warp_one(const SweepMaps &maps, const StepArgs &a, int num_sms, cudaStream_t st, int *grid_out)
 {
-   static int ctas_per_sm = -1;
+   static DevicePlanCache plans;
+   std::atomic<int> *plan_slot = nullptr;
+   if (cudaError_t e0 = device_plan_slot(plans, &plan_slot)) return e0;
+   int ctas_per_sm = plan_slot->load(std::memory_order_acquire);
    auto kern = step_warp_kernel<CORR, CPT, NW>;
    const size_t smem = (size_t)NW * 3 * 32 * CPT * 16 + 1024; // per warp 2 X + H/OUT, + alignment slack
-   if (ctas_per_sm < 0)
+   if (ctas_per_sm <= 0)
    {
       cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (e != cudaSuccess) return e;
@@ -595,9 +602,10 @@ static cudaError_t launch_warp_one(const SweepMaps &maps, const StepArgs &a, int
       e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32 * NW, smem);
       if (e != cudaSuccess) return e;
       ctas_per_sm = occ > 0 ? occ : 1;
-      const char *cap = getenv("RT_CUDA_STEP_CTAS"); // resident CTAs per SM (experiments)
-      if (cap && atoi(cap) >= 1 && atoi(cap) < ctas_per_sm) ctas_per_sm = atoi(cap);
+      plan_slot->store(ctas_per_sm, std::memory_order_release);
    }
+   const char *cap = getenv("RT_CUDA_STEP_CTAS"); // resident CTAs per SM (experiments)
+   if (cap && atoi(cap) >= 1 && atoi(cap) < ctas_per_sm) ctas_per_sm = atoi(cap);
    const long long total = (long long)a.n_chains * a.tiles_per_chain;
    long long grid = (long long)num_sms * ctas_per_sm;
    if (grid > total) grid = total;

@@ -490,11 +490,15 @@ template <int KIND, bool CORR, int THREADS, int CPT>
 static cudaError_t launch_one(int ring_pref, const SweepMaps &maps, const SweepArgs &a, int num_sms, cudaStream_t st, int *grid_out)
 {
    // plan once per instantiation: X1 ring depth and resident CTAs per SM
-   static int ctas_per_sm = -1, ring = 3;
+   static DevicePlanCache plans; // per device: ctas_per_sm * 8 + ring
+   std::atomic<int> *plan_slot = nullptr;
+   if (cudaError_t e0 = device_plan_slot(plans, &plan_slot)) return e0;
+   const int packed = plan_slot->load(std::memory_order_acquire);
+   int ctas_per_sm = packed >> 3, ring = packed & 7;
    auto k3 = sweep_kernel<KIND, CORR, THREADS, CPT, 3>;
    auto k2 = sweep_kernel<KIND, CORR, THREADS, CPT, 2>;
    const size_t s3 = smem_bytes<KIND, CORR, THREADS, CPT, 3>(), s2 = smem_bytes<KIND, CORR, THREADS, CPT, 2>();
-   if (ctas_per_sm < 0)
+   if (packed <= 0)
    {
       cudaError_t e = cudaFuncSetAttribute(k3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s3);
       if (e != cudaSuccess) return e;
@@ -511,6 +515,7 @@ static cudaError_t launch_one(int ring_pref, const SweepMaps &maps, const SweepA
       if (ring_pref == 2 || ring_pref == 3) ring = ring_pref;
       ctas_per_sm = (ring == 2) ? o2 : o3;
       if (ctas_per_sm < 1) ctas_per_sm = 1;
+      plan_slot->store(ctas_per_sm * 8 + ring, std::memory_order_release);
    }
    const long long total = (long long)a.n_chains * a.tiles_per_chain;
    long long grid = (long long)num_sms * ctas_per_sm;

@@ -355,10 +355,13 @@ template <bool CORR, int THREADS, int CPT, int MB>
 static cudaError_t var_step_launch_one(const SweepMaps &maps, const MatMaps &mats, const VarStepArgs &va, int num_sms, cudaStream_t st,
                                        int *grid_out)
 {
-   static int ctas_per_sm = -1;
+   static DevicePlanCache plans;
+   std::atomic<int> *plan_slot = nullptr;
+   if (cudaError_t e0 = device_plan_slot(plans, &plan_slot)) return e0;
+   int ctas_per_sm = plan_slot->load(std::memory_order_acquire);
    auto kern = var_step_kernel<CORR, THREADS, CPT, MB>;
    const size_t smem = (size_t)var_step_smem_bytes<CORR, THREADS, CPT, MB>();
-   if (ctas_per_sm < 0)
+   if (ctas_per_sm <= 0)
    {
       cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (e != cudaSuccess) return e;
@@ -366,6 +369,7 @@ static cudaError_t var_step_launch_one(const SweepMaps &maps, const MatMaps &mat
       e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, THREADS, smem);
       if (e != cudaSuccess) return e;
       ctas_per_sm = occ > 0 ? occ : 1;
+      plan_slot->store(ctas_per_sm, std::memory_order_release);
    }
    const long long total = (long long)va.s.n_chains * va.s.tiles_per_chain;
    long long grid = (long long)num_sms * ctas_per_sm;

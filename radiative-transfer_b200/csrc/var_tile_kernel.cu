@@ -317,10 +317,13 @@ template <int KIND, bool CORR, int THREADS, int CPT>
 static cudaError_t var_launch_one(const SweepMaps &maps, const MatMaps &mats, const VarTileArgs &va, int num_sms, cudaStream_t st,
                                   int *grid_out)
 {
-   static int ctas_per_sm = -1;
+   static DevicePlanCache plans;
+   std::atomic<int> *plan_slot = nullptr;
+   if (cudaError_t e0 = device_plan_slot(plans, &plan_slot)) return e0;
+   int ctas_per_sm = plan_slot->load(std::memory_order_acquire);
    auto k = var_tile_kernel<KIND, CORR, THREADS, CPT>;
    const size_t sm = (size_t)var_smem_bytes<KIND, CORR, THREADS, CPT>();
-   if (ctas_per_sm < 0)
+   if (ctas_per_sm <= 0)
    {
       cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
       if (e != cudaSuccess) return e;
@@ -328,6 +331,7 @@ static cudaError_t var_launch_one(const SweepMaps &maps, const MatMaps &mats, co
       e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k, THREADS, sm);
       if (e != cudaSuccess) return e;
       ctas_per_sm = occ < 1 ? 1 : occ;
+      plan_slot->store(ctas_per_sm, std::memory_order_release);
    }
    const long long total = (long long)va.s.n_chains * va.s.tiles_per_chain;
    long long grid = (long long)num_sms * ctas_per_sm;
