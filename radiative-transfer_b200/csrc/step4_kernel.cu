@@ -255,6 +255,7 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step4_kernel(const __grid_co
    __shared__ __align__(8) unsigned long long s_full[NW][2];
    __shared__ __align__(8) unsigned long long s_cfull[3];
    __shared__ int s_decoded;  // ring entries decoded by warp 0 so far
+   __shared__ int s_cissued;  // tiles whose row constants warp 0 has requested so far (the other warps never run ahead of it)
    __shared__ int s_done[NW]; // tiles each warp has finished (or sat out)
 
    // warp index through a shuffle: ptxas then KNOWS it is warp-uniform (step_warp_kernel.cu, "convergence is stated")
@@ -349,7 +350,7 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step4_kernel(const __grid_co
    }
    for (int i = threadIdx.x; i < 4 * 4 * NW; i += 32 * NW) (&s_carry[0][0][0])[i] = make_double2(0.0, 0.0);
    if (threadIdx.x < NW) s_done[threadIdx.x] = 0;
-   if (threadIdx.x == 0) s_decoded = 0;
+   if (threadIdx.x == 0) { s_decoded = 0; s_cissued = 0; }
    __syncthreads(); // the only CTA-wide barrier
 
    double acc[CPT]; // PHI: sum over the run's rows of w_m psi at this lane's cells
@@ -376,12 +377,23 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step4_kernel(const __grid_co
       }
       else
       {
+         // wait until warp 0 has requested this tile's row constants (hence decoded it).  Waiting for the decode alone is not
+         // enough: a warp that sits tiles out (row ends before its sub-tile) would run ahead of warp 0 and find the
+         // constants' mbarrier in an OLDER phase of the same parity -- and take the stale entry for the new one.
          long long spins = 0;
-         while (again((avail = ld_flag(&s_decoded)) <= seq))
+         while (again(ld_flag(&s_cissued) <= seq))
             if (++spins > SPIN_SHARED) __trap();
+         avail = ld_flag(&s_decoded); // the warp's own tile loads may run ahead as far as the descriptors are decoded
          __threadfence_block();
       }
       const Tile ti = s_desc[seq & 15];
+      if (NW > 1 && warp == 0 && ti.row < 0)
+      {
+         // no more tiles: release the warps waiting for this tile's constants (a CTA that drew no tile at all never gets
+         // to the publishing store below)
+         if (lane == 0) st_flag(&s_cissued, 0x7fffffff);
+         __syncwarp();
+      }
       if (ti.row < 0) break;
       // warp 0: probe the predecessor tile's four look-back words first of all (lane k holds the word of stage k), so
       // that the L2 round trip overlaps the issue of the next tile's loads and pass A
@@ -407,6 +419,15 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step4_kernel(const __grid_co
          ++issued;
       }
       __syncwarp();
+      if (NW > 1 && warp == 0)
+      {
+         if (lane == 0)
+         {
+            __threadfence_block();
+            st_flag(&s_cissued, issued);
+         }
+         __syncwarp();
+      }
       const int tile_start = (ti.tf >> 4) * TILE, sub_start = tile_start + warp * WT;
       const int valid_total = min(TILE, a.N - tile_start);
       const int valid = min(WT, valid_total - warp * WT); // cells of this warp's sub-tile inside the row (<= 0: none)

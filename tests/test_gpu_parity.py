@@ -163,7 +163,10 @@ def test_step_output_matches_moments(rt):
         buf = np.zeros((p.G, p.N))
         s.set_step_output(buf.ctypes.data_as(C.c_void_p), True)
         s.solve()
-        assert np.array_equal(buf, s.moments_group_major()[0])
+        # the step kernel adds up w_m psi itself (per run of rows and per sign, then a combine): the same M terms as the
+        # moments pass (ascending m, solver.cpp:191-204) in another association -> equal to rounding, not bit for bit
+        from parity_util import state_err
+        assert state_err(buf, s.moments_group_major()[0], group_axis=0) <= 1e-13
 
 
 def test_validation_failure_is_loud(rt):

@@ -122,7 +122,9 @@ def test_step_phi_from_the_step_kernel(rt, monkeypatch, M, bcl, N):
     p = synthetic_parameters(rt, M=M, G=5, N=N, dt=1e-3, V=1.0, steps=3, bc_left=bcl, bc_right=1)
     fused, phi, tm = _solve_with_step_output(rt, p, True, monkeypatch)
     staged, phi2, _ = _solve_with_step_output(rt, p, False, monkeypatch)
-    assert np.array_equal(phi, phi2)          # the state itself does not depend on who sums phi
+    # the state itself does not depend on who sums phi (the PHI / non-PHI instantiations are separate compilations of the
+    # kernel and may contract multiply-adds differently: agreement to rounding, not bitwise)
+    assert state_err(phi, phi2, group_axis=0) <= 1e-13, state_err(phi, phi2, group_axis=0)
     assert np.array_equal(staged, phi2)       # the moments pass of the last step is the final phi
     assert state_err(fused, phi, group_axis=0) <= 1e-13, state_err(fused, phi, group_axis=0)
     assert np.isfinite(fused).all()
