@@ -182,6 +182,18 @@ int rt_reset_timing(rt_solver *s);
 int rt_planck_groups(int device, int G, const double *e_edge, int ncell, const double *T, double *B, double *dBdT,
                      double *kernel_ms);
 
+/* NO COUNTERPART IN THE REFERENCE.  rt_planck_groups for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it): same inputs,
+ * same outputs (HOST pointers; B, dBdT are [ncell][G], g fastest), same kernels, but it calls no cudaMalloc / cudaFree /
+ * allocating library routine.  Its device scratch (copies of e_edge and T, the kernel's two group-major tables, the
+ * staging of the layout conversion) is ONE static device array of RT_NOALLOC_MAX_DOUBLES doubles (8 MiB) that every GPU
+ * which loads the library holds until the process exits.  Limit: 3*G*ncell + G + 1 + ncell doubles (each part rounded up
+ * to 32) must fit, e.g. 256 groups x 1024 temperatures; larger requests fail with a message and nothing is computed.
+ * All calls share the array and it keeps the last call's contents (the tables are cleared at the start of every call):
+ * calls that overlap on one GPU -- two host threads, two streams -- RACE; serialise them.  The call is synchronous. */
+#define RT_NOALLOC_MAX_DOUBLES (1 << 20)
+int rt_planck_groups_noalloc(int device, int G, const double *e_edge, int ncell, const double *T, double *B, double *dBdT);
+
 /* Correction::generate_multigroup_opacities (correction.cpp:66-97; kept by the reference but never called -- second
  * statement tests/test_planckian.cpp:267-349): Planck-weighted group opacities at temperature T normalised so that
  * sum_g kappa_g B_g = kappa_grey a c T^4.  Outputs are G long, any may be NULL. */

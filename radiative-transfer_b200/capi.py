@@ -24,6 +24,7 @@ EXPORTS = (
     "rt_moments_group_major", "rt_balance", "rt_group_ends", "rt_get_group_terms", "rt_get_psi_source",
     "rt_validate", "rt_set_step_output", "rt_get_timing", "rt_reset_timing", "rt_planck_groups", "rt_bench_steps",
     "rt_host_alloc", "rt_host_free", "rt_multigroup_opacities", "rt_set_allreduce", "rt_get_temperature",
+    "rt_planck_groups_noalloc",
 )
 
 #: int fn(void *device_buf, size_t count, void *cuda_stream, void *user)  (include/rt_cuda.h: rt_allreduce_fn)
@@ -111,6 +112,7 @@ def lib():
         L.rt_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
         L.rt_host_free.argtypes = [C.c_void_p]
         L.rt_planck_groups.argtypes = [C.c_int, C.c_int, _dp, C.c_int, _dp, _dp, _dp, _dp]
+        L.rt_planck_groups_noalloc.argtypes = [C.c_int, C.c_int, _dp, C.c_int, _dp, _dp, _dp]
         L.rt_multigroup_opacities.argtypes = [C.c_int, C.c_int, _dp, C.c_double, C.c_double, _dp, _dp, _dp, _dp]
         L.rt_set_allreduce.argtypes = [vp, ALLREDUCE_FN, C.c_void_p]
         L.rt_get_temperature.argtypes = [vp, _dp, _dp]

@@ -1572,3 +1572,77 @@ extern "C" int rt_host_free(void *p)
    if (p) CK(cudaFreeHost(p));
    return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// rt_planck_groups_noalloc -- the Planck group integrals of rt_planck_groups WITHOUT any allocation.
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  rt_planck_groups allocates five device
+// buffers per call (copies of e_edge and T, the kernel's group-major tables B and dB/dT, the staging of the layout
+// conversion); here they live in ONE file-scope device array of a fixed, modest size that every GPU which loads the
+// library holds until the process exits.
+//
+// The array's NAME is a host-side stand-in in host code, not a device address: what the kernels get is the pointer that
+// cudaGetSymbolAddress returns, looked up once per device with that device current (noalloc_scratch below).
+// Every call shares the array and finds the previous call's contents in it: the two tables are cleared at the start of
+// each call (the last group keeps "the previous value" when the grey remainder is not positive, Planck.cpp:73-76, so
+// they must start at zero).  Calls that overlap on one GPU -- two host threads, or this entry point next to itself on
+// another stream -- RACE on the array: serialise them.  The call itself is synchronous (it ends with the result copies).
+constexpr size_t NOALLOC_ALIGN = 32; // doubles: every sub-array starts on a 256-byte boundary
+static __device__ __align__(256) double g_noalloc_scratch[RT_NOALLOC_MAX_DOUBLES];
+
+static size_t noalloc_round(size_t n) { return (n + NOALLOC_ALIGN - 1) / NOALLOC_ALIGN * NOALLOC_ALIGN; }
+
+// device address of the scratch array on the CURRENT device (cached per device; the lookup itself allocates nothing)
+static int noalloc_scratch(int device, double **out)
+{
+   static std::atomic<double *> cache[RT_MAX_DEVICES];
+   if (device < 0 || device >= RT_MAX_DEVICES) return fail("rt_planck_groups_noalloc: device %d outside [0,%d)", device, RT_MAX_DEVICES);
+   double *p = cache[device].load(std::memory_order_acquire);
+   if (!p)
+   {
+      const cudaError_t e = cudaGetSymbolAddress((void **)&p, g_noalloc_scratch);
+      if (e != cudaSuccess || !p)
+         return fail("rt_planck_groups_noalloc: cudaGetSymbolAddress(scratch) on device %d -> %s", device, cudaGetErrorString(e));
+      cache[device].store(p, std::memory_order_release);
+   }
+   *out = p;
+   return 0;
+}
+
+extern "C" int rt_planck_groups_noalloc(int device, int G, const double *e_edge, int ncell, const double *T, double *B, double *dBdT)
+{
+   if (!e_edge || !T || !B || !dBdT || G < 1 || ncell < 1) return fail("rt_planck_groups_noalloc: bad argument");
+   // layout of the scratch: e_edge (G+1) | T (ncell) | B [G][ncell] | dB/dT [G][ncell] | staging [ncell][G]
+   const size_t n = (size_t)G * (size_t)ncell;
+   const size_t o_e = 0, o_T = o_e + noalloc_round((size_t)G + 1), o_B = o_T + noalloc_round((size_t)ncell), o_dB = o_B + noalloc_round(n),
+                o_tmp = o_dB + noalloc_round(n), need = o_tmp + noalloc_round(n);
+   if (need > (size_t)RT_NOALLOC_MAX_DOUBLES)
+      return fail("rt_planck_groups_noalloc: G = %d groups x ncell = %d temperatures need %zu doubles of scratch, the static array holds "
+                  "RT_NOALLOC_MAX_DOUBLES = %d (3*G*ncell + G + 1 + ncell, each part rounded up to 32): use rt_planck_groups, or fewer "
+                  "temperatures per call", G, ncell, need, RT_NOALLOC_MAX_DOUBLES);
+   int ndev = 0;
+   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail("rt_planck_groups_noalloc: no CUDA device available");
+   if (device < 0 || device >= ndev) return fail("rt_planck_groups_noalloc: device %d not in [0,%d)", device, ndev);
+   CK(cudaSetDevice(device));
+   double *s = nullptr;
+   if (noalloc_scratch(device, &s)) return 1;
+   double *d_e = s + o_e, *d_T = s + o_T, *d_B = s + o_B, *d_dB = s + o_dB, *d_tmp = s + o_tmp;
+   CK(cudaMemcpyAsync(d_e, e_edge, ((size_t)G + 1) * sizeof(double), cudaMemcpyHostToDevice, 0));
+   CK(cudaMemcpyAsync(d_T, T, (size_t)ncell * sizeof(double), cudaMemcpyHostToDevice, 0));
+   // the array keeps the last call's contents: what must start at zero is cleared every time
+   CK(cudaMemsetAsync(d_B, 0, n * sizeof(double), 0));
+   CK(cudaMemsetAsync(d_dB, 0, n * sizeof(double), 0));
+   double pt[12], w[12];
+   gauss12_host(pt, w);
+   upload_gauss_rule(pt, w);
+   launch_planck(G, ncell, d_e, d_T, d_B, d_dB, 0);
+   CK(cudaGetLastError());
+   // the device tables are group-major [G][ncell]; the caller gets [ncell][G] like rt_planck_groups (conversion at the ABI edge)
+   launch_transpose_gn(d_B, d_tmp, G, ncell, 0, ncell, 0);
+   CK(cudaGetLastError());
+   CK(cudaMemcpy(B, d_tmp, n * sizeof(double), cudaMemcpyDeviceToHost));
+   launch_transpose_gn(d_dB, d_tmp, G, ncell, 0, ncell, 0);
+   CK(cudaGetLastError());
+   CK(cudaMemcpy(dBdT, d_tmp, n * sizeof(double), cudaMemcpyDeviceToHost));
+   return 0;
+}
