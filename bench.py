@@ -208,6 +208,95 @@ def run_reference_arm(args, rt, M, G, N, bcl, bcr, workload):
     emit(line)
 
 
+def cell_fields(p, N):
+    """smooth synthetic rho(c), T(c), kappa_g(c) (extension)"""
+    x = (np.arange(N) + 0.5) / N
+    p.T_cell = 1.0 + 0.3 * np.sin(2 * np.pi * x) ** 2
+    p.rho_cell = 1.0 + 0.5 * np.cos(3 * np.pi * x)
+    p.kappa_cell = np.asarray(p.group_kappa)[:, None] * (1.0 + 0.5 * np.sin(7 * np.pi * x))[None, :]
+
+
+def device_timed(rt, sharding, p, dims, local_rank, world, rank, dist, W, K, groups_per_batch=0):
+    """`value` of one workload: exactly K time steps of every owned group after W warm-up steps, CUDA events on the launching
+    stream, max over ranks; clocks sampled during the timed region."""
+    M, G, N = dims
+    g0, gn = sharding.group_range(G, world, rank)
+    s = rt.Solver(p, device=local_rank, group_begin=g0, group_count=gn, groups_per_batch=groups_per_batch, fetch_psi=False, dist=dist)
+    try:
+        if dist is not None:
+            dist.barrier()
+        with ClockSampler(local_rank) as clk:
+            ms = s.bench_steps(W, K)
+        tm, plan = s.timing(), s.plan()
+        T = s.temperature() if getattr(p, "cv", 0.0) else None
+    finally:
+        s.close()
+    ms_max = sharding.reduce_scalar(ms, "max", dist)
+    return {"value": M * G * N * 4 * K / (ms_max * 1e-3), "ms": ms_max, "tm": tm, "plan": plan, "clocks": clk.summary(), "gn": gn, "T": T}
+
+
+def identical_over_ranks(a, dist, local_rank):
+    """True when the fp64 array is bit-identical on every rank (min == max over the ranks of its int64 image)"""
+    if dist is None:
+        return True
+    import torch
+    t = torch.from_numpy(np.ascontiguousarray(a).view(np.int64).copy()).cuda(local_rank)
+    lo, hi = t.clone(), t.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    return bool(torch.equal(lo, hi))
+
+
+def temperature_parity(rt, sharding, dist, world, rank, local_rank):
+    """The temperature-coupled path through the SAME exchange (group shards over the ranks, all-reduce of the group sums
+    every step) on a slab small enough for the CPU checker: T(c) after every step and the final phi against oracle-2 of
+    the whole problem at 1e-9 (rank 0 runs the checker; outside every timed region).  PARITY UNPINNED by nature: the
+    reference has no temperature update, the oracle's restatement is its definition."""
+    M, G, N, steps = 8, 24, 1500, 3
+    p = synthetic_parameters(rt, M, G, N, 2, 1, 1e-3, steps)
+    x = (np.arange(N) + 0.5) / N
+    p.T_cell = 0.8 + 0.4 * np.sin(2 * np.pi * x) ** 2
+    p.rho_cell = 1.0 + 0.5 * np.cos(3 * np.pi * x)
+    p.cv = 0.7
+    g0, gn = sharding.group_range(G, world, rank)
+    o = None
+    if rank == 0:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import oracle_py  # TEST INFRASTRUCTURE, used here as the checker only
+        oracle_py.build()
+        mu, wt = rt.grid.gauss_legendre(M)
+        o = oracle_py.oracle_from_parameters(p, mu, wt, rt.grid.group_edges(G, p.efirst, p.elast), p.group_kappa, num_threads=min(8, host_cores()))
+    worst_T, same = 0.0, True
+    with rt.Solver(p, device=local_rank, group_begin=g0, group_count=gn, fetch_psi=False, dist=dist) as s:
+        for _ in range(steps):
+            s.run_stages(4)
+            T = s.temperature()
+            same = same and identical_over_ranks(T, dist, local_rank)
+            if o is not None:
+                o.run_stages(4)
+                T_ref = o.temperature()
+                worst_T = max(worst_T, float(np.max(np.abs(T - T_ref) / np.abs(T_ref))))
+        phi = sharding.gather_group_rows(s.moments_group_major()[0], G, dist)
+        moved = float(np.max(np.abs(T - p.T_cell)))
+    worst_phi = None
+    if o is not None:
+        ref = np.ascontiguousarray(o.moments()[0])  # (G, N) in reference order g + G*c == [g, c]
+        gmax = np.max(np.abs(ref), axis=1, keepdims=True)
+        per_group = np.max(np.abs(phi - ref) / (np.abs(ref) + 1e-3 * gmax), axis=1)
+        # the tolerance of tests/parity_util.py (group_rtol): 1e-9, except that the LAST group's Planck integral is the
+        # reference's own cancellation remainder a c T^4 - sum of the others (Planck.cpp:58-76), uncertain by ~eps*sum(B)/B_last
+        # (with T(c) the remainder is smallest in the coldest cell: sizes taken from the checker's own phi, per cell)
+        tol = np.full(G, 1e-9)
+        tol[-1] += 32 * np.finfo(np.float64).eps * float(np.max(np.sum(np.abs(ref), axis=0) / np.maximum(np.abs(ref[-1]), 1e-300)))
+        worst_phi = float(np.max(per_group / tol)) * 1e-9  # err/tol, expressed on the 1e-9 scale
+        o.close()
+    ok = same and (rank != 0 or (worst_T <= 1e-9 and worst_phi <= 1e-9 and moved > 1e-4))
+    ok = bool(sharding.reduce_scalar(0.0 if ok else 1.0, "max", dist) == 0.0)
+    return {"parity_ok": ok, "T_identical_on_all_ranks": same, "worst_rel_T_vs_oracle": worst_T, "worst_phi_vs_oracle": worst_phi,
+            "T_moved": moved, "tolerance": 1e-9, "pinned": False,
+            "what": f"{N} cells x S{M} x {G} groups sharded x{world}, {steps} BDF2 steps with the update; oracle-2 of the whole problem on rank 0"}
+
+
 _JSON_FD = None
 
 
@@ -250,6 +339,9 @@ def main():
     ap.add_argument("--groups", type=int, default=0, help="override the number of groups (debug)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the c5 and temperature_coupled sub-runs of the default command")
+    ap.add_argument("--tc-cv", type=float, default=1.0, help="specific heat of the temperature_coupled sub-run")
+    ap.add_argument("--tc-dt", type=float, default=1e-5, help="time step of the temperature_coupled sub-run (1e-3 is unstable on c5r)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -284,25 +376,12 @@ def main():
         p.cv = args.cv
         args.cell_fields = True
     if args.cell_fields:
-        x = (np.arange(N) + 0.5) / N
-        p.T_cell = 1.0 + 0.3 * np.sin(2 * np.pi * x) ** 2
-        p.rho_cell = 1.0 + 0.5 * np.cos(3 * np.pi * x)
-        p.kappa_cell = np.asarray(p.group_kappa)[:, None] * (1.0 + 0.5 * np.sin(7 * np.pi * x))[None, :]
+        cell_fields(p, N)
 
     # ------------------------------------------------------------- device-resident timing (`value`)
-    s = rt.Solver(p, device=local_rank, group_begin=g0, group_count=gn, groups_per_batch=args.groups_per_batch, fetch_psi=False,
-                  dist=dist)
-    plan = s.plan()
-    if dist is not None:
-        dist.barrier()
-    with ClockSampler(local_rank) as clk:
-        ms = s.bench_steps(W, K)
-    tm = s.timing()
-    plan = s.plan()
-    s.close()
-    ms_max = sharding.reduce_scalar(ms, "max", dist)
+    main_run = device_timed(rt, sharding, p, (M, G, N), local_rank, world, rank, dist, W, K, args.groups_per_batch)
+    tm, plan, ms_max, value = main_run["tm"], main_run["plan"], main_run["ms"], main_run["value"]
     unknown_stages = M * G * N * 4 * K
-    value = unknown_stages / (ms_max * 1e-3)
 
     # roofline of the dominant kernel: algorithmic bytes / event time of its launches, this rank
     kinds = ["BE", "CN", "BDF"]
@@ -388,7 +467,8 @@ def main():
         nt = int(tm.tupdate_count)
         tupdate = {"updates": nt, "exchange_ms_per_step": tm.tupdate_ms / nt, "tables_ms_per_step": tm.tables_ms / nt,
                    "sweep_ms_per_step": (sum(tm.sweep_ms) + tm.step_ms) / nt, "allreduce": "NCCL (torch.distributed) on the library's device buffer" if world > 1 else "none (all groups owned)",
-                   "allreduce_bytes_per_step": 3 * N * 8,
+                   # a shard exchanges the 3N group sums and the 2N Planck remainder sums; a handle that owns every group none
+                   "allreduce_bytes_per_step": (5 * N * 8) if world > 1 else 0,
                    "what": "exchange = moments + group sums A,E,D + all-reduce + T update; tables = Planck integrals of all G groups per cell "
                            "+ per-cell correction terms at the new T"}
 
@@ -419,20 +499,67 @@ def main():
                "what": "Solver(params) [tables H2D, Planck+correction terms, state init] + solve() of K steps with phi of every "
                        "step copied to pinned host memory; wall clock incl. allocation"}
 
+    # ------------------------------------------------------------- the scaling series: C5 at THIS number of GPUs
+    # BASELINE.json's multi-GPU config (2^20 x S32 x 4096 groups, groups sharded, fixed total work = strong scaling).  At
+    # N > 1 it is the line's own workload; at N = 1 the line's `value` is C4 (BASELINE's single-GPU config), so C5 is
+    # measured here as well: divide c5.value at N by c5.value at 1.
+    c5 = None
+    if not args.no_extras and args.workload == "auto":
+        if workload == "c5":
+            c5 = {"value": value, "ms_per_step": ms_max / K, "steps": K, "warmup": W, "batches": plan.n_batches,
+                  "groups_per_batch": plan.groups_per_batch, "clocks": main_run["clocks"], "same_run_as": "value"}
+        else:
+            M5, G5, N5, l5, r5 = WORKLOADS["c5"]
+            K5 = max(K, 5)
+            p5 = synthetic_parameters(rt, M5, G5, N5, l5, r5, args.dt, K5, V=args.V)
+            r = device_timed(rt, sharding, p5, (M5, G5, N5), local_rank, world, rank, dist, max(W, 3), K5)
+            c5 = {"value": r["value"], "ms_per_step": r["ms"] / K5, "steps": K5, "warmup": max(W, 3), "batches": r["plan"].n_batches,
+                  "groups_per_batch": r["plan"].groups_per_batch, "clocks": r["clocks"], "same_run_as": None}
+        c5.update({"workload": "c5", "M": WORKLOADS["c5"][0], "G": WORKLOADS["c5"][1], "N": WORKLOADS["c5"][2], "n_gpus": world,
+                   "per_gpu_value": c5["value"] / world, "scaling": "strong"})
+
+    # ------------------------------------------------------------- the path's one collective: temperature-coupled c5r
+    # (extension, parity unpinned: the reference has no temperature update).  Every step all-reduces the group sums over
+    # the ranks (NCCL on the library's device buffers) before T is updated and the per-cell Planck tables are rebuilt.
+    tc = None
+    if not args.no_extras and args.workload == "auto":
+        Mt, Gt, Nt, lt, rt_bc = WORKLOADS["c5r"]
+        Kt = max(K, 10)
+        # dt = 1e-5: the explicitly coupled update is only conditionally stable, and on this slab (4096 narrow groups, opacities
+        # over three decades) dt = 1e-3 is outside the range -- T runs away within five steps, in the CPU oracle exactly as on
+        # the device (the library now reports it, rt_capi.cu check_temperature).  The kernels and the exchange are the same.
+        pt = synthetic_parameters(rt, Mt, Gt, Nt, lt, rt_bc, args.tc_dt, Kt, V=args.V)
+        pt.cv = args.tc_cv
+        cell_fields(pt, Nt)
+        r = device_timed(rt, sharding, pt, (Mt, Gt, Nt), local_rank, world, rank, dist, max(W, 3), Kt)
+        nt = max(int(r["tm"].tupdate_count), 1)
+        tc = {"workload": "c5r", "M": Mt, "G": Gt, "N": Nt, "cv": args.tc_cv, "dt": args.tc_dt,
+              "T_range_after_run": [float(np.min(r["T"])), float(np.max(r["T"]))], "T_finite": bool(np.isfinite(r["T"]).all()), "n_gpus": world, "steps": Kt, "warmup": max(W, 3),
+              "value": r["value"], "per_gpu_value": r["value"] / world, "ms_per_step": r["ms"] / Kt,
+              "exchange_ms_per_step": r["tm"].tupdate_ms / nt, "tables_ms_per_step": r["tm"].tables_ms / nt,
+              "sweep_ms_per_step": (sum(r["tm"].sweep_ms) + r["tm"].step_ms) / nt,
+              "allreduce": "NCCL all-reduce on the library's device buffers, twice per step (3N group sums, 2N Planck remainder sums)" if world > 1 else "none (one rank owns every group)",
+              "allreduce_bytes_per_step": (5 * Nt * 8) if world > 1 else 0, "clocks": r["clocks"],
+              "T_identical_on_all_ranks": identical_over_ranks(r["T"], dist, local_rank),
+              "pinned": False, "note": "parity unpinned by nature: the reference has no temperature update (SURVEY F3); checker = oracle-2's restatement"}
+        tc.update(temperature_parity(rt, sharding, dist, world, rank, local_rank))
+        tc["parity_ok"] = bool(tc["parity_ok"] and tc["T_identical_on_all_ranks"] and tc["T_finite"])
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline_port(rt, M, args.dt, host_cores())
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-                "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "strong" if workload == "c5" else "weak",
+                "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "strong", "per_gpu_value": value / world,
+                "scaling_series": "c5.value at every N (2^20 x S32 x 4096 groups, fixed total work); the N = 1 `value` is C4, BASELINE's single-GPU config",
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": workload, "M": M, "G": G, "N": N, "dt": args.dt, "ts_method": "BDF2 (BE,CN,BE,BDF)",
                            "bc": [bcl, bcr], "V": args.V, "cell_fields": bool(args.cell_fields), "cv": args.cv, "use_correction": True, "parallelism": f"groups sharded x{world}",
                            "groups_per_rank": gn, "groups_per_batch": plan.groups_per_batch, "batches": plan.n_batches,
-                           "l2": "inputs larger than L2 (each launch streams >= 10 GB)" if M * min(plan.groups_per_batch, gn) * N * 32 > 2e8 else "inputs smaller than L2"},
-                "roofline": roofline, "temperature_update": tupdate, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": gpu_launches,
-                "clocks": clk.summary(), "s_per_bdf2_step": ms_max / K * 1e-3,
+                           "l2": (lambda b: f"inputs {'larger' if b > 2.52e8 else 'smaller'} than L2: each step launch streams {b / 1e9:.2f} GB (L2 = 0.126 GB)")(M * min(plan.groups_per_batch, gn) * N * 32.0)},
+                "roofline": roofline, "temperature_update": tupdate, "c5": c5, "temperature_coupled": tc, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": gpu_launches,
+                "clocks": main_run["clocks"], "s_per_bdf2_step": ms_max / K * 1e-3,
                 "sweep_grid": plan.sweep_grid, "sweep_block": plan.sweep_block, "fused_step": bool(plan.fused),
                 "step_tile_cells": plan.step_tile_cells, "step_chain_warps": plan.step_chain}
         emit(line)

@@ -107,7 +107,8 @@ typedef struct rt_plan
    int step_block;       /* threads per CTA of the fused step kernel                                             */
    int step_chain;       /* warps chained per CTA tile (1 for the CTA-wide tile shapes)                          */
    int time_levels;      /* time-level buffers allocated: 2 for the fused step, 4 once a step has run stage by stage (ABI 4) */
-   int step_kernel;      /* fused step: 4 = one 4-vector scan per sub-tile (step4_kernel.cu), 1 = four scalar scans       */
+   int step_kernel;      /* fused step kernel a whole step would use now: 1 = four scalar scans (plain steps), 4 = one 4-vector
+                          * scan that also sums phi (per-step output on); RT_CUDA_STEP_KERNEL=1|4 forces one                */
 } rt_plan;
 
 const char *rt_last_error(void);

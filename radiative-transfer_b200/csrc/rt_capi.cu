@@ -82,6 +82,7 @@ struct rt_solver
    double *d_T_prev = nullptr, *d_xsums = nullptr, *d_xpart = nullptr; // N ; 3N (A, E, D) ; chunks*3N
    double *d_ppart = nullptr;      // 2N: per-cell partial sums of the raw Planck integrals (sharded evaluation)
    long long tsteps_done = 0;      // temperature updates since the state was initialised
+   int *d_T_bad = nullptr;         // 0, or the number of the first update that left some cell with T <= 0 or a non-finite T
    rt_allreduce_fn allreduce = nullptr;
    void *allreduce_user = nullptr;
    // batching
@@ -129,7 +130,11 @@ struct rt_solver
    bool timing_on = true;
    // fused BDF2-step kernel (step_kernel.cu): RT_CUDA_FUSED=0 runs every step stage by stage
    bool fused = true, fused_var = false, half_stale = false;
-   int step_kernel = 4;        // 4: one 4-vector scan per sub-tile (step4_kernel.cu, default) ; 1: four scalar scans (RT_CUDA_STEP_KERNEL=1)
+   // fused uniform step: 0 = automatic (default): the four-scan kernel (step_warp_kernel.cu, ~2 % faster on C4) for plain steps,
+   // the one-scan kernel (step4_kernel.cu) when the step also has to deliver phi (it adds up w_m psi in the same pass and
+   // saves the separate moments pass over the state) ; RT_CUDA_STEP_KERNEL=1 | 4 forces one of them
+   int step_kernel = 0;
+   bool step4_ok = true;       // the tile shape in use is one the one-scan kernel supports
    int step_threads = 32, step_cpt = 8, step_chain = 4, step_box_cells = 256, step_tile_cells = 1024, step_tiles_per_row = 0;
    SweepMaps maps_step;
    int ticket_batch = 8;       // tickets per atomic draw (RT_CUDA_TICKET_BATCH)
@@ -402,6 +407,7 @@ static int load_batch(rt_solver *s, int start)
          s->T_moved = false;
       }
       s->tsteps_done = 0;
+      CK(cudaMemsetAsync(s->d_T_bad, 0, sizeof(int), s->st));
    }
    if (s->var) launch_init_state_var(s->E[0], s->d_B_c, s->p.M, s->p.N, s->Np, s->p.G, s->p.group_begin + start, s->batch_groups, s->st);
    else launch_init_state(s->E[0], s->d_B, s->p.M, s->p.N, s->Np, s->p.group_begin + start, s->batch_groups, s->st);
@@ -449,6 +455,7 @@ extern "C" int rt_destroy(rt_solver *s)
       cudaMemPool_t pool;
       if (cudaDeviceGetDefaultMemPool(&pool, s->p.device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0);
    }
+   if (s->d_T_bad) cudaFree(s->d_T_bad);
    if (s->d_tile_status) cudaFree(s->d_tile_status);
    if (s->d_ticket) cudaFree(s->d_ticket);
    for (auto &ep : s->ev_pool) { cudaEventDestroy(ep.a); cudaEventDestroy(ep.b); }
@@ -557,8 +564,9 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       s->step_tiles_per_row = (N + s->step_tile_cells - 1) / s->step_tile_cells;
       s->max_tiles_per_row = std::max(s->max_tiles_per_row, 4 * s->step_tiles_per_row); // 4 look-back words per tile
       if (s->var) s->max_tiles_per_row = std::max(s->max_tiles_per_row, 4 * ((N + 255) / 256)); // fused cell-dependent step, 256-cell tiles
-      if (const char *ke = getenv("RT_CUDA_STEP_KERNEL")) s->step_kernel = (atoi(ke) == 1) ? 1 : 4;
-      if (s->step_threads != 32 || s->step_cpt != 8 || !step4_chain_supported(s->step_chain)) s->step_kernel = 1;
+      if (const char *ke = getenv("RT_CUDA_STEP_KERNEL")) s->step_kernel = (atoi(ke) == 1) ? 1 : (atoi(ke) == 4 ? 4 : 0);
+      s->step4_ok = s->step_threads == 32 && s->step_cpt == 8 && step4_chain_supported(s->step_chain);
+      if (!s->step4_ok) s->step_kernel = 1;
       for (int r = 1; r <= 8; ++r)
          if ((M / 2) % r == 0) s->phi_run = r;
       const char *fe = getenv("RT_CUDA_FUSED");
@@ -632,6 +640,8 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       {
          CKD(dalloc(&s->d_sdB, (size_t)s->Gl * s->vt_pitch)); CKD(dalloc(&s->d_T_prev, N)); CKD(dalloc(&s->d_xsums, (size_t)3 * N)); CKD(dalloc(&s->d_ppart, (size_t)2 * N));
          CKD(dalloc(&s->d_xpart, (size_t)exchange_chunks(s->Gl) * 3 * N));
+         CKD(dalloc(&s->d_T_bad, 1));
+         CKC(cudaMemsetAsync(s->d_T_bad, 0, sizeof(int), s->st));
          for (int m = 0; m < M; ++m) s->wsum += s->wt[m];
       }
       CKC(cudaMemsetAsync(s->d_B_c, 0, (size_t)G * N * sizeof(double), s->st));
@@ -718,7 +728,7 @@ extern "C" int rt_get_plan(const rt_solver *s, rt_plan *plan)
    plan->bytes_per_group = (size_t)s->plan_levels * s->p.M * s->Np * sizeof(double2);
    plan->state_bytes = (size_t)s->levels * s->buf_elems * sizeof(double2);
    plan->time_levels = s->levels;
-   plan->step_kernel = s->step_kernel;
+   plan->step_kernel = (s->step_kernel == 4 || (s->step_kernel == 0 && s->step_phi_host && s->step_group_major && s->d_phi_part)) ? 4 : 1;
    cudaSetDevice(s->p.device);
    cudaMemGetInfo(&plan->free_bytes, &plan->total_bytes);
    return 0;
@@ -902,8 +912,9 @@ static int run_fused_step(rt_solver *s)
    if (ensure_levels(s, 2)) return 1;
    const int in = s->i_ends, out = pick_free(in, -1, -1, -1);
    // the per-step scalar intensity rides along in the one-scan kernel: partial sums of w_m psi per run of rows
-   const bool v4 = s->step_kernel == 4;
-   const bool phi = v4 && s->step_phi_host && s->step_group_major && s->d_phi_part;
+   const bool want_phi = s->step_phi_host && s->step_group_major && s->d_phi_part;
+   const bool v4 = s->step_kernel == 4 || (s->step_kernel == 0 && want_phi);
+   const bool phi = v4 && want_phi;
    StepArgs a;
    a.x = s->E[in];
    a.ix = in; a.iout = out;
@@ -1043,7 +1054,8 @@ static int temperature_update(rt_solver *s)
       const int rc = s->allreduce(s->d_xsums, (size_t)3 * p.N, (void *)s->st, s->allreduce_user);
       if (rc) return fail("rt: the all-reduce hook failed with code %d in the temperature update after stage %d", rc, s->stages_done);
    }
-   launch_temperature_update(p.N, p.ts_method == 3 && s->tsteps_done > 0, p.dt, p.cv, s->d_rho_c, s->d_xsums, s->d_T_c, s->d_T_prev, s->st);
+   launch_temperature_update(p.N, p.ts_method == 3 && s->tsteps_done > 0, p.dt, p.cv, s->d_rho_c, s->d_xsums, s->d_T_c, s->d_T_prev,
+                             (int)s->tsteps_done + 1, s->d_T_bad, s->st);
    s->tm.kernel_launches += 1;
    if (event_end(s, ep)) return 1;
    if (event_begin(s, 6, &ep)) return 1;
@@ -1053,6 +1065,19 @@ static int temperature_update(rt_solver *s)
    s->tsteps_done++;
    s->tm.tupdate_count++;
    s->T_moved = true;
+   return 0;
+}
+
+// after the stream has been synchronised: did a temperature update leave the physical range?
+static int check_temperature(rt_solver *s)
+{
+   if (!s->tupdate || !s->d_T_bad) return 0;
+   int bad = 0;
+   CK(cudaMemcpy(&bad, s->d_T_bad, sizeof(int), cudaMemcpyDeviceToHost));
+   if (bad)
+      return fail("rt: the material temperature left the physical range (T <= 0 or not finite in some cell) in temperature update %d: "
+                  "the explicitly coupled update (rt_params::cv) is only conditionally stable -- reduce dt or raise cv "
+                  "(dt = %g, cv = %g; the CPU oracle diverges on the same input)", bad, s->p.dt, s->p.cv);
    return 0;
 }
 
@@ -1090,7 +1115,7 @@ extern "C" int rt_run_stages(rt_solver *s, int n)
    if (flush_events(s)) return 1;
    CK(cudaStreamSynchronize(s->st));
    if (s->step_phi_host) CK(cudaStreamSynchronize(s->copy_st));
-   return 0;
+   return check_temperature(s);
 }
 
 extern "C" int rt_solve(rt_solver *s)
@@ -1116,7 +1141,7 @@ extern "C" int rt_solve(rt_solver *s)
    if (flush_events(s)) return 1;
    CK(cudaStreamSynchronize(s->st));
    if (s->step_phi_host) CK(cudaStreamSynchronize(s->copy_st));
-   return 0;
+   return check_temperature(s);
 }
 
 extern "C" int rt_set_allreduce(rt_solver *s, rt_allreduce_fn fn, void *user)
@@ -1365,7 +1390,7 @@ extern "C" int rt_set_step_output(rt_solver *s, double *phi_host, int group_majo
       }
       // the one-scan step kernel adds up w_m psi itself (RT_CUDA_STEP_PHI=0: separate moments pass over the state)
       const char *pe = getenv("RT_CUDA_STEP_PHI");
-      if (group_major && s->fused && s->step_kernel == 4 && s->p.ts_method == 3 && !(pe && pe[0] == '0') && !s->d_phi_part)
+      if (group_major && s->fused && s->step_kernel != 1 && s->step4_ok && s->p.ts_method == 3 && !(pe && pe[0] == '0') && !s->d_phi_part)
       {
          const size_t np = (size_t)s->Gb * 2 * ((size_t)(s->p.M / 2) / s->phi_run) * (size_t)s->phi_pitch;
          if (dalloc(&s->d_phi_part, np)) return 1;
@@ -1557,7 +1582,7 @@ extern "C" int rt_bench_steps(rt_solver *s, int warmup_steps, int timed_steps, d
    CK(cudaEventDestroy(e1));
    s->results_valid = false;
    *device_ms = total;
-   return 0;
+   return check_temperature(s);
 }
 
 // pinned host memory for the caller-owned result buffers of the end-to-end path

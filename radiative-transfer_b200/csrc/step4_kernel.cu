@@ -469,7 +469,15 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step4_kernel(const __grid_co
             }
             else
             {
+               // The writer publishes the words of stages 0..3 in that order.  Polling all four with one 16-byte load per lane
+               // costs 8 shared-memory wavefronts per iteration (2-way conflicted) and ran ~12 times per sub-tile: a quarter of
+               // the kernel's shared-memory traffic (profiles/r02_step4_cellmajor_ncu_digest.txt).  So: every lane polls the
+               // 8-byte sequence number of the LAST word (one broadcast wavefront), then the four words are read once -- each
+               // still checked against its own sequence number, so nothing rests on the order the stores become visible in.
                const double2 *src = carry_slot + (lane & 3) * NW + (warp - 1);
+               const int *last_seq = reinterpret_cast<const int *>(carry_slot + 3 * NW + (warp - 1)) + 2; // low word of .y
+               while (again(ld_flag(last_seq) != seq + 1))
+                  if (++spins > SPIN_SHARED) __trap();
                w = lds_word(src);
                while (again((int)__double_as_longlong(w.y) != seq + 1))
                {

@@ -381,6 +381,12 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
             // the previous warp's inclusive value of this tile and stage, through shared memory
             const double2 *src = carry_slot + k * NW + (warp - 1);
             long long spins = 0;
+            // wait on the 8-byte sequence number (one broadcast wavefront per poll instead of two for the 16-byte word:
+            // the polls are a measurable share of the shared-memory traffic, profiles/r02_step4_cellmajor_ncu_digest.txt),
+            // then read the word -- still checked against its own sequence number below
+            const int *seq_word = reinterpret_cast<const int *>(src) + 2;
+            while (poll_again<4>(ld_flag(seq_word) != seq + 1))
+               if (++spins > SPIN_LIMIT_S) __trap();
             double2 w = lds_word(src);
             while (poll_again<4>((int)__double_as_longlong(w.y) != seq + 1))
             {

@@ -346,8 +346,12 @@ int launch_exchange_sums(const ExchangeArgs &a, cudaStream_t st)
    return 2;
 }
 
+// first_bad: 0 until some cell's new temperature is not a positive finite number, then the (1-based) number of the update
+// that produced it -- the explicitly coupled update is only conditionally stable (stiff slabs at large dt run away, in the
+// oracle's restatement exactly as here), and a solve must not carry on silently with T <= 0 or NaN
 __global__ void temperature_update_kernel(int N, int bdf2, double dt, double cv, const double *__restrict__ rho_cell,
-                                          const double *__restrict__ sums, double *__restrict__ T, double *__restrict__ T_prev)
+                                          const double *__restrict__ sums, double *__restrict__ T, double *__restrict__ T_prev,
+                                          int update_no, int *__restrict__ first_bad)
 {
    const int c = blockIdx.x * blockDim.x + threadIdx.x;
    if (c >= N) return;
@@ -358,12 +362,13 @@ __global__ void temperature_update_kernel(int N, int bdf2, double dt, double cv,
    else tn = (rcv * (2. * t - 0.5 * T_prev[c]) + dt * (A - E + D * t)) / (1.5 * rcv + dt * D);
    T_prev[c] = t;
    T[c] = tn;
+   if (!(tn > 0.0) || !isfinite(tn)) atomicCAS(first_bad, 0, update_no);
 }
 
 void launch_temperature_update(int N, bool bdf2, double dt, double cv, const double *rho_cell, const double *sums, double *T,
-                               double *T_prev, cudaStream_t st)
+                               double *T_prev, int update_no, int *first_bad, cudaStream_t st)
 {
-   temperature_update_kernel<<<(N + 255) / 256, 256, 0, st>>>(N, bdf2 ? 1 : 0, dt, cv, rho_cell, sums, T, T_prev);
+   temperature_update_kernel<<<(N + 255) / 256, 256, 0, st>>>(N, bdf2 ? 1 : 0, dt, cv, rho_cell, sums, T, T_prev, update_no, first_bad);
 }
 
 // ------------------------------------------------------------------------------------------ diagnostics

@@ -109,7 +109,7 @@ inline int exchange_chunks(int groups) { return (groups + EXCHANGE_GROUPS_PER_CH
 int launch_exchange_sums(const ExchangeArgs &a, cudaStream_t st);
 // T <- T' from the (all-reduced) sums; T_prev <- T.  bdf2 = later steps of a BDF2 run
 void launch_temperature_update(int N, bool bdf2, double dt, double cv, const double *rho_cell, const double *sums, double *T,
-                               double *T_prev, cudaStream_t st);
+                               double *T_prev, int update_no, int *first_bad, cudaStream_t st);
 
 // balance (solver.cpp:240-284) with per-cell sigma and T, group-end spectra (826-850)
 void launch_diagnostics_var(const double2 *ends, const double *phi, const double *mu, const double *wt, const double *sigma_cell,

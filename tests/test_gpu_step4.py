@@ -15,6 +15,13 @@ from parity_util import make_oracle, state_err, state_ok, synthetic_parameters
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True)
+def _one_scan_kernel(monkeypatch):
+    """the library picks the kernel by job (four-scan for plain steps, one-scan when the step sums phi): these tests are
+    about the one-scan kernel, so it is forced; the tests that compare both set the variable themselves"""
+    monkeypatch.setenv("RT_CUDA_STEP_KERNEL", "4")
+
+
 def _oracle_state(oracle, rt, p, stages, threads=2):
     o = make_oracle(oracle, rt, p, num_threads=threads)
     o.run_stages(stages)
@@ -167,3 +174,24 @@ def test_full_size_rows_local_regime_and_no_correction(rt, oracle, dt, V):
         assert ok, f"phi err/tol {worst:.3e}"
         ok, worst, _ = state_ok(s.ends(0), oends, B)
         assert ok, f"ends err/tol {worst:.3e}"
+
+
+def test_kernel_is_chosen_by_the_job(rt, monkeypatch):
+    """default (no RT_CUDA_STEP_KERNEL): plain steps run the four-scan kernel; once the per-step scalar intensity is asked
+    for, whole steps run the one-scan kernel, which sums it in the same pass"""
+    monkeypatch.delenv("RT_CUDA_STEP_KERNEL")
+    p = synthetic_parameters(rt, M=8, G=4, N=2100, dt=1e-3, V=1.0, steps=2)
+    pin = C.c_void_p()
+    rt.capi.check(rt.capi.lib().rt_host_alloc(C.byref(pin), p.G * p.N * 8))
+    try:
+        with rt.Solver(p, fetch_psi=False) as s:
+            assert s.plan().step_kernel == 1
+            s.set_step_output(pin, True)
+            assert s.plan().step_kernel == 4
+            s.solve()
+            out = np.ctypeslib.as_array(C.cast(pin, C.POINTER(C.c_double)), shape=(p.G * p.N,)).reshape(p.G, p.N).copy()
+            assert state_err(out, s.moments_group_major()[0], group_axis=0) <= 1e-13
+            s.set_step_output(None, True)
+            assert s.plan().step_kernel == 1
+    finally:
+        rt.capi.lib().rt_host_free(pin)

@@ -185,3 +185,25 @@ def test_grey_single_group_with_temperature_update(rt, oracle):
         for k in range(3):
             s.run_stages(4)
             _check_step(s, ref[k], B)
+
+
+def test_a_runaway_temperature_is_reported_not_carried_on(rt):
+    """The explicitly coupled update is only conditionally stable: on a stiff slab (512 narrow groups with opacities spread
+    over three decades, c dt = 30 cells) T leaves the physical range within a few steps -- in the oracle's restatement
+    exactly as on the device (checked on the CPU, tools/gpu_debug_tc.py).  The solve must say so instead of returning NaN."""
+    N = 256
+    p = synthetic_parameters(rt, M=8, G=512, N=N, dt=1e-3, V=1.0, steps=10, bc_left=1, bc_right=1)
+    x = (np.arange(N) + 0.5) / N
+    p.T_cell = 1.0 + 0.3 * np.sin(2 * np.pi * x) ** 2
+    p.rho_cell = 1.0 + 0.5 * np.cos(3 * np.pi * x)
+    p.kappa_cell = np.asarray(p.group_kappa)[:, None] * (1.0 + 0.5 * np.sin(7 * np.pi * x))[None, :]
+    p.cv = 1.0
+    with rt.Solver(p, fetch_psi=False) as s:
+        with pytest.raises(rt.capi.RtError, match="left the physical range"):
+            s.solve()
+        # the same slab at a step inside the stability range runs through and stays physical
+    p.dt, p.max_timesteps = 1e-5, 4
+    with rt.Solver(p, fetch_psi=False) as s:
+        s.solve()
+        T = s.temperature()
+        assert np.isfinite(T).all() and T.min() > 0.9 and T.max() < 1.4

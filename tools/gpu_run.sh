@@ -47,12 +47,12 @@ PY
     done ;;
   launches)
     timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c ${NCU_COUNT:-400} --csv --log-file $OUT/launches.csv \
-        python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline "$@" > $OUT/launches_run.log 2>&1
+        python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline --no-extras "$@" > $OUT/launches_run.log 2>&1
     echo "ncu launch list exit $?"; grep -c . $OUT/launches.csv ;;
   ncu)
     local re=$1; shift
     timeout 1500 ncu --set full --import-source on --clock-control none -k regex:$re -s ${NCU_SKIP:-2} -c 1 -f -o $OUT/full_$n \
-        python bench.py --steps 1 --warmup 2 --no-e2e --no-cpu-baseline "$@" > $OUT/ncu_run_$n.log 2>&1
+        python bench.py --steps 1 --warmup 2 --no-e2e --no-cpu-baseline --no-extras "$@" > $OUT/ncu_run_$n.log 2>&1
     echo "ncu full exit $?"; ls -la $OUT/full_$n.ncu-rep 2>/dev/null
     ncu -i $OUT/full_$n.ncu-rep --page raw --csv > $OUT/full_${n}_raw.csv 2>/dev/null ;;
   *) echo "unknown mode $mode"; return 2 ;;
