@@ -227,12 +227,12 @@ def device_timed(rt, sharding, p, dims, local_rank, world, rank, dist, W, K, gro
             dist.barrier()
         with ClockSampler(local_rank) as clk:
             ms = s.bench_steps(W, K)
-        tm, plan = s.timing(), s.plan()
+        tm, plan, exchange = s.timing(), s.plan(), s.exchange
         T = s.temperature() if getattr(p, "cv", 0.0) else None
     finally:
         s.close()
     ms_max = sharding.reduce_scalar(ms, "max", dist)
-    return {"value": M * G * N * 4 * K / (ms_max * 1e-3), "ms": ms_max, "tm": tm, "plan": plan, "clocks": clk.summary(), "gn": gn, "T": T}
+    return {"value": M * G * N * 4 * K / (ms_max * 1e-3), "ms": ms_max, "tm": tm, "plan": plan, "clocks": clk.summary(), "gn": gn, "T": T, "exchange": exchange}
 
 
 def identical_over_ranks(a, dist, local_rank):
@@ -538,7 +538,7 @@ def main():
               "value": r["value"], "per_gpu_value": r["value"] / world, "ms_per_step": r["ms"] / Kt,
               "exchange_ms_per_step": r["tm"].tupdate_ms / nt, "tables_ms_per_step": r["tm"].tables_ms / nt,
               "sweep_ms_per_step": (sum(r["tm"].sweep_ms) + r["tm"].step_ms) / nt,
-              "allreduce": "NCCL all-reduce on the library's device buffers, twice per step (3N group sums, 2N Planck remainder sums)" if world > 1 else "none (one rank owns every group)",
+              "allreduce": r["exchange"] + ("; twice per step: 3N group sums, 2N Planck remainder sums" if world > 1 else ""),
               "allreduce_bytes_per_step": (5 * Nt * 8) if world > 1 else 0, "clocks": r["clocks"],
               "T_identical_on_all_ranks": identical_over_ranks(r["T"], dist, local_rank),
               "pinned": False, "note": "parity unpinned by nature: the reference has no temperature update (SURVEY F3); checker = oracle-2's restatement"}

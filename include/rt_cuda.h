@@ -162,6 +162,45 @@ typedef int (*rt_allreduce_fn)(void *device_buf, size_t count, void *cuda_stream
 int rt_set_allreduce(rt_solver *s, rt_allreduce_fn fn, void *user);
 int rt_get_temperature(rt_solver *s, double *T, double *sums3);
 
+/* Native NCCL for that exchange ("the library owns streams, device buffers and NCCL communicators"; the
+ * reference itself has no collective).  For hosts that run ONE PROCESS PER GPU: rank 0 calls
+ * rt_nccl_unique_id (128 bytes, ncclUniqueId), the host distributes the id (MPI_Bcast, torch.distributed.broadcast ...),
+ * every rank calls rt_set_nccl on its handle after rt_create: the library creates the communicator on the handle's device
+ * and sums the group sums with ncclAllReduce on its own stream -- no host callback in the time loop.  libnccl.so.2 is
+ * loaded with dlopen on first use (RT_CUDA_NCCL_LIB overrides the name); a process that never asks needs no NCCL.
+ * The communicator belongs to the handle (rt_destroy releases it); rt_set_allreduce replaces it with the host's own sum. */
+int rt_nccl_unique_id(void *id128);
+int rt_set_nccl(rt_solver *s, const void *id128, int nranks, int rank);
+
+/* ---- ONE process, SEVERAL GPUs (csrc/rt_multi.cu).  The reference's drivers construct one rt::Solver in one process
+ * (src/main.cc:100-113, tests/test_gray.cpp:68-79); for that host to use more than one B200 the sharding lives here
+ * ("the library owns streams, device buffers and NCCL communicators (single-process multi-GPU)").
+ * rt_multi_create: `p` describes the whole problem (p->device is ignored); the groups [group_begin, group_begin+group_count)
+ * are cut into ndev contiguous blocks, shard k on devices[k], every shard driven by its own host thread.  A device may be
+ * listed twice (two shards on one GPU) unless cv > 0: the temperature update sums over the shards with ncclAllReduce on
+ * communicators created here (ncclCommInitAll), one distinct device per shard.  Results come back in the reference's
+ * index order over ALL owned groups (G = p->group_count in the layouts at the top of this file).  The drop-in
+ * rt::Solver (host/solver.cpp) takes the device list from RT_CUDA_DEVICES. */
+typedef struct rt_multi rt_multi;
+int rt_multi_create(const rt_params *p, int ndev, const int *devices, rt_multi **out);
+int rt_multi_destroy(rt_multi *m);
+int rt_multi_shards(const rt_multi *m, int *n, int *group_begin, int *group_count, int *device); /* arrays of n, may be NULL */
+int rt_multi_solve(rt_multi *m);                              /* rt_solve on every shard, concurrently                    */
+int rt_multi_run_stages(rt_multi *m, int n);
+int rt_multi_reset(rt_multi *m);
+int rt_multi_stages_done(const rt_multi *m, int *n);
+int rt_multi_get_psi(rt_multi *m, double *psi);               /* M*G*N                                                    */
+int rt_multi_get_ends(rt_multi *m, int which, double *ends);  /* M*G*N*2                                                  */
+int rt_multi_moments(rt_multi *m, double *phi, double *phi_plus, double *F); /* G*N each, any may be NULL               */
+int rt_multi_balance(rt_multi *m, double *balance);           /* G                                                        */
+int rt_multi_group_ends(rt_multi *m, double *left, double *right);
+int rt_multi_get_group_terms(rt_multi *m, double *B, double *dBdT, double *dEB, double *dsigEdE, double *dkapEB, double *kappa_edge);
+int rt_multi_validate(rt_multi *m, double *sums3, int *ok);
+int rt_multi_get_temperature(rt_multi *m, double *T, double *sums3);
+int rt_multi_bench_steps(rt_multi *m, int warmup_steps, int timed_steps, double *device_ms); /* slowest shard's device time */
+int rt_multi_get_timing(const rt_multi *m, int shard, rt_timing *t);
+int rt_multi_get_plan(const rt_multi *m, int shard, rt_plan *plan);
+
 /* After every completed time step (BDF2: 4 stage sweeps) copy phi (Gl*N, group-major g*N + c when
  * group_major != 0, reference order otherwise) into `phi_host`; NULL switches it off.  Used by the
  * end-to-end measurement: the device->host read of each step's result is inside rt_solve. */

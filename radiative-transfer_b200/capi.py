@@ -24,7 +24,11 @@ EXPORTS = (
     "rt_moments_group_major", "rt_balance", "rt_group_ends", "rt_get_group_terms", "rt_get_psi_source",
     "rt_validate", "rt_set_step_output", "rt_get_timing", "rt_reset_timing", "rt_planck_groups", "rt_bench_steps",
     "rt_host_alloc", "rt_host_free", "rt_multigroup_opacities", "rt_set_allreduce", "rt_get_temperature",
-    "rt_planck_groups_noalloc",
+    "rt_planck_groups_noalloc", "rt_nccl_unique_id", "rt_set_nccl",
+    "rt_multi_create", "rt_multi_destroy", "rt_multi_shards", "rt_multi_solve", "rt_multi_run_stages", "rt_multi_reset",
+    "rt_multi_stages_done", "rt_multi_get_psi", "rt_multi_get_ends", "rt_multi_moments", "rt_multi_balance", "rt_multi_group_ends",
+    "rt_multi_get_group_terms", "rt_multi_validate", "rt_multi_get_temperature", "rt_multi_bench_steps", "rt_multi_get_timing",
+    "rt_multi_get_plan",
 )
 
 #: int fn(void *device_buf, size_t count, void *cuda_stream, void *user)  (include/rt_cuda.h: rt_allreduce_fn)
@@ -116,6 +120,27 @@ def lib():
         L.rt_multigroup_opacities.argtypes = [C.c_int, C.c_int, _dp, C.c_double, C.c_double, _dp, _dp, _dp, _dp]
         L.rt_set_allreduce.argtypes = [vp, ALLREDUCE_FN, C.c_void_p]
         L.rt_get_temperature.argtypes = [vp, _dp, _dp]
+        ip = C.POINTER(C.c_int)
+        L.rt_multi_create.argtypes = [C.POINTER(RtParams), C.c_int, ip, C.POINTER(vp)]
+        L.rt_multi_destroy.argtypes = [vp]
+        L.rt_multi_shards.argtypes = [vp, ip, ip, ip, ip]
+        L.rt_multi_solve.argtypes = [vp]
+        L.rt_multi_run_stages.argtypes = [vp, C.c_int]
+        L.rt_multi_reset.argtypes = [vp]
+        L.rt_multi_stages_done.argtypes = [vp, ip]
+        L.rt_multi_get_psi.argtypes = [vp, _dp]
+        L.rt_multi_get_ends.argtypes = [vp, C.c_int, _dp]
+        L.rt_multi_moments.argtypes = [vp, _dp, _dp, _dp]
+        L.rt_multi_balance.argtypes = [vp, _dp]
+        L.rt_multi_group_ends.argtypes = [vp, _dp, _dp]
+        L.rt_multi_get_group_terms.argtypes = [vp] + [_dp] * 6
+        L.rt_multi_validate.argtypes = [vp, _dp, ip]
+        L.rt_multi_get_temperature.argtypes = [vp, _dp, _dp]
+        L.rt_multi_bench_steps.argtypes = [vp, C.c_int, C.c_int, _dp]
+        L.rt_multi_get_timing.argtypes = [vp, C.c_int, C.POINTER(RtTiming)]
+        L.rt_multi_get_plan.argtypes = [vp, C.c_int, C.POINTER(RtPlan)]
+        L.rt_nccl_unique_id.argtypes = [C.c_void_p]
+        L.rt_set_nccl.argtypes = [vp, C.c_void_p, C.c_int, C.c_int]
         _lib = L
     return _lib
 

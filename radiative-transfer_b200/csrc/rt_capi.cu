@@ -85,6 +85,7 @@ struct rt_solver
    int *d_T_bad = nullptr;         // 0, or the number of the first update that left some cell with T <= 0 or a non-finite T
    rt_allreduce_fn allreduce = nullptr;
    void *allreduce_user = nullptr;
+   void *nccl_comm = nullptr;      // communicator created by rt_set_nccl (owned by the handle) ; rt_multi owns its own
    // batching
    int Gl = 0, Gb = 0, n_batches = 0, Np = 0;
    size_t buf_elems = 0; // double2 elements per time-level buffer
@@ -416,6 +417,8 @@ static int load_batch(rt_solver *s, int start)
    return 0;
 }
 
+static void release_nccl(rt_solver *s); // (NCCL section at the end of the file)
+
 // time-level buffers are allocated on demand: two for the fused step, four when a step runs stage by stage
 static int ensure_levels(rt_solver *s, int n)
 {
@@ -460,6 +463,7 @@ extern "C" int rt_destroy(rt_solver *s)
    if (s->d_ticket) cudaFree(s->d_ticket);
    for (auto &ep : s->ev_pool) { cudaEventDestroy(ep.a); cudaEventDestroy(ep.b); }
    for (int k = 0; k < 2; ++k) if (s->step_ev[k]) cudaEventDestroy(s->step_ev[k]);
+   release_nccl(s);
    if (s->copy_st) cudaStreamDestroy(s->copy_st);
    if (s->st) cudaStreamDestroy(s->st);
    delete s;
@@ -1671,3 +1675,129 @@ extern "C" int rt_planck_groups_noalloc(int device, int G, const double *e_edge,
    CK(cudaMemcpy(dBdT, d_tmp, n * sizeof(double), cudaMemcpyDeviceToHost));
    return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Native NCCL for the material-temperature update's exchange (the ONE collective of the path).
+// libnccl.so.2 is loaded with dlopen the first time it is asked for: a single-GPU host needs nothing new, and a process
+// that already holds NCCL (torch) gets that very copy.  The types NCCL's ABI needs are declared here (nccl.h:37-38,
+// 260-286, 392): no header or link-time dependency.  The all-reduce itself goes through the handle's existing hook
+// (rt_set_allreduce), so temperature_update() has one code path whoever provides the sum.
+#include <dlfcn.h>
+
+namespace
+{
+struct NcclId { char internal[128]; };
+typedef void *NcclComm;
+struct NcclApi
+{
+   int (*GetUniqueId)(NcclId *) = nullptr;
+   int (*CommInitRank)(NcclComm *, int, NcclId, int) = nullptr;
+   int (*CommInitAll)(NcclComm *, int, const int *) = nullptr;
+   int (*CommDestroy)(NcclComm) = nullptr;
+   int (*AllReduce)(const void *, void *, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
+   const char *(*GetErrorString)(int) = nullptr;
+   void *dl = nullptr;
+};
+constexpr int NCCL_DOUBLE = 8, NCCL_SUM = 0;
+
+// nullptr (and the error message set) when NCCL cannot be loaded
+NcclApi *nccl_api()
+{
+   static NcclApi api;
+   static std::atomic<int> state{0}; // 0 untried, 1 ready, -1 failed
+   static std::string why;
+   if (state.load(std::memory_order_acquire) == 0)
+   {
+      const char *name = getenv("RT_CUDA_NCCL_LIB");
+      void *dl = dlopen(name ? name : "libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+      if (!dl && !name) dl = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+      bool ok = dl != nullptr;
+      if (!ok) why = std::string("dlopen(libnccl.so.2): ") + (dlerror() ? dlerror() : "not found");
+      auto sym = [&](const char *n) -> void * {
+         void *p = ok ? dlsym(dl, n) : nullptr;
+         if (ok && !p) { ok = false; why = std::string("libnccl has no symbol ") + n; }
+         return p;
+      };
+      api.GetUniqueId = (decltype(api.GetUniqueId))sym("ncclGetUniqueId");
+      api.CommInitRank = (decltype(api.CommInitRank))sym("ncclCommInitRank");
+      api.CommInitAll = (decltype(api.CommInitAll))sym("ncclCommInitAll");
+      api.CommDestroy = (decltype(api.CommDestroy))sym("ncclCommDestroy");
+      api.AllReduce = (decltype(api.AllReduce))sym("ncclAllReduce");
+      api.GetErrorString = (decltype(api.GetErrorString))sym("ncclGetErrorString");
+      api.dl = dl;
+      state.store(ok ? 1 : -1, std::memory_order_release);
+   }
+   if (state.load(std::memory_order_acquire) != 1)
+   {
+      fail("rt: NCCL is not available (%s); set RT_CUDA_NCCL_LIB to the library, or pass your own sum with rt_set_allreduce", why.c_str());
+      return nullptr;
+   }
+   return &api;
+}
+
+// the hook installed by rt_set_nccl / rt_multi: in-place sum on the library's own device buffer, on the library's stream
+int nccl_allreduce_hook(void *buf, size_t count, void *stream, void *user)
+{
+   NcclApi *api = nccl_api();
+   if (!api) return 1;
+   const int rc = api->AllReduce(buf, buf, count, NCCL_DOUBLE, NCCL_SUM, (NcclComm)user, (cudaStream_t)stream);
+   if (rc != 0) fprintf(stderr, "rt: ncclAllReduce failed: %s\n", api->GetErrorString(rc));
+   return rc;
+}
+} // namespace
+
+static void release_nccl(rt_solver *s)
+{
+   if (!s->nccl_comm) return;
+   if (NcclApi *api = nccl_api()) api->CommDestroy((NcclComm)s->nccl_comm);
+   s->nccl_comm = nullptr;
+}
+
+extern "C" int rt_nccl_unique_id(void *id128)
+{
+   if (!id128) return fail("rt_nccl_unique_id: null argument");
+   NcclApi *api = nccl_api();
+   if (!api) return 1;
+   NcclId id;
+   const int rc = api->GetUniqueId(&id);
+   if (rc != 0) return fail("rt_nccl_unique_id: ncclGetUniqueId -> %s", api->GetErrorString(rc));
+   std::memcpy(id128, id.internal, sizeof id.internal);
+   return 0;
+}
+
+extern "C" int rt_set_nccl(rt_solver *s, const void *id128, int nranks, int rank)
+{
+   if (!s || !id128) return fail("rt_set_nccl: null argument");
+   if (nranks < 1 || rank < 0 || rank >= nranks) return fail("rt_set_nccl: rank %d outside [0,%d)", rank, nranks);
+   NcclApi *api = nccl_api();
+   if (!api) return 1;
+   CK(cudaSetDevice(s->p.device));
+   release_nccl(s);
+   NcclId id;
+   std::memcpy(id.internal, id128, sizeof id.internal);
+   NcclComm comm = nullptr;
+   const int rc = api->CommInitRank(&comm, nranks, id, rank);
+   if (rc != 0 || !comm) return fail("rt_set_nccl: ncclCommInitRank(rank %d of %d, device %d) -> %s", rank, nranks, s->p.device, api->GetErrorString(rc));
+   s->nccl_comm = comm;
+   s->allreduce = nccl_allreduce_hook;
+   s->allreduce_user = comm;
+   return 0;
+}
+
+// ---- helpers for rt_multi.cu (rt_internal.h)
+#include "rt_internal.h"
+int rt_internal_fail(const char *msg) { return fail("%s", msg); }
+int rt_internal_nccl_init_all(void **comms, int ndev, const int *devices)
+{
+   NcclApi *api = nccl_api();
+   if (!api) return 1;
+   const int rc = api->CommInitAll((NcclComm *)comms, ndev, devices);
+   if (rc != 0) return fail("rt: ncclCommInitAll over %d devices -> %s", ndev, api->GetErrorString(rc));
+   return 0;
+}
+void rt_internal_nccl_destroy(void *comm)
+{
+   if (!comm) return;
+   if (NcclApi *api = nccl_api()) api->CommDestroy((NcclComm)comm);
+}
+int rt_internal_nccl_hook(void *device_buf, size_t count, void *cuda_stream, void *user) { return nccl_allreduce_hook(device_buf, count, cuda_stream, user); }

@@ -123,8 +123,33 @@ Solver::Solver(ParameterHandler &parameter_handler,
    p.use_correction = ph.get_use_correction() ? 1 : 0;
    p.use_mg_equilib = ph.get_use_mg_equilib() ? 1 : 0;
    p.validate = ph.get_validation() ? 1 : 0;
-   const char *dev = getenv("RT_CUDA_DEVICE");
-   p.device = dev ? atoi(dev) : 0;
+   // GPUs: RT_CUDA_DEVICES = a count ("8": devices 0..7) or a list ("0,2,5"); default: the one device RT_CUDA_DEVICE (or 0).
+   // The energy groups are sharded over them inside the library (rt_multi_*, one host thread per device).
+   std::vector<int> devices;
+   if (const char *dl = getenv("RT_CUDA_DEVICES"))
+   {
+      const std::string str(dl);
+      if (str.find(',') == std::string::npos) { for (int k = 0; k < atoi(dl); ++k) devices.push_back(k); }
+      else
+      {
+         size_t pos = 0;
+         while (pos <= str.size())
+         {
+            const size_t e = str.find(',', pos);
+            const std::string tok = str.substr(pos, e == std::string::npos ? std::string::npos : e - pos);
+            if (!tok.empty()) devices.push_back(atoi(tok.c_str()));
+            if (e == std::string::npos) break;
+            pos = e + 1;
+         }
+      }
+   }
+   if (devices.empty())
+   {
+      const char *dev = getenv("RT_CUDA_DEVICE");
+      devices.push_back(dev ? atoi(dev) : 0);
+   }
+   if ((int)devices.size() > num_groups) devices.resize(num_groups); // at least one group per shard
+   p.device = devices[0];
    p.groups_per_batch = 0;
    p.dx = ph.get_dx(); p.dt = ph.get_dt(); p.rho = ph.get_rho(); p.T = ph.get_T(); p.V = ph.get_V();
    p.kappa_grey = ph.get_kappa_grey();
@@ -132,12 +157,18 @@ Solver::Solver(ParameterHandler &parameter_handler,
    p.psi_source = have_src ? src.data() : nullptr;
    p.rho_cell = p.T_cell = p.kappa_cell = nullptr; // the reference's slab is uniform (solver.cpp:150-157)
    p.cv = 0.0;                                     // and its temperature never changes
-   if (rt_create(&p, &handle)) die("Solver");
+   if (rt_multi_create(&p, (int)devices.size(), devices.data(), &handle)) die("Solver");
+   if (devices.size() > 1)
+   {
+      cout << "energy groups sharded over " << devices.size() << " GPUs:";
+      for (int d : devices) cout << " " << d;
+      cout << endl;
+   }
 
    // initial condition psi = B_g, evaluated on the device (solver.cpp:166-181)
    pull_psi();
    std::vector<double> B(num_groups);
-   if (rt_get_group_terms(handle, B.data(), nullptr, nullptr, nullptr, nullptr, nullptr)) die("Solver");
+   if (rt_multi_get_group_terms(handle, B.data(), nullptr, nullptr, nullptr, nullptr, nullptr)) die("Solver");
    cout << "B:";
    for (int g = 0; g < num_groups; ++g) cout << " " << B[g];
    cout << endl;
@@ -146,19 +177,24 @@ Solver::Solver(ParameterHandler &parameter_handler,
 
 Solver::~Solver()
 {
-   if (handle) rt_destroy(handle);
+   if (handle) rt_multi_destroy(handle);
    handle = nullptr;
 }
 
 // psi of the current state into the caller's tensor (reference index order == the C ABI's)
 void Solver::pull_psi()
 {
-   rt_plan plan;
-   if (rt_get_plan(handle, &plan)) die("Solver");
-   if (!plan.resident) return; // batched solves keep psi on the device; moments remain available
+   int shards = 0;
+   if (rt_multi_shards(handle, &shards, nullptr, nullptr, nullptr)) die("Solver");
+   for (int k = 0; k < shards; ++k)
+   {
+      rt_plan plan;
+      if (rt_multi_get_plan(handle, k, &plan)) die("Solver");
+      if (!plan.resident) return; // batched solves keep psi on the device; moments remain available
+   }
    const size_t n = (size_t)M * num_groups * N;
    stage_buf.resize(n);
-   if (rt_get_psi(handle, stage_buf.data())) die("Solver");
+   if (rt_multi_get_psi(handle, stage_buf.data())) die("Solver");
    size_t k = 0;
    for (int c = 0; c < N; ++c)
       for (int g = 0; g < num_groups; ++g)
@@ -170,7 +206,7 @@ void Solver::pull_moment(int which, Eigen::Ref<Eigen::MatrixXd> dst)
    const size_t n = (size_t)num_groups * N;
    stage_buf.resize(n);
    double *b = stage_buf.data();
-   if (rt_moments(handle, which == 0 ? b : nullptr, which == 1 ? b : nullptr, which == 2 ? b : nullptr)) die("Solver");
+   if (rt_multi_moments(handle, which == 0 ? b : nullptr, which == 1 ? b : nullptr, which == 2 ? b : nullptr)) die("Solver");
    size_t k = 0;
    for (int c = 0; c < N; ++c)
       for (int g = 0; g < num_groups; ++g) dst(g, c) = b[k++];
@@ -179,9 +215,9 @@ void Solver::pull_moment(int which, Eigen::Ref<Eigen::MatrixXd> dst)
 void Solver::solve()
 {
    // the whole stage loop of solver.cpp:590-823 runs on the device; validation failure is fatal like the assert
-   if (rt_solve(handle)) die("Solver::solve");
+   if (rt_multi_solve(handle)) die("Solver::solve");
    int done = 0;
-   rt_stages_done(handle, &done);
+   rt_multi_stages_done(handle, &done);
    cout << "============= stage sweeps: " << done << " =============" << endl;
    pull_psi();
 }
@@ -195,7 +231,7 @@ void Solver::compute_radiative_flux() { pull_moment(2, F_ref); }
 void Solver::compute_balance()
 {
    stage_buf.resize(num_groups);
-   if (rt_balance(handle, stage_buf.data())) die("Solver::compute_balance");
+   if (rt_multi_balance(handle, stage_buf.data())) die("Solver::compute_balance");
    for (int g = 0; g < num_groups; ++g)
    {
       balance(g) = stage_buf[g];
@@ -206,7 +242,7 @@ void Solver::compute_balance()
 void Solver::compute_group_ends()
 {
    std::vector<double> l(num_groups), r(num_groups);
-   if (rt_group_ends(handle, l.data(), r.data())) die("Solver::compute_group_ends");
+   if (rt_multi_group_ends(handle, l.data(), r.data())) die("Solver::compute_group_ends");
    for (int g = 0; g < num_groups; ++g) { left_ends(g) = l[g]; right_ends(g) = r[g]; }
 }
 

@@ -25,7 +25,7 @@
 #include <string>
 #include <vector>
 
-struct rt_solver; // include/rt_cuda.h
+struct rt_multi; // include/rt_cuda.h: the multi-device handle (one shard per GPU of RT_CUDA_DEVICES)
 
 using namespace std;
 
@@ -54,7 +54,7 @@ private:
    Eigen::MatrixXd phi_plus;
    Eigen::VectorXd balance, left_ends, right_ends;
 
-   rt_solver *handle;
+   rt_multi *handle;
    std::vector<double> stage_buf; // contiguous staging between the C ABI and Eigen objects
 
    void die(const char *where) const;
@@ -85,7 +85,7 @@ public:
    void get_ends(const string side, Eigen::Ref<Eigen::VectorXd> group_ends);
 
    // additions (not in the reference): the handle for callers that want timing / per-step hooks
-   rt_solver *c_handle() const { return handle; }
+   rt_multi *c_handle() const { return handle; }
 };
 } // End namespace rt
 #endif // SOLVER

@@ -119,3 +119,20 @@ def make_allreduce_hook(dist, device: int):
             return 1
 
     return capi.ALLREDUCE_FN(hook)
+
+
+def broadcast_nccl_id(dist, device: int):
+    """The 128-byte ncclUniqueId for rt_set_nccl (include/rt_cuda.h): made by rank 0 inside the library, handed to every
+    rank through torch.distributed (the host's own transport, used once at set-up -- never in the time loop).
+    Returns a ctypes buffer."""
+    import ctypes as C
+    import torch
+    from . import capi
+    buf = C.create_string_buffer(128)
+    if dist.get_rank() == 0:
+        capi.check(capi.lib().rt_nccl_unique_id(buf))
+    dev = torch.device("cuda", device) if dist.get_backend() == "nccl" else torch.device("cpu")
+    t = torch.tensor(list(buf.raw), dtype=torch.uint8, device=dev)
+    dist.broadcast(t, src=0)
+    C.memmove(buf, bytes(t.cpu().tolist()), 128)
+    return buf

@@ -28,7 +28,7 @@ class Solver:
     def __init__(self, parameter_handler: Parameters, psi_mat: Optional[np.ndarray] = None,
                  phi: Optional[np.ndarray] = None, F: Optional[np.ndarray] = None, *, device: int = 0,
                  group_begin: int = 0, group_count: Optional[int] = None, groups_per_batch: int = 0,
-                 fetch_psi: bool = True, dist=None):
+                 fetch_psi: bool = True, dist=None, devices=None):
         ph = self.ph = parameter_handler
         self.M, self.N, self.num_groups = ph.M, ph.N, ph.G
         self.group_begin = group_begin
@@ -90,21 +90,49 @@ class Solver:
         # extension: material-temperature update when the specific heat is given
         p.cv = float(getattr(ph, "cv", 0.0) or 0.0)
         self._h = C.c_void_p()
-        capi.check(capi.lib().rt_create(C.byref(p), C.byref(self._h)))
+        # devices=[d0, d1, ...]: ONE process, several GPUs -- the library shards the owned groups itself (rt_multi_*,
+        # csrc/rt_multi.cu), the way the C++ drop-in does with RT_CUDA_DEVICES; results come back over all owned groups
+        self._multi = devices is not None
+        if self._multi:
+            devs = (C.c_int * len(devices))(*[int(d) for d in devices])
+            capi.check(capi.lib().rt_multi_create(C.byref(p), len(devices), devs, C.byref(self._h)))
+            self._n_shards = len(devices)
+        else:
+            capi.check(capi.lib().rt_create(C.byref(p), C.byref(self._h)))
         # a group shard of a temperature-coupled solve: the group sums go through torch.distributed (NCCL) every step
         self._allreduce = None
-        if p.cv > 0.0 and dist is not None and dist.is_initialized() and dist.get_world_size() > 1:
+        self.exchange = "none (this handle owns every group)"
+        if self._multi and p.cv > 0.0 and len(devices) > 1:
+            self.exchange = "ncclAllReduce inside the library (rt_multi: one communicator per device, one process)"
+        elif p.cv > 0.0 and dist is not None and dist.is_initialized() and dist.get_world_size() > 1:
             from . import sharding
-            self._allreduce = sharding.make_allreduce_hook(dist, device)
-            capi.check(capi.lib().rt_set_allreduce(self._h, self._allreduce, None))
-        self.resident = self.plan().resident == 1
+            import os
+            if os.environ.get("RT_CUDA_ALLREDUCE", "nccl") == "torch":
+                # the host's own sum: torch.distributed.all_reduce on the library's buffer, called back from the time loop
+                self._allreduce = sharding.make_allreduce_hook(dist, device)
+                capi.check(capi.lib().rt_set_allreduce(self._h, self._allreduce, None))
+                self.exchange = "torch.distributed all_reduce through the rt_set_allreduce callback"
+            else:
+                # native: the library creates its own NCCL communicator and calls ncclAllReduce on its stream
+                capi.check(capi.lib().rt_set_nccl(self._h, sharding.broadcast_nccl_id(dist, device), dist.get_world_size(), dist.get_rank()))
+                self.exchange = "ncclAllReduce inside the library (rt_set_nccl)"
+        self.resident = all(self.plan(k).resident == 1 for k in range(self._n_shards)) if self._multi else self.plan().resident == 1
         if fetch_psi and self.resident:
             self._pull_psi()  # initial condition psi = B_g (solver.cpp:166-181)
+
+    def _f(self, name):
+        """the entry point `rt_<name>` of a single handle, or `rt_multi_<name>` of a multi-device handle"""
+        if self._multi:
+            fn = getattr(capi.lib(), "rt_multi_" + name, None)
+            if fn is None:
+                raise capi.RtError(f"rt_{name} is not available on a multi-device handle (devices=[...])")
+            return fn
+        return getattr(capi.lib(), "rt_" + name)
 
     # ------------------------------------------------------------------ lifetime
     def close(self):
         if getattr(self, "_h", None):
-            capi.lib().rt_destroy(self._h)
+            self._f("destroy")(self._h)
             self._h = None
 
     def __del__(self):
@@ -134,21 +162,21 @@ class Solver:
 
     def solve(self):
         """solver.cpp:590-823"""
-        capi.check(capi.lib().rt_solve(self._h))
+        capi.check(self._f("solve")(self._h))
         if self._fetch_psi and self.resident:
             self._pull_psi()
 
     def compute_angle_integrated_intensity(self):
-        capi.check(capi.lib().rt_moments(self._h, capi.ptr(self.phi_ref), None, None))
+        capi.check(self._f("moments")(self._h, capi.ptr(self.phi_ref), None, None))
 
     def compute_positive_angle_integrated_intensity(self):
-        capi.check(capi.lib().rt_moments(self._h, None, capi.ptr(self.phi_plus), None))
+        capi.check(self._f("moments")(self._h, None, capi.ptr(self.phi_plus), None))
 
     def compute_radiative_flux(self):
-        capi.check(capi.lib().rt_moments(self._h, None, None, capi.ptr(self.F_ref)))
+        capi.check(self._f("moments")(self._h, None, None, capi.ptr(self.F_ref)))
 
     def compute_balance(self):
-        capi.check(capi.lib().rt_balance(self._h, capi.ptr(self.balance)))
+        capi.check(self._f("balance")(self._h, capi.ptr(self.balance)))
 
     def get_balance(self):
         return self.balance.copy()
@@ -160,7 +188,7 @@ class Solver:
         return self.e_ave.copy()
 
     def compute_group_ends(self):
-        capi.check(capi.lib().rt_group_ends(self._h, capi.ptr(self.left_ends), capi.ptr(self.right_ends)))
+        capi.check(self._f("group_ends")(self._h, capi.ptr(self.left_ends), capi.ptr(self.right_ends)))
 
     def get_ends(self, side: str):
         assert side in ("left", "right"), "Invalid option for 'side'."
@@ -219,7 +247,7 @@ class Solver:
                      dtype=np.int64).tofile(f)
             while self.stages_done < self.total_stages:
                 todo = min(every * per_step, self.total_stages - self.stages_done)
-                capi.check(capi.lib().rt_run_stages(self._h, int(todo)))
+                capi.check(self._f("run_stages")(self._h, int(todo)))
                 phi, pp, F = self.moments_group_major()
                 np.array([self.stages_done // per_step, self.stages_done], dtype=np.int64).tofile(f)
                 for a in (phi, pp, F):
@@ -250,39 +278,43 @@ class Solver:
                 yield rec
 
     def _pull_psi(self):
-        capi.check(capi.lib().rt_get_psi(self._h, capi.ptr(self.psi_mat_ref)))
+        capi.check(self._f("get_psi")(self._h, capi.ptr(self.psi_mat_ref)))
 
     def run_stages(self, n: int):
-        capi.check(capi.lib().rt_run_stages(self._h, int(n)))
+        capi.check(self._f("run_stages")(self._h, int(n)))
         if self._fetch_psi and self.resident:
             self._pull_psi()
 
     def reset(self):
-        capi.check(capi.lib().rt_reset(self._h))
+        capi.check(self._f("reset")(self._h))
 
     @property
     def stages_done(self) -> int:
         n = C.c_int()
-        capi.check(capi.lib().rt_stages_done(self._h, C.byref(n)))
+        capi.check(self._f("stages_done")(self._h, C.byref(n)))
         return n.value
 
     @property
     def total_stages(self) -> int:
+        if self._multi:
+            return self.ph.max_timesteps * (4 if self.ph.ts_method == 3 else 1)
         n = C.c_int()
         capi.check(capi.lib().rt_total_stages(self._h, C.byref(n)))
         return n.value
 
     def ends(self, which: int = 0):
         a = _f((self.M, self.group_count, self.N, 2))
-        capi.check(capi.lib().rt_get_ends(self._h, which, capi.ptr(a)))
+        capi.check(self._f("get_ends")(self._h, which, capi.ptr(a)))
         return a
 
     def moments(self):
         phi, pp, F = (_f((self.group_count, self.N)) for _ in range(3))
-        capi.check(capi.lib().rt_moments(self._h, capi.ptr(phi), capi.ptr(pp), capi.ptr(F)))
+        capi.check(self._f("moments")(self._h, capi.ptr(phi), capi.ptr(pp), capi.ptr(F)))
         return phi, pp, F
 
     def moments_group_major(self):
+        if self._multi:
+            return tuple(np.ascontiguousarray(a) for a in self.moments())
         phi, pp, F = (np.zeros((self.group_count, self.N)) for _ in range(3))
         capi.check(capi.lib().rt_moments_group_major(self._h, capi.ptr(phi), capi.ptr(pp), capi.ptr(F)))
         return phi, pp, F
@@ -291,7 +323,7 @@ class Solver:
         G = self.num_groups
         out = {k: np.zeros(G) for k in ("B", "dBdT", "dEB", "dsigEdE", "dkapEB")}
         out["kappa_edge"] = np.zeros(G + 1)
-        capi.check(capi.lib().rt_get_group_terms(
+        capi.check(self._f("get_group_terms")(
             self._h, *[capi.ptr(out[k]) for k in ("B", "dBdT", "dEB", "dsigEdE", "dkapEB", "kappa_edge")]))
         return out
 
@@ -300,41 +332,55 @@ class Solver:
         power, emission derivative; after the all-reduce) of the most recent temperature update"""
         T = np.zeros(self.N)
         sums = np.zeros((3, self.N)) if with_sums else None
-        capi.check(capi.lib().rt_get_temperature(self._h, capi.ptr(T), capi.ptr(sums) if with_sums else None))
+        capi.check(self._f("get_temperature")(self._h, capi.ptr(T), capi.ptr(sums) if with_sums else None))
         return (T, sums[0], sums[1], sums[2]) if with_sums else T
 
     def psi_source(self):
         a = _f((self.M, self.num_groups))
-        capi.check(capi.lib().rt_get_psi_source(self._h, capi.ptr(a)))
+        capi.check(self._f("get_psi_source")(self._h, capi.ptr(a)))
         return a
 
     def validate(self):
         sums = np.zeros(3)
         ok = C.c_int()
-        capi.check(capi.lib().rt_validate(self._h, capi.ptr(sums), C.byref(ok)))
+        capi.check(self._f("validate")(self._h, capi.ptr(sums), C.byref(ok)))
         return bool(ok.value), sums
 
     def set_step_output(self, phi_host_ptr, group_major: bool = True):
-        capi.check(capi.lib().rt_set_step_output(self._h, phi_host_ptr, int(group_major)))
+        capi.check(self._f("set_step_output")(self._h, phi_host_ptr, int(group_major)))
 
     def bench_steps(self, warmup_steps: int, timed_steps: int) -> float:
         """device milliseconds of exactly `timed_steps` time steps of all owned groups (summed over batches)"""
         ms = C.c_double()
-        capi.check(capi.lib().rt_bench_steps(self._h, warmup_steps, timed_steps, C.cast(C.byref(ms), C.POINTER(C.c_double))))
+        capi.check(self._f("bench_steps")(self._h, warmup_steps, timed_steps, C.cast(C.byref(ms), C.POINTER(C.c_double))))
         return ms.value
 
-    def timing(self) -> capi.RtTiming:
+    def timing(self, shard: int = 0) -> capi.RtTiming:
         t = capi.RtTiming()
-        capi.check(capi.lib().rt_get_timing(self._h, C.byref(t)))
+        if self._multi:
+            capi.check(capi.lib().rt_multi_get_timing(self._h, int(shard), C.byref(t)))
+        else:
+            capi.check(capi.lib().rt_get_timing(self._h, C.byref(t)))
         return t
 
     def reset_timing(self):
-        capi.check(capi.lib().rt_reset_timing(self._h))
+        capi.check(self._f("reset_timing")(self._h))
 
-    def plan(self) -> capi.RtPlan:
+    def plan(self, shard: int = 0) -> capi.RtPlan:
         pl = capi.RtPlan()
-        capi.check(capi.lib().rt_get_plan(self._h, C.byref(pl)))
+        if self._multi:
+            capi.check(capi.lib().rt_multi_get_plan(self._h, int(shard), C.byref(pl)))
+        else:
+            capi.check(capi.lib().rt_get_plan(self._h, C.byref(pl)))
         return pl
+
+    def shards(self):
+        """[(first group, groups, device)] of a multi-device handle"""
+        n = C.c_int()
+        capi.check(capi.lib().rt_multi_shards(self._h, C.byref(n), None, None, None))
+        g0, gn, dev = ((C.c_int * n.value)() for _ in range(3))
+        capi.check(capi.lib().rt_multi_shards(self._h, C.byref(n), g0, gn, dev))
+        return [(g0[k], gn[k], dev[k]) for k in range(n.value)]
 
 
 def planck_groups(e_edge, T, device: int = 0):
