@@ -369,6 +369,8 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     sharding = importlib.import_module("radiative-transfer_b200.sharding")
+    # each rank on the NUMA node of its GPU before any pinned buffer exists (the e2e path drains phi to the host every step)
+    numa = sharding.bind_to_gpu_numa_node(local_rank) if (world > 1 and os.environ.get("RT_NUMA_BIND", "1") != "0") else {"bound": False}
     g0, gn = sharding.group_range(G, world, rank)
     K, W = args.steps, args.warmup
     p = synthetic_parameters(rt, M, G, N, bcl, bcr, args.dt, K, V=args.V)
@@ -430,13 +432,15 @@ def main():
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                     "traffic": per_unknown * unknowns_per_launch if per_unknown else None,
                     "algorithmic_bytes_per_launch": alg, "avg_launch_ms": avg_ms, "peak_source": peak_src,
-                    "kernel": "rtk::step_warp_kernel<CORR,CPT,NW> (BE,CN,BE,BDF fused: one launch per BDF2 step and batch)",
+                    "kernel": "rtk::step_warp_kernel<CORR,8,4> (BE,CN,BE,BDF fused: one launch per BDF2 step and batch; plain steps) -- steps that also deliver phi run rtk::step4_kernel<CORR,PHI,4> (the e2e path)",
                     "algorithmic_bytes_per_unknown_step": STEP_BYTES_PER_UNKNOWN,
-                    "note": "DRAM traffic = the algorithmic 32 B per unknown and step; the kernel is issue/latency bound at 16 warps "
-                            "per SM (profiles/r01_v6_step_ncu_full_wide.txt: issue slots 55 %, fp64 pipe 35 %); run stage by stage "
-                            "the same step moves 176 B per unknown",
+                    "note": "DRAM traffic = the algorithmic 32 B per unknown and step (ncu on C4: 32.3); the kernel is bound by the latency "
+                            "of dependent instructions at 16 warps per SM (profiles/r02_step_ncu_full_c4.txt: issue slots 54 %, fp64 pipe "
+                            "35 %, stalls wait 33 % + short scoreboard 23 %); run stage by stage the same step moves 176 B per unknown",
                     "staged_equivalent_GBps": sum(bpu[k] * (2 if k == "BE" else 1) for k in kinds) * unknowns_per_launch / (avg_ms * 1e-3) / 1e9,
-                    "fp64_pipe_pct": tr.get("step_fp64_pipe_pct"), "issue_active_pct": tr.get("step_issue_active_pct")}
+                    "fp64_pipe_pct": tr.get("step_fp64_pipe_pct"), "issue_active_pct": tr.get("step_issue_active_pct"),
+                    "traffic_source": tr.get("step_source"), "traffic_build": tr.get("step_build"),
+                    "traffic_note": "traffic / fp64 / issue figures come from the ncu capture named in traffic_source, scaled by the unknowns of THIS run's launches; achieved / frac are measured live in this run"}
     else:
         alg_bytes = sum(bpu[k] * unknowns_per_launch * tm.sweep_launches[i] for i, k in enumerate(kinds))
         sweep_ms = sum(tm.sweep_ms)
@@ -496,6 +500,7 @@ def main():
         e2e = {"value": unknown_stages / wall_max, "unit": UNIT, "h2d_bytes_per_step": int(tm2.h2d_bytes // K),
                "d2h_bytes_per_step": int(tm2.d2h_bytes // K), "wall_s": wall_max,
                "setup_s": t_setup, "moments_ms_per_step": tm2.moments_ms / K,
+               "numa_bind": numa,
                "what": "Solver(params) [tables H2D, Planck+correction terms, state init] + solve() of K steps with phi of every "
                        "step copied to pinned host memory; wall clock incl. allocation"}
 

@@ -136,3 +136,40 @@ def broadcast_nccl_id(dist, device: int):
     dist.broadcast(t, src=0)
     C.memmove(buf, bytes(t.cpu().tolist()), 128)
     return buf
+
+
+def bind_to_gpu_numa_node(device: int):
+    """Pin this process to the CPU cores of the NUMA node its GPU hangs off, so that pinned host buffers allocated
+    afterwards (first touch) and the copy engine's writes stay on that node.  With 8 ranks draining phi to the host at
+    once, buffers on a remote node cost more than half of the PCIe rate (profiles/r02_d2h_ceiling.json).
+    Returns a dict describing what was done (nothing, when the topology cannot be read)."""
+    import os
+    info = {"device": device, "numa_node": None, "cpus": None, "bound": False}
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(device)
+        bus = None
+        if all(hasattr(pr, k) for k in ("pci_domain_id", "pci_bus_id", "pci_device_id")) and isinstance(pr.pci_bus_id, int):
+            bus = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        if bus is None:
+            import subprocess
+            bus = subprocess.run(["nvidia-smi", "-i", str(device), "--query-gpu=pci.bus_id", "--format=csv,noheader"],
+                                 capture_output=True, text=True, timeout=10).stdout.strip()
+        bus = str(bus).lower()
+        if bus.count(":") == 2 and len(bus.split(":")[0]) == 8:
+            bus = bus[4:]  # nvidia-smi prints an 8-digit domain, sysfs uses 4
+        node = int(open(f"/sys/bus/pci/devices/{bus}/numa_node").read())
+        info["numa_node"] = node
+        if node < 0:
+            return info
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= set(os.sched_getaffinity(0))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            info["cpus"], info["bound"] = len(cpus), True
+    except Exception as exc:  # best effort: an unreadable topology must not stop a run
+        info["error"] = repr(exc)
+    return info

@@ -23,7 +23,7 @@ def main():
     rt = importlib.import_module("radiative-transfer_b200")
     sh = importlib.import_module("radiative-transfer_b200.sharding")
     import oracle_py
-    from parity_util import make_oracle, state_ok, synthetic_parameters
+    from parity_util import CELL_FLOOR, make_oracle, state_ok, synthetic_parameters
     G, N, steps = 12, 2000, 3
     p = synthetic_parameters(rt, M=8, G=G, N=N, dt=1e-3, V=1.0, steps=steps, bc_left=2, bc_right=1)
     x = (np.arange(N) + 0.5) / N
@@ -43,7 +43,7 @@ def main():
             errs = [np.max(np.abs(T - T_ref) / T_ref), np.max(np.abs(a - A) / A), np.max(np.abs(e - E) / E), np.max(np.abs(d - D) / D)]
             worst = max(worst, *errs)
             B = np.maximum(o.group_terms()["B"], 1e-300)
-            good, w, _ = state_ok(s.psi_mat_ref, o.psi()[:, g0:g0 + gn, :], B[g0:g0 + gn])
+            good, w, _ = state_ok(s.psi_mat_ref, o.psi()[:, g0:g0 + gn, :], B[g0:g0 + gn], floor=CELL_FLOOR)
             ok = ok and good and max(errs) <= 1e-9
         moved = float(np.max(np.abs(s.temperature() - p.T_cell)))
         tm = s.timing()

@@ -8,6 +8,13 @@ from conftest import GOLDEN, PRM_DIR, host_setup
 #: north_star tolerance: 1e-9 relative on scalar intensity / radiation energy at each BDF2 step
 RTOL = 1e-9
 
+#: absolute floor of the state comparison for CELL-DEPENDENT temperature fields, as a fraction of the group's largest entry.
+#: The reference-pinned uniform cases use 1e-6 (tests/parity_util.py).  With T(c) a high-energy group's intensity varies
+#: by orders of magnitude from cell to cell, and the last group is the reference's own cancellation remainder
+#: a c T^4 - sum of the others (Planck.cpp:58-76): its cold-cell entries carry a relative uncertainty of eps * sum(B) / B_last(T_cold)
+#: that the uniform-T allowance does not describe.  These extensions are parity-unpinned (no reference counterpart).
+CELL_FLOOR = 1e-3
+
 
 def load_golden(name):
     return dict(np.load(os.path.join(GOLDEN, name + ".npz")))
@@ -33,12 +40,14 @@ def rel_err(a, b):
     return float(np.max(r)) if r.size else 0.0
 
 
-def state_err(a, b, group_axis=1, floor=1e-3):
+def state_err(a, b, group_axis=1, floor=1e-6):
     """max |a-b| / (|b| + floor*gmax), gmax = max |b| over the entry's energy group.
 
-    <= RTOL means: 1e-9 relative elementwise, with an absolute floor of 1e-12 x the group's scale for entries that
-    are more than 1000x smaller than the group's largest one (zero crossings of the oscillating DG solution, where
-    an elementwise relative error is meaningless for reference and reformulation alike)."""
+    <= RTOL means: 1e-9 relative elementwise, with an absolute floor of 1e-15 x the group's scale for entries that
+    are more than a million times smaller than the group's largest one (zero crossings of the oscillating DG solution,
+    where an elementwise relative error is meaningless for reference and reformulation alike).  Round 1 used a floor of
+    1e-3; the errors observed on B200 under this stricter measure are <= 0.08 of the tolerance on every golden and
+    synthetic case (tools/gpu_tolerance_audit.py), so a regression of one order of magnitude now fails."""
     a = np.asarray(a, dtype=np.float64)
     b = np.asarray(b, dtype=np.float64)
     if b.size == 0:
@@ -65,7 +74,7 @@ def group_rtol(B):
     return r
 
 
-def state_ok(a, b, B, group_axis=1, floor=1e-3):
+def state_ok(a, b, B, group_axis=1, floor=1e-6):
     """(ok, worst ratio err/tol, per-group errors) for a state array with an energy-group axis; see state_err, group_rtol"""
     a = np.asarray(a, dtype=np.float64)
     b = np.asarray(b, dtype=np.float64)
@@ -77,6 +86,15 @@ def state_ok(a, b, B, group_axis=1, floor=1e-3):
     per_group = np.max(r, axis=axes)
     ratio = per_group / group_rtol(B)
     return bool(np.all(ratio <= 1.0)), float(np.max(ratio)), per_group
+
+
+def flux_err(F, F_ref, phi_ref):
+    """max |F - F_ref| against max |F_ref| -- the flux's OWN scale -- wherever the flux is a meaningful quantity
+    (max |F| > 1e-6 max phi); in equilibrium cases F is a cancellation residue of O(eps phi) and the phi scale is the
+    only one there is (GrayTest's criterion, tests/test_gray.cpp:89, is of that kind).  <= RTOL required."""
+    mF, mphi = float(np.max(np.abs(F_ref))), float(np.max(np.abs(phi_ref)))
+    scale = mF if mF > 1e-6 * mphi else mphi
+    return scaled_err(F, F_ref, scale)
 
 
 def scaled_err(a, b, scale):

@@ -11,7 +11,7 @@ outflow nodes, with a lower-triangular 4x4 transfer matrix per chunk of cells th
 so a lane runs all four stages over its 8 cells with ZERO inflow (pass A, no communication), the warp does ONE
 Kogge-Stone scan of 4-vectors with the tabulated T, T^2, .. T^16 (instead of four dependent scalar scans), and pass B
 adds the response R c_in to the local stage-3 result.  This script emulates exactly that structure (lanes, sub-tiles,
-carries, row-first / junction / ragged handling) and compares it with the serial scan form of scan_form_check.py.
+carries, row-first / junction / ragged handling) and compares it with the serial scan form of scan_form.py.
 Development aid: the kernel's device code is a transliteration of pass_a / chunk_tables below."""
 import importlib
 import os
@@ -20,8 +20,8 @@ import sys
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path[:0] = [ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tools")]
-from scan_form_check import C, coef  # noqa: E402
+sys.path[:0] = [ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "oracle")]
+from scan_form import C, coef  # noqa: E402
 
 CPT, LANES = 8, 32
 WT = CPT * LANES

@@ -13,7 +13,7 @@ import numpy as np
 import pytest
 
 from conftest import PRM_DIR, ROOT
-from parity_util import make_oracle, state_ok, synthetic_parameters
+from parity_util import CELL_FLOOR, make_oracle, state_ok, synthetic_parameters
 
 pytestmark = pytest.mark.gpu
 
@@ -138,7 +138,7 @@ def test_two_gpus_temperature_update_through_nccl_in_one_process(rt, oracle):
             T, a, e, d = s.temperature(with_sums=True)
             for got, ref in ((T, T_ref), (a, A), (e, E), (d, D)):
                 assert np.max(np.abs(got - ref) / np.abs(ref)) <= 1e-9
-            ok, worst, _ = state_ok(s.psi_mat_ref, o.psi(), np.maximum(o.group_terms()["B"], 1e-300))
+            ok, worst, _ = state_ok(s.psi_mat_ref, o.psi(), np.maximum(o.group_terms()["B"], 1e-300), floor=CELL_FLOOR)
             assert ok, worst
         assert np.max(np.abs(s.temperature() - p.T_cell)) > 1e-4
     o.close()

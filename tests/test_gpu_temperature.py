@@ -9,7 +9,7 @@ import os
 import numpy as np
 import pytest
 
-from parity_util import make_oracle, state_ok, synthetic_parameters
+from parity_util import CELL_FLOOR, make_oracle, state_ok, synthetic_parameters
 
 pytestmark = pytest.mark.gpu
 
@@ -42,9 +42,9 @@ def _check_step(s, ref, B, groups=slice(None)):
     assert np.max(np.abs(T - ref["T"]) / ref["T"]) <= RTOL
     for got, want in ((A, ref["A"]), (E, ref["E"]), (D, ref["D"])):
         assert np.max(np.abs(got - want) / np.abs(want)) <= RTOL
-    ok, w, _ = state_ok(s.psi_mat_ref, ref["psi"][:, groups, :], B[groups])
+    ok, w, _ = state_ok(s.psi_mat_ref, ref["psi"][:, groups, :], B[groups], floor=CELL_FLOOR)
     assert ok, f"psi err/tol {w:.3e}"
-    ok, w, _ = state_ok(s.moments()[0], ref["phi"][groups, :], B[groups], group_axis=0)
+    ok, w, _ = state_ok(s.moments()[0], ref["phi"][groups, :], B[groups], group_axis=0, floor=CELL_FLOOR)
     assert ok, f"phi err/tol {w:.3e}"
 
 

@@ -11,7 +11,10 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def test_two_ranks_nccl_match_the_oracle():
+@pytest.mark.parametrize("exchange", ["nccl", "torch"])
+def test_two_ranks_nccl_match_the_oracle(exchange):
+    """exchange = nccl: the library's own communicator and ncclAllReduce (rt_set_nccl, the default) ; torch: the host's
+    torch.distributed.all_reduce called back through rt_set_allreduce"""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
@@ -21,7 +24,7 @@ def test_two_ranks_nccl_match_the_oracle():
     s.close()
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
            "--master-port", str(port), os.path.join(ROOT, "tests", "nccl_temperature_worker.py")]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=dict(os.environ, RT_CUDA_ALLREDUCE=exchange))
     lines = [ln for ln in r.stdout.splitlines() if ln.startswith("NCCL_TEMPERATURE")]
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert len(lines) == 2 and all("ok=True" in ln for ln in lines), lines

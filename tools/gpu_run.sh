@@ -1,6 +1,9 @@
 #!/bin/bash
-# The one GPU-side runner (called through gpurun from the build container):
+# The one runner.  On the GPU box (called through gpurun from the build container):
 #   bash tools/gpu_run.sh <tag> <mode> [args...]          results under gpurun_out/<tag>/
+# In the build container (no GPU):
+#   bash tools/gpu_run.sh <tag> build-rev <git-rev>        full library build of a git revision for A/B runs ->
+#                                                          radiative-transfer_b200/csrc/build/ab/<tag>.so (select it with RT_CUDA_LIB)
 # modes (several may be chained with "--"):
 #   tests [pytest args]     pytest -m gpu (default: whole suite, -x)
 #   bench [bench.py args]   one bench.py line -> bench_<n>.json
@@ -8,6 +11,17 @@
 #   launches [bench args]   ncu launch list (gpu__time_duration.sum) of a short bench run -> launches.csv
 #   ncu <kernel-regex> [bench args]   one --set full capture of the first matching launch -> full.ncu-rep + digest
 TAG=$1; shift
+if [ "$1" == "build-rev" ]; then
+  set -e
+  AB=radiative-transfer_b200/csrc/build/ab; D=$AB/${TAG}_tree
+  rm -rf $D; mkdir -p $D
+  git archive $2 radiative-transfer_b200/csrc include | tar -x -C $D
+  make -C $D/radiative-transfer_b200/csrc > /dev/null
+  cp $D/radiative-transfer_b200/librt_cuda.so $AB/$TAG.so
+  rm -rf $D
+  echo built $AB/$TAG.so
+  exit 0
+fi
 OUT=gpurun_out/$TAG; mkdir -p $OUT
 n=0
 run_mode() {
