@@ -216,12 +216,15 @@ def cell_fields(p, N):
     p.kappa_cell = np.asarray(p.group_kappa)[:, None] * (1.0 + 0.5 * np.sin(7 * np.pi * x))[None, :]
 
 
-def device_timed(rt, sharding, p, dims, local_rank, world, rank, dist, W, K, groups_per_batch=0):
+def device_timed(rt, sharding, p, dims, local_rank, world, rank, dist, W, K, groups_per_batch=0, devices=None):
     """`value` of one workload: exactly K time steps of every owned group after W warm-up steps, CUDA events on the launching
     stream, max over ranks; clocks sampled during the timed region."""
     M, G, N = dims
     g0, gn = sharding.group_range(G, world, rank)
-    s = rt.Solver(p, device=local_rank, group_begin=g0, group_count=gn, groups_per_batch=groups_per_batch, fetch_psi=False, dist=dist)
+    # devices=[...]: ONE process drives several GPUs through the library's multi-device handle (rt_multi_*, what the C++
+    # drop-in uses with RT_CUDA_DEVICES); the time is the slowest shard's device time (CUDA events on every device)
+    s = rt.Solver(p, device=local_rank, group_begin=g0, group_count=gn, groups_per_batch=groups_per_batch, fetch_psi=False, dist=dist,
+                  devices=devices)
     try:
         if dist is not None:
             dist.barrier()
@@ -339,6 +342,8 @@ def main():
     ap.add_argument("--groups", type=int, default=0, help="override the number of groups (debug)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--in-process-gpus", type=int, default=0,
+                    help="ONE process, this many GPUs, sharded inside the library (rt_multi_*): device-timed value only")
     ap.add_argument("--no-extras", action="store_true", help="skip the c5 and temperature_coupled sub-runs of the default command")
     ap.add_argument("--tc-cv", type=float, default=1.0, help="specific heat of the temperature_coupled sub-run")
     ap.add_argument("--tc-dt", type=float, default=1e-5, help="time step of the temperature_coupled sub-run (1e-3 is unstable on c5r)")
@@ -355,6 +360,27 @@ def main():
         N = args.cells
     if args.groups:
         G = args.groups
+
+    if args.in_process_gpus > 0:
+        # the single-process multi-GPU path of the C ABI: no torchrun, no torch.distributed
+        sharding = importlib.import_module("radiative-transfer_b200.sharding")
+        n = args.in_process_gpus
+        if args.workload == "auto":
+            workload = "c5"
+            M, G, N, bcl, bcr = WORKLOADS[workload]
+        K, W = args.steps, args.warmup
+        p = synthetic_parameters(rt, M, G, N, bcl, bcr, args.dt if args.cv == 0.0 else args.tc_dt, K, V=args.V)
+        if args.cv > 0.0:
+            p.cv = args.cv
+            cell_fields(p, N)
+        r = device_timed(rt, sharding, p, (M, G, N), 0, 1, 0, None, W, K, args.groups_per_batch, devices=list(range(n)))
+        emit({"metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": n, "steps": K, "warmup": W, "ms_per_step": r["ms"] / K,
+              "per_gpu_value": r["value"] / n, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+              "data": "synthetic", "config": {"workload": workload, "M": M, "G": G, "N": N, "cv": args.cv, "batches_shard0": r["plan"].n_batches,
+                                               "parallelism": f"ONE process, {n} devices, groups sharded inside the library (rt_multi_*)"},
+              "exchange": r["exchange"], "clocks_device0": r["clocks"], "gpu_launches": int(r["tm"].kernel_launches),
+              "note": "device-timed: slowest shard's CUDA-event time of exactly K steps; timing/launches are shard 0's"})
+        return
 
     if args.impl == "reference":
         if rank == 0:

@@ -69,6 +69,36 @@ PY
         python bench.py --steps 1 --warmup 2 --no-e2e --no-cpu-baseline --no-extras "$@" > $OUT/ncu_run_$n.log 2>&1
     echo "ncu full exit $?"; ls -la $OUT/full_$n.ncu-rep 2>/dev/null
     ncu -i $OUT/full_$n.ncu-rep --page raw --csv > $OUT/full_${n}_raw.csv 2>/dev/null ;;
+  multigpu)
+    # everything that needs N GPUs of one box, N = $1: host-drain ceiling (bound / unbound), bench under torchrun, the
+    # single-process path of the C ABI
+    local N=$1; shift
+    local TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1"
+    for k in 1 2 4 8; do
+      [ $k -gt $N ] && continue
+      for b in 1 0; do
+        RT_NUMA_BIND=$b timeout 120 $TR --nproc-per-node $k --master-port $((29600 + k)) tools/d2h_ceiling.py 2>/dev/null | grep '^{' > $OUT/d2h_n${k}_bind$b.json
+        python -c "import json; d=json.load(open('$OUT/d2h_n${k}_bind$b.json')); print('d2h n=$k bind=$b per-gpu min/max %.1f/%.1f total %.1f GB/s' % (d['GBps_per_gpu_min'], d['GBps_per_gpu_max'], d['GBps_total']), d['numa_bind_rank0'])" 2>&1 | tail -1
+      done
+    done
+    timeout 900 $TR --nproc-per-node $N --master-port 29700 bench.py --gpus $N --steps 5 --warmup 3 > $OUT/bench_n$N.json 2> $OUT/bench_n$N.err; echo "bench n=$N exit $?"
+    RT_NUMA_BIND=0 timeout 600 $TR --nproc-per-node $N --master-port 29701 bench.py --gpus $N --steps 5 --warmup 3 --no-extras > $OUT/bench_n${N}_nobind.json 2> $OUT/bench_n${N}_nobind.err; echo "bench n=$N unbound exit $?"
+    timeout 600 python bench.py --in-process-gpus $N --steps 5 --warmup 3 > $OUT/bench_inprocess_n$N.json 2> $OUT/bench_inprocess_n$N.err; echo "in-process n=$N exit $?"
+    timeout 600 python bench.py --in-process-gpus $N --workload c5r --cv 1 --steps 10 --warmup 3 > $OUT/bench_inprocess_cv_n$N.json 2> $OUT/bench_inprocess_cv_n$N.err; echo "in-process cv n=$N exit $?"
+    python - $OUT $N <<'PY'
+import json, sys
+out, N = sys.argv[1], sys.argv[2]
+for f in (f"bench_n{N}.json", f"bench_n{N}_nobind.json", f"bench_inprocess_n{N}.json", f"bench_inprocess_cv_n{N}.json"):
+    try:
+        d = json.load(open(f"{out}/{f}"))
+        e = d.get("e2e") or {}
+        print(f, f"value {d['value']:.4e} per_gpu {d['per_gpu_value']:.4e} ms/step {d['ms_per_step']:.2f} e2e {e.get('value')} e2e/value {(e.get('value') or 0) / d['value']:.3f}")
+        tc = d.get("temperature_coupled")
+        if tc: print("   tc", {k: tc[k] for k in ("value", "ms_per_step", "exchange_ms_per_step", "allreduce", "parity_ok", "T_identical_on_all_ranks")})
+    except Exception as ex:
+        print(f, "unreadable:", ex)
+PY
+    ;;
   *) echo "unknown mode $mode"; return 2 ;;
   esac
 }
