@@ -71,7 +71,7 @@ class ClockSampler:
     def __enter__(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -81,7 +81,7 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.time(), line.strip()))
 
     def __exit__(self, *exc):
         if self.proc:
@@ -91,10 +91,14 @@ class ClockSampler:
             except subprocess.TimeoutExpired:
                 self.proc.kill()
 
-    def summary(self):
+    def summary(self, t0=None, t1=None):
+        """clocks / throttle reasons of the samples that ARRIVED inside the wall-clock window [t0, t1] (the timed region plus its
+        warm-up); the sampler itself is started earlier -- nvidia-smi needs most of a second to deliver its first line, longer
+        when eight ranks start one each, and a sub-second timed region would otherwise see no sample at all"""
         sm, smax, power, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        inside = [ln for (t, ln) in self.lines if (t0 is None or t >= t0) and (t1 is None or t <= t1 + 0.15)]
+        for ln in inside:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 9:
                 continue
@@ -223,19 +227,22 @@ def device_timed(rt, sharding, p, dims, local_rank, world, rank, dist, W, K, gro
     g0, gn = sharding.group_range(G, world, rank)
     # devices=[...]: ONE process drives several GPUs through the library's multi-device handle (rt_multi_*, what the C++
     # drop-in uses with RT_CUDA_DEVICES); the time is the slowest shard's device time (CUDA events on every device)
-    s = rt.Solver(p, device=local_rank, group_begin=g0, group_count=gn, groups_per_batch=groups_per_batch, fetch_psi=False, dist=dist,
-                  devices=devices)
-    try:
-        if dist is not None:
-            dist.barrier()
-        with ClockSampler(local_rank) as clk:
+    with ClockSampler(local_rank) as clk:  # started before the solver exists, see ClockSampler.summary
+        s = rt.Solver(p, device=local_rank, group_begin=g0, group_count=gn, groups_per_batch=groups_per_batch, fetch_psi=False, dist=dist,
+                      devices=devices)
+        try:
+            if dist is not None:
+                dist.barrier()
+            t0 = time.time()
             ms = s.bench_steps(W, K)
-        tm, plan, exchange = s.timing(), s.plan(), s.exchange
-        T = s.temperature() if getattr(p, "cv", 0.0) else None
-    finally:
-        s.close()
+            t1 = time.time()
+            tm, plan, exchange = s.timing(), s.plan(), s.exchange
+            T = s.temperature() if getattr(p, "cv", 0.0) else None
+        finally:
+            s.close()
     ms_max = sharding.reduce_scalar(ms, "max", dist)
-    return {"value": M * G * N * 4 * K / (ms_max * 1e-3), "ms": ms_max, "tm": tm, "plan": plan, "clocks": clk.summary(), "gn": gn, "T": T, "exchange": exchange}
+    return {"value": M * G * N * 4 * K / (ms_max * 1e-3), "ms": ms_max, "tm": tm, "plan": plan, "clocks": clk.summary(t0, t1), "gn": gn, "T": T,
+            "exchange": exchange}
 
 
 def identical_over_ranks(a, dist, local_rank):
