@@ -203,7 +203,7 @@ def run_reference_arm(args, rt, M, G, N, bcl, bcr, workload):
     value = M * Gs * cores * Ns * 4 * args.steps / t_all
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * t_all / args.steps, "higher_is_better": True,
-            "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload, "M": M, "G": G, "N": N, "dt": args.dt, "ts_method": "BDF2",
                        "sample": sample},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},

@@ -145,6 +145,14 @@ int rt_group_ends(rt_solver *s, double *left, double *right); /* Gl each ; compu
 int rt_get_group_terms(rt_solver *s, double *B, double *dBdT, double *dEB, double *dsigEdE, double *dkapEB,
                        double *kappa_edge);
 int rt_get_psi_source(rt_solver *s, double *psi_source);   /* M*G */
+/* Correction::Print (correction.cpp:404-603): the class's text report -- energy grid, Planck integrals, opacities, edge
+ * opacities, dEB, dsigEdE, cor1..3 and the zero-sum check of dkapEB -- formatted from the device's tables with the
+ * reference's titles, column widths and number format (6 significant digits).  No reference driver calls Print; the
+ * drop-in offers it as Solver::print_correction.  text may be NULL (then only *length is set); the text is
+ * NUL-terminated, *length excludes the terminator; a buffer that is too small is an error.  The three columns the
+ * reference never fills (ukappa, ckappa, emis_spec: generate_multigroup_opacities is commented out, correction.cpp:376)
+ * print 0. */
+int rt_correction_print(rt_solver *s, char *text, size_t capacity, size_t *length);
 /* Correction::validate_correction (correction.cpp:39-63,100-122): sums3 = {sum B, sum dBdT, sum kappa*B};
  * *ok = 1 when all three identities hold to 1e-6 */
 int rt_validate(rt_solver *s, double *sums3, int *ok);
@@ -197,6 +205,7 @@ int rt_multi_group_ends(rt_multi *m, double *left, double *right);
 int rt_multi_get_group_terms(rt_multi *m, double *B, double *dBdT, double *dEB, double *dsigEdE, double *dkapEB, double *kappa_edge);
 int rt_multi_validate(rt_multi *m, double *sums3, int *ok);
 int rt_multi_get_temperature(rt_multi *m, double *T, double *sums3);
+int rt_multi_correction_print(rt_multi *m, char *text, size_t capacity, size_t *length);
 int rt_multi_bench_steps(rt_multi *m, int warmup_steps, int timed_steps, double *device_ms); /* slowest shard's device time */
 int rt_multi_get_timing(const rt_multi *m, int shard, rt_timing *t);
 int rt_multi_get_plan(const rt_multi *m, int shard, rt_plan *plan);

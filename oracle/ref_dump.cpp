@@ -7,6 +7,10 @@
 // reference's CSV writers keep only 6 significant digits.
 //
 // usage: ref_dump <file.prm> <out.bin>      (cwd must contain ../prm/ for the
+//        ref_dump <file.prm> --print        the reference's own Correction::Print() (correction.cpp:404-603) after one
+//                                            compute_correction, between two marker lines on stdout: the golden text of
+//                                            tests/golden/correction_print_*.txt (no reference driver ever calls it)
+//
 //                                            group-bounds / kappa data files,
 //                                            reference src/ParameterHandler.cpp:141,172)
 //
@@ -50,7 +54,7 @@ static void put_scalar(const char *name, double v) { put(name, &v, {1}); }
 
 int main(int argc, char **argv)
 {
-   if (argc != 3) { std::fprintf(stderr, "usage: ref_dump <file.prm> <out.bin>\n"); return 2; }
+   if (argc != 3) { std::fprintf(stderr, "usage: ref_dump <file.prm> <out.bin> | ref_dump <file.prm> --print\n"); return 2; }
    ParameterHandler ph(argv[1]);
    const int M = ph.get_M(), N = ph.get_N(), G = ph.get_G();
 
@@ -60,6 +64,15 @@ int main(int argc, char **argv)
    Eigen::VectorXd balance(G), e_ave(G), left_ends(G), right_ends(G);
 
    rt::Solver solver(ph, psi, phi, F);
+
+   if (std::strcmp(argv[2], "--print") == 0)
+   {
+      solver.correction->compute_correction(psi); // fills the edge opacities, differences and cor1..3 (correction.cpp:372-401)
+      std::cout << "@@@ Correction::Print begin" << std::endl;
+      solver.correction->Print();
+      std::cout << "@@@ Correction::Print end" << std::endl;
+      return 0;
+   }
 
    g_out = std::fopen(argv[2], "wb");
    if (!g_out) { std::perror("open out"); return 2; }

@@ -1801,3 +1801,24 @@ void rt_internal_nccl_destroy(void *comm)
    if (NcclApi *api = nccl_api()) api->CommDestroy((NcclComm)comm);
 }
 int rt_internal_nccl_hook(void *device_buf, size_t count, void *cuda_stream, void *user) { return nccl_allreduce_hook(device_buf, count, cuda_stream, user); }
+
+int rt_internal_print_tables(rt_solver *s, rt_print_tables *t)
+{
+   CK(cudaSetDevice(s->p.device));
+   const int G = s->p.G;
+   t->G = G;
+   t->T = s->p.T;
+   t->kappa_grey = s->p.kappa_grey;
+   t->e_edge = s->e_edge;
+   t->kappa = s->kappa;
+   struct { std::vector<double> *dst; const double *src; size_t n; } parts[] = {
+      {&t->B, s->d_B, (size_t)G},         {&t->dBdT, s->d_dBdT, (size_t)G},   {&t->dEB, s->d_dEB, (size_t)G},
+      {&t->dsigEdE, s->d_dsig, (size_t)G}, {&t->dkapEB, s->d_dkap, (size_t)G}, {&t->kappa_edge, s->d_kappa_edge, (size_t)G + 1},
+      {&t->cor1, s->d_cor1, (size_t)G},   {&t->cor2, s->d_cor2, (size_t)G},   {&t->cor3, s->d_cor3, (size_t)G}};
+   for (auto &p : parts)
+   {
+      p.dst->assign(p.n, 0.0);
+      if (download(s, p.dst->data(), p.src, p.n)) return 1;
+   }
+   return 0;
+}

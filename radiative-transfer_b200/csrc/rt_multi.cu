@@ -264,6 +264,13 @@ extern "C" int rt_multi_validate(rt_multi *m, double *sums3, int *ok)
    return rt_validate(m->h[0], sums3, ok);
 }
 
+// the per-group tables hold all G groups on every shard: shard 0 answers
+extern "C" int rt_multi_correction_print(rt_multi *m, char *text, size_t capacity, size_t *length)
+{
+   if (!m) return mfail("rt_multi_correction_print: null handle");
+   return rt_correction_print(m->h[0], text, capacity, length);
+}
+
 // T(c) is identical on every shard after the all-reduce: shard 0 answers
 extern "C" int rt_multi_get_temperature(rt_multi *m, double *T, double *sums3)
 {

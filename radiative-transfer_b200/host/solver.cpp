@@ -172,6 +172,8 @@ Solver::Solver(ParameterHandler &parameter_handler,
    cout << "B:";
    for (int g = 0; g < num_groups; ++g) cout << " " << B[g];
    cout << endl;
+   if (const char *pc = getenv("RT_CUDA_PRINT_CORRECTION"))
+      if (atoi(pc) != 0) print_correction();
    cout << "end solver constructor\n";
 }
 
@@ -237,6 +239,15 @@ void Solver::compute_balance()
       balance(g) = stage_buf[g];
       cout << "balance at (" << g << "): " << balance(g) << endl;
    }
+}
+
+void Solver::print_correction(std::ostream &os)
+{
+   size_t n = 0;
+   if (rt_multi_correction_print(handle, nullptr, 0, &n)) die("Solver::print_correction");
+   std::vector<char> text(n + 1);
+   if (rt_multi_correction_print(handle, text.data(), text.size(), &n)) die("Solver::print_correction");
+   os << text.data();
 }
 
 void Solver::compute_group_ends()

@@ -86,6 +86,10 @@ public:
 
    // additions (not in the reference): the handle for callers that want timing / per-step hooks
    rt_multi *c_handle() const { return handle; }
+   // Correction::Print() (correction.cpp:404-603) -- the reference's Solver keeps its Correction private and never calls
+   // Print; here the report is formatted from the device's tables.  RT_CUDA_PRINT_CORRECTION=1 prints it from the
+   // constructor, so that an unmodified driver can show it.
+   void print_correction(std::ostream &os = std::cout);
 };
 } // End namespace rt
 #endif // SOLVER

@@ -327,6 +327,17 @@ class Solver:
             self._h, *[capi.ptr(out[k]) for k in ("B", "dBdT", "dEB", "dsigEdE", "dkapEB", "kappa_edge")]))
         return out
 
+    def correction_report(self) -> str:
+        """the text of the reference's Correction::Print() (correction.cpp:404-603) from the device's tables"""
+        n = C.c_size_t()
+        capi.check(self._f("correction_print")(self._h, None, 0, C.byref(n)))
+        buf = C.create_string_buffer(n.value + 1)
+        capi.check(self._f("correction_print")(self._h, buf, n.value + 1, C.byref(n)))
+        return buf.value.decode()
+
+    def print_correction(self, file=None):
+        print(self.correction_report(), end="", file=file)
+
     def temperature(self, with_sums: bool = False):
         """extension: the material temperature T(c); with_sums also the group sums A, E, D (absorbed power, emitted
         power, emission derivative; after the all-reduce) of the most recent temperature update"""
