@@ -74,6 +74,11 @@ struct rt_solver
    MatMaps mat_maps;
    int var_step_mat_slots = 1;     // RT_CUDA_VAR_STEP_MATBUF=1|2 (fused cell-dependent step; 1 = one more resident CTA, measured +10 %)
    int var_threads = 64, var_cpt = 4; // tile shape of var_tile_kernel: RT_CUDA_VAR_THREADS=64|128 (0 = the chain-walk kernel), RT_CUDA_VAR_CPT=4|8
+   // fused cell-dependent step from warp tiles (var_warp_kernel.cu): RT_CUDA_VAR_WARP=1|0, RT_CUDA_VAR_CHAIN=2|4|8 warps per CTA tile
+   bool var_warp = false;
+   int var_chain = 4;
+   SweepMaps maps_vwarp;
+   MatMaps mat_maps_vwarp;
    double *d_edge_state[4] = {nullptr, nullptr, nullptr, nullptr};  // B_left, dEB_left, B_right, dEB_right (G each)
    // material-temperature update (extension; rt_params::cv > 0)
    bool tupdate = false, T_moved = false;
@@ -431,6 +436,7 @@ static int ensure_levels(rt_solver *s, int n)
       for (int kind = 0; kind < 3; ++kind) CK(make_tile_map(&s->maps[kind].m[k], s->E[k], rows, s->Np, s->tile_cells[kind]));
       CK(make_tile_map(&s->maps_step.m[k], s->E[k], rows, s->Np, s->step_box_cells));
       if (s->var && s->var_threads > 0) CK(make_tile_map(&s->maps_var.m[k], s->E[k], rows, s->Np, s->var_threads * s->var_cpt));
+      if (s->var && s->var_warp) CK(make_tile_map(&s->maps_vwarp.m[k], s->E[k], rows, s->Np, var_warp_subtile_cells()));
       s->levels = k + 1;
    }
    return 0;
@@ -639,6 +645,10 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
       if (!(s->var_threads > 0 && var_step_shape_supported(s->var_threads, s->var_cpt))) s->fused_var = false;
       if (const char *me = getenv("RT_CUDA_VAR_STEP_MATBUF"))
          if (atoi(me) == 1 || atoi(me) == 2) s->var_step_mat_slots = atoi(me);
+      if (const char *we = getenv("RT_CUDA_VAR_WARP")) s->var_warp = atoi(we) != 0;
+      if (const char *ce = getenv("RT_CUDA_VAR_CHAIN"))
+         if (var_warp_chain_supported(atoi(ce))) s->var_chain = atoi(ce);
+      if (!s->fused_var || p->ts_method != 3) s->var_warp = false;
       for (int k = 0; k < 4; ++k) CKD(dalloc(&s->d_edge_state[k], G));
       if (s->tupdate)
       {
@@ -699,6 +709,8 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
    if (s->var && s->var_threads > 0)
       for (int k = 0; k < 5; ++k) // a table row as pitch/2 16-byte "cells": the same 128-byte-swizzled box as a time-level tile
          CKC(make_tile_map(&s->mat_maps.m[k], s->d_vt[k], 2 * s->Gl, s->vt_pitch / 2, s->var_threads * s->var_cpt / 2));
+   if (s->var && s->var_warp)
+      for (int k = 0; k < 5; ++k) CKC(make_tile_map(&s->mat_maps_vwarp.m[k], s->d_vt[k], 2 * s->Gl, s->vt_pitch / 2, var_warp_subtile_cells() / 2));
    const size_t ntiles = (size_t)gb * M * s->max_tiles_per_row;
    CKD(dalloc(&s->d_tile_status, ntiles));
    CKC(cudaMemsetAsync(s->d_tile_status, 0, ntiles * sizeof(double2), s->st));
@@ -726,8 +738,8 @@ extern "C" int rt_get_plan(const rt_solver *s, rt_plan *plan)
    plan->sweep_grid = s->last_grid;
    plan->sweep_block = s->last_block ? s->last_block : s->threads[KIND_BE];
    plan->fused = ((s->fused || s->fused_var) && s->p.ts_method == 3) ? 1 : 0;
-   plan->step_tile_cells = s->var ? s->var_threads * s->var_cpt : s->step_tile_cells;
-   plan->step_block = s->var ? s->var_threads : s->step_threads * s->step_chain;
+   plan->step_tile_cells = s->var ? (s->var_warp ? s->var_chain * var_warp_subtile_cells() : s->var_threads * s->var_cpt) : s->step_tile_cells;
+   plan->step_block = s->var ? (s->var_warp ? 32 * s->var_chain : s->var_threads) : s->step_threads * s->step_chain;
    plan->step_chain = s->var ? 1 : s->step_chain;
    plan->bytes_per_group = (size_t)s->plan_levels * s->p.M * s->Np * sizeof(double2);
    plan->state_bytes = (size_t)s->levels * s->buf_elems * sizeof(double2);
@@ -971,7 +983,7 @@ static int run_fused_step_var(rt_solver *s)
 {
    const rt_params &p = s->p;
    const int in = s->i_ends, out = pick_free(in, -1, -1, -1);
-   const int tile = s->var_threads * s->var_cpt;
+   const int tile = s->var_warp ? s->var_chain * var_warp_subtile_cells() : s->var_threads * s->var_cpt;
    VarStepArgs va;
    StepArgs &a = va.s;
    a.x = s->E[in];
@@ -994,12 +1006,13 @@ static int run_fused_step_var(rt_solver *s)
    EventPair *ep;
    if (event_begin(s, 4, &ep)) return 1;
    int grid = 0;
-   CK(launch_var_step(corr, s->var_threads, s->var_cpt, s->var_threads == 64 ? s->var_step_mat_slots : 2, s->maps_var, s->mat_maps, va, s->num_sms, s->st, &grid));
+   if (s->var_warp) CK(launch_var_warp(corr, s->var_chain, s->maps_vwarp, s->mat_maps_vwarp, va, s->num_sms, s->st, &grid));
+   else CK(launch_var_step(corr, s->var_threads, s->var_cpt, s->var_threads == 64 ? s->var_step_mat_slots : 2, s->maps_var, s->mat_maps, va, s->num_sms, s->st, &grid));
    if (event_end(s, ep)) return 1;
    const unsigned long long total_tiles = (unsigned long long)a.n_chains * a.tiles_per_chain;
    s->ticket_base += (total_tiles + s->ticket_batch - 1) / s->ticket_batch + (unsigned long long)grid;
    s->last_grid = grid;
-   s->last_block = s->var_threads;
+   s->last_block = s->var_warp ? 32 * s->var_chain : s->var_threads;
    s->i_prev = in;
    s->i_ends = out;
    s->i_half_neg = s->i_half_pos = -1;

@@ -74,12 +74,18 @@ struct RowConst
       }
    }
 
-   // stepper constants of a cell from sigma and its (precomputed) source terms
-   __device__ __forceinline__ RowCoef cell_q(double sig, double qa, double qb) const
+   // 1/det of a cell: the one expensive part of its constants (shared by the two BE stages of a BDF2 step)
+   __device__ __forceinline__ double inv_det(double sig) const
+   {
+      const double d = fma(d1, sig, d0);
+      return rcp_normal(fma(d, d, o2));
+   }
+   __device__ __forceinline__ RowCoef cell_q(double sig, double qa, double qb) const { return cell_from_inv(sig, inv_det(sig), qa, qb); }
+   // stepper constants of a cell from sigma, 1/det and its (precomputed) source terms
+   __device__ __forceinline__ RowCoef cell_from_inv(double sig, double inv, double qa, double qb) const
    {
       RowCoef c;
       const double d = fma(d1, sig, d0);
-      const double inv = rcp_normal(fma(d, d, o2));
       c.id = d * inv;
       c.io = o * inv;
       c.alpha = c.io * k;

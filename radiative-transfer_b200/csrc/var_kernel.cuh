@@ -43,6 +43,12 @@ struct VarStepArgs
    int G0, Gl;
    double dx, tau, dt, beta; // tau = dt/2
 };
+// var_warp_kernel.cu: the fused step from warp tiles -- chain_warps consecutive sub-tiles of var_warp_subtile_cells() cells per
+// CTA tile; maps / mats must have boxes of ONE sub-tile
+bool var_warp_chain_supported(int chain_warps); // 2, 4, 8
+int var_warp_subtile_cells();
+cudaError_t launch_var_warp(bool corr, int chain_warps, const SweepMaps &maps, const MatMaps &mats, const VarStepArgs &va, int num_sms,
+                            cudaStream_t st, int *grid_out);
 bool var_step_shape_supported(int threads, int cpt); // 64 x 4, 128 x 4
 // mat_slots: shared-memory slots of material tables, 2 or (64 x 4 only) 1
 cudaError_t launch_var_step(bool corr, int threads, int cpt, int mat_slots, const SweepMaps &maps, const MatMaps &mats,
