@@ -536,6 +536,25 @@ def main():
                "numa_bind": numa,
                "what": "Solver(params) [tables H2D, Planck+correction terms, state init] + solve() of K steps with phi of every "
                        "step copied to pinned host memory; wall clock incl. allocation"}
+        # the same call delivering the OTHER per-step quantity the north_star names -- the radiation energy (1/c) sum_g phi_g(c)
+        # of every step (rt_set_step_history: summed over the groups on the device, N doubles per step) -- instead of phi of
+        # every group: what the D2H link costs in the number above
+        if dist is not None:
+            dist.barrier()
+        t0 = time.perf_counter()
+        s3 = rt.Solver(p, device=local_rank, group_begin=g0, group_count=gn, groups_per_batch=args.groups_per_batch, fetch_psi=False,
+                       dist=dist)
+        E_hist, _ = s3.set_step_history(K)
+        s3.solve()
+        tm3 = s3.timing()
+        wall3 = time.perf_counter() - t0
+        s3.close()
+        wall3_max = sharding.reduce_scalar(wall3, "max", dist)
+        e2e["energy_history"] = {"value": unknown_stages / wall3_max, "unit": UNIT, "wall_s": wall3_max,
+                                 "d2h_bytes_per_step": int(tm3.d2h_bytes // K), "h2d_bytes_per_step": int(tm3.h2d_bytes // K),
+                                 "finite": bool(np.isfinite(E_hist).all()), "range_last_step": [float(E_hist[-1].min()), float(E_hist[-1].max())],
+                                 "what": "the same Solver(params) + solve(), delivering the radiation energy density of every step "
+                                         "(this rank's groups) instead of phi of every group"}
 
     # ------------------------------------------------------------- the scaling series: C5 at THIS number of GPUs
     # BASELINE.json's multi-GPU config (2^20 x S32 x 4096 groups, groups sharded, fixed total work = strong scaling).  At

@@ -206,6 +206,8 @@ int rt_multi_get_group_terms(rt_multi *m, double *B, double *dBdT, double *dEB, 
 int rt_multi_validate(rt_multi *m, double *sums3, int *ok);
 int rt_multi_get_temperature(rt_multi *m, double *T, double *sums3);
 int rt_multi_correction_print(rt_multi *m, char *text, size_t capacity, size_t *length);
+/* energy: summed over the shards (ascending); temperature: identical on all shards, shard 0 answers */
+int rt_multi_set_step_history(rt_multi *m, double *energy, double *temperature, int capacity_steps);
 int rt_multi_bench_steps(rt_multi *m, int warmup_steps, int timed_steps, double *device_ms); /* slowest shard's device time */
 int rt_multi_get_timing(const rt_multi *m, int shard, rt_timing *t);
 int rt_multi_get_plan(const rt_multi *m, int shard, rt_plan *plan);
@@ -219,6 +221,16 @@ int rt_set_step_output(rt_solver *s, double *phi_host, int group_major);
  * exactly `timed_steps` time steps (BDF2: 4 stage sweeps each) with CUDA events on the launching stream.
  * *device_ms is the sum over batches; rt_timing afterwards covers the timed regions only. */
 int rt_bench_steps(rt_solver *s, int warmup_steps, int timed_steps, double *device_ms);
+/* Per-step history: the per-step quantities the port's acceptance names besides the scalar intensity (no counterpart in
+ * the reference, which keeps nothing per step).  After every completed time step k (0-based, counted from the initial state,
+ * k < capacity_steps):
+ *   energy[k*N + c]      = (1/c_light) * sum over the groups THIS handle owns of phi_g(c): radiation energy density in the
+ *                          reference's normalisation of phi (solver.cpp:191-204; equilibrium value a T^4)
+ *   temperature[k*N + c] = T(c) after the update of step k (needs rt_params::cv > 0)
+ * Either pointer may be NULL; both NULL switches the history off.  The rows stay on the device while the steps run (group
+ * batches add their share) and are copied into the caller's arrays when rt_run_stages / rt_solve returns. */
+int rt_set_step_history(rt_solver *s, double *energy, double *temperature, int capacity_steps);
+
 /* pinned host memory for caller-owned result buffers (cudaMallocHost / cudaFreeHost) */
 int rt_host_alloc(void **p, size_t bytes);
 int rt_host_free(void *p);

@@ -28,7 +28,7 @@ EXPORTS = (
     "rt_multi_create", "rt_multi_destroy", "rt_multi_shards", "rt_multi_solve", "rt_multi_run_stages", "rt_multi_reset",
     "rt_multi_stages_done", "rt_multi_get_psi", "rt_multi_get_ends", "rt_multi_moments", "rt_multi_balance", "rt_multi_group_ends",
     "rt_multi_get_group_terms", "rt_multi_validate", "rt_multi_get_temperature", "rt_multi_bench_steps", "rt_multi_get_timing",
-    "rt_multi_get_plan", "rt_correction_print", "rt_multi_correction_print",
+    "rt_multi_get_plan", "rt_correction_print", "rt_multi_correction_print", "rt_set_step_history", "rt_multi_set_step_history",
 )
 
 #: int fn(void *device_buf, size_t count, void *cuda_stream, void *user)  (include/rt_cuda.h: rt_allreduce_fn)
@@ -136,6 +136,8 @@ def lib():
         L.rt_multi_get_group_terms.argtypes = [vp] + [_dp] * 6
         L.rt_multi_validate.argtypes = [vp, _dp, ip]
         L.rt_multi_get_temperature.argtypes = [vp, _dp, _dp]
+        for f in (L.rt_set_step_history, L.rt_multi_set_step_history):
+            f.argtypes = [vp, _dp, _dp, C.c_int]
         for f in (L.rt_correction_print, L.rt_multi_correction_print):
             f.argtypes = [vp, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.rt_multi_bench_steps.argtypes = [vp, C.c_int, C.c_int, _dp]

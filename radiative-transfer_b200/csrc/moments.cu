@@ -229,4 +229,17 @@ void launch_diagnostics(const double2 *ends, const double *phi, const double *mu
    diagnostics_kernel<<<groups, 1024, 0, st>>>(ends, phi, mu, wt, sigma, de_ave, M, N, Np, G0, dx, T, balance, left_ends,
                                               right_ends);
 }
+__global__ void group_sum_kernel(const double *__restrict__ phi, int groups, int N, double scale, int add, double *__restrict__ E)
+{
+   const int c = blockIdx.x * blockDim.x + threadIdx.x;
+   if (c >= N) return;
+   double acc = 0.0;
+   for (int g = 0; g < groups; ++g) acc += phi[(size_t)g * N + c]; // coalesced over cells
+   E[c] = add ? E[c] + scale * acc : scale * acc;
+}
+
+void launch_group_sum(const double *phi, int groups, int N, double scale, bool add, double *E, cudaStream_t st)
+{
+   group_sum_kernel<<<(N + 127) / 128, 128, 0, st>>>(phi, groups, N, scale, add ? 1 : 0, E);
+}
 } // namespace rtk

@@ -17,4 +17,6 @@ void launch_export_ends(const double2 *neg, const double2 *pos, double *out, int
 void launch_diagnostics(const double2 *ends, const double *phi, const double *mu, const double *wt, const double *sigma,
                         const double *de_ave, int M, int N, int Np, int G0, int groups, double dx, double T,
                         double *balance, double *left_ends, double *right_ends, cudaStream_t st);
+// E[c] = (add ? E[c] : 0) + scale * sum_g phi[g][c] (ascending g, one thread per cell: deterministic) -- radiation energy of a time step
+void launch_group_sum(const double *phi, int groups, int N, double scale, bool add, double *E, cudaStream_t st);
 } // namespace rtk

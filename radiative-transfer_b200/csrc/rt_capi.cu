@@ -129,6 +129,11 @@ struct rt_solver
    long long phi_pitch = 0;   // cells per partial row (whole tiles)
    int phi_run = 1;           // rows per run = tickets per draw: the largest divisor of M/2 that is <= 8
    bool step_phi_fused = false; // the step just completed has left its partial sums in d_phi_part
+   // per-step history (rt_set_step_history): radiation energy and material temperature of every time step, kept on the
+   // device ([hist_cap][N] each) and delivered when the call that ran the steps returns
+   double *hist_E_host = nullptr, *hist_T_host = nullptr;
+   double *d_hist_E = nullptr, *d_hist_T = nullptr;
+   int hist_cap = 0, hist_lo = 0, hist_hi = 0; // rows [hist_lo, hist_hi) were written since the last delivery
    // timing
    rt_timing tm;
    std::vector<EventPair> ev_pool;
@@ -451,7 +456,7 @@ extern "C" int rt_destroy(rt_solver *s)
                      s->d_dEB, s->d_dsig, s->d_dkap, s->d_cor1, s->d_cor2, s->d_cor3, s->d_sigma, s->d_srcB, s->d_de_ave,
                      s->d_sums, s->d_psi_source, s->d_bdry, s->d_phi, s->d_phip, s->d_F,
                      s->d_balance, s->d_left, s->d_right, s->d_stage, s->d_step_phi[0], s->d_step_phi[1],
-                     s->d_coef[0], s->d_coef[1], s->d_coef[2], s->d_coef_step, s->d_coef4, s->d_phi_part};
+                     s->d_coef[0], s->d_coef[1], s->d_coef[2], s->d_coef_step, s->d_coef4, s->d_phi_part, s->d_hist_E, s->d_hist_T};
    for (double *t : tabs) if (t) cudaFree(t);
    double *vtabs[] = {s->d_rho_c, s->d_T_c, s->d_kappa_c, s->d_B_c, s->d_dBdT_c, s->d_vt[0], s->d_vt[1], s->d_vt[2], s->d_vt[3],
                       s->d_vt[4], s->d_edge_state[0], s->d_edge_state[1], s->d_edge_state[2], s->d_edge_state[3],
@@ -744,7 +749,7 @@ extern "C" int rt_get_plan(const rt_solver *s, rt_plan *plan)
    plan->bytes_per_group = (size_t)s->plan_levels * s->p.M * s->Np * sizeof(double2);
    plan->state_bytes = (size_t)s->levels * s->buf_elems * sizeof(double2);
    plan->time_levels = s->levels;
-   plan->step_kernel = (s->step_kernel == 4 || (s->step_kernel == 0 && s->step_phi_host && s->step_group_major && s->d_phi_part)) ? 4 : 1;
+   plan->step_kernel = (s->step_kernel == 4 || (s->step_kernel == 0 && ((s->step_phi_host && s->step_group_major) || s->hist_E_host) && s->d_phi_part)) ? 4 : 1;
    cudaSetDevice(s->p.device);
    cudaMemGetInfo(&plan->free_bytes, &plan->total_bytes);
    return 0;
@@ -928,7 +933,7 @@ static int run_fused_step(rt_solver *s)
    if (ensure_levels(s, 2)) return 1;
    const int in = s->i_ends, out = pick_free(in, -1, -1, -1);
    // the per-step scalar intensity rides along in the one-scan kernel: partial sums of w_m psi per run of rows
-   const bool want_phi = s->step_phi_host && s->step_group_major && s->d_phi_part;
+   const bool want_phi = ((s->step_phi_host && s->step_group_major) || s->hist_E_host) && s->d_phi_part;
    const bool v4 = s->step_kernel == 4 || (s->step_kernel == 0 && want_phi);
    const bool phi = v4 && want_phi;
    StepArgs a;
@@ -1043,6 +1048,8 @@ static int materialize_half(rt_solver *s)
 }
 
 static int step_output(rt_solver *s);
+static int step_history(rt_solver *s);
+static int deliver_history(rt_solver *s);
 static int finish_batch(rt_solver *s);
 static int ensure_result_arrays(rt_solver *s);
 
@@ -1119,6 +1126,8 @@ static int run_stages(rt_solver *s, int n)
          if (temperature_update(s)) return 1;
       if (s->step_phi_host && s->stages_done % per_step == 0)
          if (step_output(s)) return 1;
+      if ((s->hist_E_host || s->hist_T_host) && s->stages_done % per_step == 0)
+         if (step_history(s)) return 1;
    }
    return 0;
 }
@@ -1130,6 +1139,7 @@ extern "C" int rt_run_stages(rt_solver *s, int n)
    CK(cudaSetDevice(s->p.device));
    if (run_stages(s, n)) return 1;
    if (flush_events(s)) return 1;
+   if (deliver_history(s)) return 1;
    CK(cudaStreamSynchronize(s->st));
    if (s->step_phi_host) CK(cudaStreamSynchronize(s->copy_st));
    return check_temperature(s);
@@ -1156,6 +1166,7 @@ extern "C" int rt_solve(rt_solver *s)
       s->results_valid = true;
    }
    if (flush_events(s)) return 1;
+   if (deliver_history(s)) return 1;
    CK(cudaStreamSynchronize(s->st));
    if (s->step_phi_host) CK(cudaStreamSynchronize(s->copy_st));
    return check_temperature(s);
@@ -1387,6 +1398,18 @@ extern "C" int rt_validate(rt_solver *s, double *sums3, int *ok)
    return 0;
 }
 
+// the one-scan step kernel adds up w_m psi itself (RT_CUDA_STEP_PHI=0: separate moments pass over the state)
+static int ensure_phi_part(rt_solver *s)
+{
+   const char *pe = getenv("RT_CUDA_STEP_PHI");
+   if (s->fused && s->step_kernel != 1 && s->step4_ok && s->p.ts_method == 3 && !(pe && pe[0] == '0') && !s->d_phi_part)
+   {
+      const size_t np = (size_t)s->Gb * 2 * ((size_t)(s->p.M / 2) / s->phi_run) * (size_t)s->phi_pitch;
+      if (dalloc(&s->d_phi_part, np)) return 1;
+   }
+   return 0;
+}
+
 // ---------------------------------------------------------------------------------------------
 // per-step output: phi of the step just completed -> host, overlapped with the next step's sweeps
 extern "C" int rt_set_step_output(rt_solver *s, double *phi_host, int group_major)
@@ -1405,14 +1428,89 @@ extern "C" int rt_set_step_output(rt_solver *s, double *phi_host, int group_majo
          if (!s->d_step_phi[k]) { if (dalloc(&s->d_step_phi[k], n)) return 1; }
          if (!s->step_ev[k]) CK(cudaEventCreateWithFlags(&s->step_ev[k], cudaEventDisableTiming));
       }
-      // the one-scan step kernel adds up w_m psi itself (RT_CUDA_STEP_PHI=0: separate moments pass over the state)
-      const char *pe = getenv("RT_CUDA_STEP_PHI");
-      if (group_major && s->fused && s->step_kernel != 1 && s->step4_ok && s->p.ts_method == 3 && !(pe && pe[0] == '0') && !s->d_phi_part)
-      {
-         const size_t np = (size_t)s->Gb * 2 * ((size_t)(s->p.M / 2) / s->phi_run) * (size_t)s->phi_pitch;
-         if (dalloc(&s->d_phi_part, np)) return 1;
-      }
+      if (group_major && ensure_phi_part(s)) return 1;
    }
+   return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// per-step history: the two per-step quantities the north_star names besides the scalar intensity.
+//   energy[k][c]      = (1/c) sum_g phi_g(c) after time step k: radiation energy density in the reference's normalisation
+//                       of phi (sum_m w_m psi; equilibrium: a T^4), summed over the groups THIS handle owns
+//   temperature[k][c] = T(c) after the update of time step k (cv > 0 only)
+// Both stay on the device while the steps run (group batches add their groups' share to the same row) and are copied to
+// the caller's arrays when rt_run_stages / rt_solve returns: no per-step synchronisation, steps * N * 8 bytes in all.
+extern "C" int rt_set_step_history(rt_solver *s, double *energy, double *temperature, int capacity_steps)
+{
+   if (!s) return fail("rt_set_step_history: null handle");
+   CK(cudaSetDevice(s->p.device));
+   if ((energy || temperature) && capacity_steps < 1) return fail("rt_set_step_history: capacity_steps = %d", capacity_steps);
+   if (temperature && !s->tupdate) return fail("rt_set_step_history: a temperature history needs the temperature update (rt_params::cv > 0)");
+   const size_t n = (size_t)std::max(capacity_steps, 0) * s->p.N;
+   if (n * sizeof(double) > ((size_t)4 << 30))
+      return fail("rt_set_step_history: %d steps x %d cells is more than 4 GiB per array; run the steps in several calls", capacity_steps, s->p.N);
+   if (s->d_hist_E) { CK(cudaFree(s->d_hist_E)); s->d_hist_E = nullptr; }
+   if (s->d_hist_T) { CK(cudaFree(s->d_hist_T)); s->d_hist_T = nullptr; }
+   s->hist_E_host = energy;
+   s->hist_T_host = temperature;
+   s->hist_cap = (energy || temperature) ? capacity_steps : 0;
+   s->hist_lo = s->hist_hi = 0;
+   if (energy)
+   {
+      if (dalloc(&s->d_hist_E, n)) return 1;
+      if (!s->d_step_phi[0]) { if (dalloc(&s->d_step_phi[0], (size_t)s->Gb * s->p.N)) return 1; }
+      if (ensure_phi_part(s)) return 1;
+   }
+   if (temperature) { if (dalloc(&s->d_hist_T, n)) return 1; }
+   return 0;
+}
+
+// after a completed time step: this batch's share of the step's radiation energy, and T(c)
+static int step_history(rt_solver *s)
+{
+   const rt_params &p = s->p;
+   const int per_step = p.ts_method == 3 ? 4 : 1;
+   const int k = s->stages_done / per_step - 1; // time step just completed, counted from the initial state
+   if (k < 0 || k >= s->hist_cap) { s->step_phi_fused = false; return 0; } // beyond the caller's capacity: not recorded
+   if (s->hist_E_host)
+   {
+      // phi of the step: left in a staging buffer by step_output a moment ago, or formed here
+      const double *phi = nullptr;
+      if (s->step_phi_host && s->step_group_major) phi = s->d_step_phi[s->step_parity ^ 1];
+      else
+      {
+         EventPair *ep;
+         if (event_begin(s, 3, &ep)) return 1;
+         if (s->step_phi_fused)
+            launch_phi_combine(s->d_phi_part, s->phi_pitch, (p.M / 2) / s->phi_run, p.N, s->batch_groups, s->d_step_phi[0], s->st);
+         else
+            launch_moments(s->E[s->i_ends], s->d_mu, s->d_wt, p.M, p.N, s->Np, s->batch_groups, s->d_step_phi[0], nullptr, nullptr, s->st);
+         s->step_phi_fused = false;
+         if (event_end(s, ep)) return 1;
+         s->tm.kernel_launches++;
+         phi = s->d_step_phi[0];
+      }
+      EventPair *ep;
+      if (event_begin(s, 3, &ep)) return 1;
+      // the first batch of groups starts the row, the others add to it (ascending batches: deterministic)
+      launch_group_sum(phi, s->batch_groups, p.N, 1.0 / C_LIGHT, s->batch_start > 0, s->d_hist_E + (size_t)k * p.N, s->st);
+      if (event_end(s, ep)) return 1;
+      s->tm.kernel_launches++;
+   }
+   if (s->hist_T_host)
+      CK(cudaMemcpyAsync(s->d_hist_T + (size_t)k * p.N, s->d_T_c, (size_t)p.N * sizeof(double), cudaMemcpyDeviceToDevice, s->st));
+   if (s->hist_hi <= s->hist_lo) { s->hist_lo = k; s->hist_hi = k + 1; }
+   else { s->hist_lo = std::min(s->hist_lo, k); s->hist_hi = std::max(s->hist_hi, k + 1); }
+   return 0;
+}
+
+static int deliver_history(rt_solver *s)
+{
+   if (s->hist_hi <= s->hist_lo) return 0;
+   const size_t off = (size_t)s->hist_lo * s->p.N, n = (size_t)(s->hist_hi - s->hist_lo) * s->p.N;
+   if (s->hist_E_host && download(s, s->hist_E_host + off, s->d_hist_E + off, n)) return 1;
+   if (s->hist_T_host && download(s, s->hist_T_host + off, s->d_hist_T + off, n)) return 1;
+   s->hist_lo = s->hist_hi = 0;
    return 0;
 }
 

@@ -26,7 +26,25 @@ struct rt_multi
    std::vector<int> device, g0, gn;
    std::vector<void *> comm;    // NCCL communicators (temperature update on more than one shard), else empty
    int G_owned = 0;             // groups this multi handle owns (p.group_count)
+   // per-step history (rt_multi_set_step_history) on more than one shard: every shard fills its own rows, the caller's
+   // energy array is their sum
+   double *hist_E = nullptr;
+   int hist_cap = 0;
+   std::vector<std::vector<double>> hist_part;
 };
+
+// the caller's energy rows = the shards' shares added in ascending shard order
+static void combine_history(rt_multi *m)
+{
+   if (!m->hist_E || m->hist_part.empty()) return;
+   const size_t n = (size_t)m->hist_cap * m->p.N;
+   for (size_t i = 0; i < n; ++i)
+   {
+      double acc = 0.0;
+      for (const auto &part : m->hist_part) acc += part[i];
+      m->hist_E[i] = acc;
+   }
+}
 
 static int mfail(const std::string &m) { return rt_internal_fail(m.c_str()); }
 
@@ -145,13 +163,37 @@ extern "C" int rt_multi_shards(const rt_multi *m, int *n, int *group_begin, int 
 extern "C" int rt_multi_solve(rt_multi *m)
 {
    if (!m) return mfail("rt_multi_solve: null handle");
-   return for_each_shard(m, [&](int k) { return rt_solve(m->h[k]); });
+   if (for_each_shard(m, [&](int k) { return rt_solve(m->h[k]); })) return 1;
+   combine_history(m);
+   return 0;
 }
 
 extern "C" int rt_multi_run_stages(rt_multi *m, int n)
 {
    if (!m) return mfail("rt_multi_run_stages: null handle");
-   return for_each_shard(m, [&](int k) { return rt_run_stages(m->h[k], n); });
+   if (for_each_shard(m, [&](int k) { return rt_run_stages(m->h[k], n); })) return 1;
+   combine_history(m);
+   return 0;
+}
+
+extern "C" int rt_multi_set_step_history(rt_multi *m, double *energy, double *temperature, int capacity_steps)
+{
+   if (!m) return mfail("rt_multi_set_step_history: null handle");
+   const int ns = (int)m->h.size();
+   m->hist_E = nullptr;
+   m->hist_cap = 0;
+   m->hist_part.clear();
+   if (ns == 1) return rt_set_step_history(m->h[0], energy, temperature, capacity_steps);
+   if (energy)
+   {
+      if (capacity_steps < 1) return mfail("rt_multi_set_step_history: capacity_steps < 1");
+      m->hist_E = energy;
+      m->hist_cap = capacity_steps;
+      m->hist_part.assign(ns, std::vector<double>((size_t)capacity_steps * m->p.N, 0.0));
+   }
+   return for_each_shard(m, [&](int k) {
+      return rt_set_step_history(m->h[k], energy ? m->hist_part[k].data() : nullptr, k == 0 ? temperature : nullptr, capacity_steps);
+   });
 }
 
 extern "C" int rt_multi_reset(rt_multi *m)

@@ -327,6 +327,17 @@ class Solver:
             self._h, *[capi.ptr(out[k]) for k in ("B", "dBdT", "dEB", "dsigEdE", "dkapEB", "kappa_edge")]))
         return out
 
+    def set_step_history(self, capacity_steps: int, temperature: bool = False):
+        """record, for every time step k < capacity_steps, the radiation energy density (1/c) sum_g phi_g(c) -- summed over
+        the groups this solver owns: under torchrun each rank holds its share -- and, with cv > 0, the material temperature;
+        the arrays ([capacity_steps, N], returned and kept as step_energy / step_temperature) are filled when solve() /
+        run_stages() returns"""
+        self.step_energy = np.zeros((capacity_steps, self.N))
+        self.step_temperature = np.zeros((capacity_steps, self.N)) if temperature else None
+        capi.check(self._f("set_step_history")(self._h, capi.ptr(self.step_energy),
+                                                capi.ptr(self.step_temperature) if temperature else None, capacity_steps))
+        return self.step_energy, self.step_temperature
+
     def correction_report(self) -> str:
         """the text of the reference's Correction::Print() (correction.cpp:404-603) from the device's tables"""
         n = C.c_size_t()
