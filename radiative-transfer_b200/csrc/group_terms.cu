@@ -358,6 +358,55 @@ int launch_planck_shard_begin(int G, int ncell, int g0, int ng, const double *d_
    return n > 0 ? 2 : 1;
 }
 
+// ---- a group RANGE without any exchange (a handle that owns part of the groups and stores only those, rt_capi.cu): the
+// owner of the last group takes the grey remainder by the reference's sequential subtraction over ALL groups (Planck.cpp:
+// 58-76), integrating the groups it does not own on the fly instead of reading them from a table -- same function of
+// (T, edges), same order, so the result is bit for bit the one of the whole-table evaluation (planck_finalize_kernel).
+// B / dBdT are BASE pointers: entry (g, c) at B[g * ncell + c] with the GLOBAL g, rows outside [g0, g0+ng) do not exist.
+__global__ void planck_range_finalize_kernel(int G, int ncell, int g0, int ng, const double *__restrict__ e_edge,
+                                             const double *__restrict__ T, double *__restrict__ B, double *__restrict__ dBdT)
+{
+   const int c = blockIdx.x * blockDim.x + threadIdx.x;
+   if (c >= ncell) return;
+   const double t = T[c];
+   const bool owns_last = g0 + ng == G;
+   if (owns_last)
+   {
+      double bsum = rad_a_long() * C_LIGHT * (t * t) * (t * t);
+      double dsum = 4.0 * rad_a_long() * C_LIGHT * (t * t) * t;
+      for (int g = 0; g < G - 1; ++g)
+      {
+         double b, d;
+         if (g >= g0) { b = B[(size_t)g * ncell + c]; d = dBdT[(size_t)g * ncell + c]; }
+         else planck_group_pair<true>(t, e_edge[g], e_edge[g + 1], b, d);
+         bsum -= b;
+         dsum -= d;
+      }
+      const size_t o = (size_t)(G - 1) * ncell + c;
+      B[o] = K_JPK * (bsum > 0.0 ? bsum : B[o]);
+      dBdT[o] = K_JPK * (dsum > 0.0 ? dsum : dBdT[o]);
+   }
+   const int hi = owns_last ? G - 1 : g0 + ng;
+   for (int g = g0; g < hi; ++g)
+   {
+      B[(size_t)g * ncell + c] *= K_JPK;
+      dBdT[(size_t)g * ncell + c] *= K_JPK;
+   }
+}
+
+int launch_planck_range(int G, int ncell, int g0, int ng, const double *d_e_edge, const double *d_T, double *d_B_base, double *d_dBdT_base,
+                        cudaStream_t st)
+{
+   const int n = min(g0 + ng, G - 1) - g0; // owned groups other than the last one
+   if (n > 0)
+   {
+      const long long total = (long long)ncell * n;
+      planck_integrals_kernel<true><<<(unsigned)((total + 127) / 128), 128, 0, st>>>(G, ncell, g0, n, d_e_edge, d_T, d_B_base, d_dBdT_base);
+   }
+   planck_range_finalize_kernel<<<(ncell + 127) / 128, 128, 0, st>>>(G, ncell, g0, ng, d_e_edge, d_T, d_B_base, d_dBdT_base);
+   return n > 0 ? 2 : 1;
+}
+
 int launch_planck_shard_finish(int G, int ncell, const double *d_T, const double *d_part, double *d_B, double *d_dBdT, cudaStream_t st)
 {
    planck_last_kernel<<<(ncell + 127) / 128, 128, 0, st>>>(G, ncell, d_T, d_part, d_B, d_dBdT);

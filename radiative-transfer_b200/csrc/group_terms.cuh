@@ -27,6 +27,11 @@ int launch_planck(int G, int ncell, const double *d_e_edge, const double *d_T, d
 // takes the grey remainder with launch_planck_shard_finish.  Same tables ([G][ncell]), only owned rows are touched.
 int launch_planck_shard_begin(int G, int ncell, int g0, int ng, const double *d_e_edge, const double *d_T, double *d_B,
                               double *d_dBdT, double *d_part, cudaStream_t st);
+// the owned groups [g0, g0+ng) WITHOUT exchange: integrals of the owned groups and, for the owner of group G-1, the grey
+// remainder by sequential subtraction over all groups (the others integrated on the fly) -- bit for bit launch_planck's rows.
+// d_B_base / d_dBdT_base: BASE pointers of tables that hold only rows [g0, g0+ng) (entry (g, c) at base[g*ncell + c]).
+int launch_planck_range(int G, int ncell, int g0, int ng, const double *d_e_edge, const double *d_T, double *d_B_base, double *d_dBdT_base,
+                        cudaStream_t st);
 int launch_planck_shard_finish(int G, int ncell, const double *d_T, const double *d_part, double *d_B, double *d_dBdT, cudaStream_t st);
 int launch_group_terms(const GroupTermsArgs &a, cudaStream_t st);
 // correction.cpp:66-97; B in jk units (after launch_planck); all arrays G long

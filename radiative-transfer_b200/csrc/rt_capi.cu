@@ -66,7 +66,17 @@ struct rt_solver
    double sums[3] = {0, 0, 0};
    // cell-dependent material fields (extension, var_kernel.cu): inputs, Planck per cell, per-cell tables [gl][c]
    bool var = false;
-   std::vector<double> rho_cell, T_cell, kappa_cell;
+   std::vector<double> rho_cell, T_cell, kappa_cell; // kappa_cell: GROUP-MAJOR rows [tab_g0, tab_g0 + tab_n) only
+   // Per-cell tables are sharded with the groups: kappa of the owned groups and one neighbour on either side (the edge
+   // opacities interpolate between group centres, correction.cpp:125-139), B and dB/dT of the owned groups only.  The
+   // kernels index them with the GLOBAL group number through base pointers (kap_base() etc.).  The equilibrium boundary
+   // sources need ALL groups, but only at the two boundary cells: compact [G][2] copies (bd_*).
+   int tab_g0 = 0, tab_n = 0;
+   std::vector<double> bd_kappa;                                   // [G][2]: kappa_g at cell 0 / cell N-1
+   double *d_bd_T = nullptr, *d_bd_rho = nullptr, *d_bd_kappa = nullptr, *d_bd_B = nullptr, *d_bd_dB = nullptr;
+   double *kap_base() const { return d_kappa_c - (ptrdiff_t)tab_g0 * p.N; }
+   double *B_base() const { return d_B_c - (ptrdiff_t)p.group_begin * p.N; }
+   double *dB_base() const { return d_dBdT_c - (ptrdiff_t)p.group_begin * p.N; }
    double *d_rho_c = nullptr, *d_T_c = nullptr, *d_kappa_c = nullptr, *d_B_c = nullptr, *d_dBdT_c = nullptr;
    double *d_vt[5] = {nullptr, nullptr, nullptr, nullptr, nullptr}; // sigma, srcB, cor1, cor2, cor3: [sign][gl][vt_pitch] (var_kernel.cuh)
    int vt_pitch = 0;               // N rounded up to 16
@@ -315,26 +325,30 @@ static int compute_var_tables(rt_solver *s, bool with_boundary, bool sharded = f
    {
       // a group shard inside a temperature-coupled solve: integrate the owned groups only; the last group's grey
       // remainder needs the sum over all groups -> second (2N) all-reduce of the step
-      s->tm.kernel_launches += launch_planck_shard_begin(p.G, p.N, p.group_begin, s->Gl, s->d_e_edge, s->d_T_c, s->d_B_c, s->d_dBdT_c,
+      s->tm.kernel_launches += launch_planck_shard_begin(p.G, p.N, p.group_begin, s->Gl, s->d_e_edge, s->d_T_c, s->B_base(), s->dB_base(),
                                                          s->d_ppart, s->st);
       CK(cudaGetLastError());
       const int rc = s->allreduce(s->d_ppart, (size_t)2 * p.N, (void *)s->st, s->allreduce_user);
       if (rc) return fail("rt: the all-reduce hook failed with code %d in the Planck remainder after stage %d", rc, s->stages_done);
       if (p.group_begin + s->Gl == p.G)
-         s->tm.kernel_launches += launch_planck_shard_finish(p.G, p.N, s->d_T_c, s->d_ppart, s->d_B_c, s->d_dBdT_c, s->st);
+         s->tm.kernel_launches += launch_planck_shard_finish(p.G, p.N, s->d_T_c, s->d_ppart, s->B_base(), s->dB_base(), s->st);
    }
    else
    {
    // the last group keeps "the previous value" when the grey remainder is not positive (Planck.cpp:73-76); the oracle
    // starts every evaluation from zeroed vectors
-   CK(cudaMemsetAsync(s->d_B_c + (size_t)(p.G - 1) * p.N, 0, (size_t)p.N * sizeof(double), s->st));
-   CK(cudaMemsetAsync(s->d_dBdT_c + (size_t)(p.G - 1) * p.N, 0, (size_t)p.N * sizeof(double), s->st));
-   s->tm.kernel_launches += launch_planck(p.G, p.N, s->d_e_edge, s->d_T_c, s->d_B_c, s->d_dBdT_c, s->st);
+   if (p.group_begin + s->Gl == p.G)
+   {
+      CK(cudaMemsetAsync(s->B_base() + (size_t)(p.G - 1) * p.N, 0, (size_t)p.N * sizeof(double), s->st));
+      CK(cudaMemsetAsync(s->dB_base() + (size_t)(p.G - 1) * p.N, 0, (size_t)p.N * sizeof(double), s->st));
+   }
+   // the owned groups only; the owner of the last group integrates the others on the fly for the remainder (no table of them)
+   s->tm.kernel_launches += launch_planck_range(p.G, p.N, p.group_begin, s->Gl, s->d_e_edge, s->d_T_c, s->B_base(), s->dB_base(), s->st);
    }
    CellTermsArgs ca;
    ca.G = p.G; ca.N = p.N; ca.G0 = p.group_begin; ca.groups = s->Gl;
-   ca.e_edge = s->d_e_edge; ca.kappa_cell = s->d_kappa_c; ca.rho_cell = s->d_rho_c; ca.T_cell = s->d_T_c; ca.B_cell = s->d_B_c;
-   ca.dBdT_cell = s->d_dBdT_c;
+   ca.e_edge = s->d_e_edge; ca.kappa_cell = s->kap_base(); ca.rho_cell = s->d_rho_c; ca.T_cell = s->d_T_c; ca.B_cell = s->B_base();
+   ca.dBdT_cell = s->dB_base();
    ca.sigma = s->d_vt[0]; ca.srcB = s->d_vt[1]; ca.cor1 = s->d_vt[2]; ca.cor2 = s->d_vt[3]; ca.cor3 = s->d_vt[4];
    ca.pitch = s->vt_pitch;
    ca.sdB = s->d_sdB;
@@ -343,7 +357,14 @@ static int compute_var_tables(rt_solver *s, bool with_boundary, bool sharded = f
    s->tm.kernel_launches += 1;
    if (with_boundary)
    {
-      launch_boundary_state(ca, s->st);
+      // all G groups at the two boundary cells: Planck integrals at their two temperatures, then the same per-cell pipeline
+      // on the compact [G][2] tables (column 0 = cell 0, column 1 = cell N-1)
+      CK(cudaMemsetAsync(s->d_bd_B + (size_t)(p.G - 1) * 2, 0, 2 * sizeof(double), s->st));
+      CK(cudaMemsetAsync(s->d_bd_dB + (size_t)(p.G - 1) * 2, 0, 2 * sizeof(double), s->st));
+      s->tm.kernel_launches += launch_planck_range(p.G, 2, 0, p.G, s->d_e_edge, s->d_bd_T, s->d_bd_B, s->d_bd_dB, s->st);
+      CellTermsArgs cb = ca;
+      cb.N = 2; cb.kappa_cell = s->d_bd_kappa; cb.rho_cell = s->d_bd_rho; cb.T_cell = s->d_bd_T; cb.B_cell = s->d_bd_B; cb.dBdT_cell = s->d_bd_dB;
+      launch_boundary_state(cb, s->st);
       s->tm.kernel_launches += 1;
       if (upload(s, s->d_psi_source, s->psi_source.data(), (size_t)p.M * p.G)) return 1; // the caller's sources, before the BC switch
       launch_boundary_table_var(p.M, p.G, p.bc_left, p.bc_right, p.use_mg_equilib, p.V, s->d_mu, s->d_edge_state[0], s->d_edge_state[1],
@@ -420,7 +441,7 @@ static int load_batch(rt_solver *s, int start)
       s->tsteps_done = 0;
       CK(cudaMemsetAsync(s->d_T_bad, 0, sizeof(int), s->st));
    }
-   if (s->var) launch_init_state_var(s->E[0], s->d_B_c, s->p.M, s->p.N, s->Np, s->p.G, s->p.group_begin + start, s->batch_groups, s->st);
+   if (s->var) launch_init_state_var(s->E[0], s->B_base(), s->p.M, s->p.N, s->Np, s->p.G, s->p.group_begin + start, s->batch_groups, s->st);
    else launch_init_state(s->E[0], s->d_B, s->p.M, s->p.N, s->Np, s->p.group_begin + start, s->batch_groups, s->st);
    s->tm.kernel_launches += 1;
    CK(cudaGetLastError());
@@ -460,7 +481,7 @@ extern "C" int rt_destroy(rt_solver *s)
    for (double *t : tabs) if (t) cudaFree(t);
    double *vtabs[] = {s->d_rho_c, s->d_T_c, s->d_kappa_c, s->d_B_c, s->d_dBdT_c, s->d_vt[0], s->d_vt[1], s->d_vt[2], s->d_vt[3],
                       s->d_vt[4], s->d_edge_state[0], s->d_edge_state[1], s->d_edge_state[2], s->d_edge_state[3],
-                      s->d_sdB, s->d_T_prev, s->d_xsums, s->d_xpart, s->d_ppart};
+                      s->d_sdB, s->d_T_prev, s->d_xsums, s->d_xpart, s->d_ppart, s->d_bd_T, s->d_bd_rho, s->d_bd_kappa, s->d_bd_B, s->d_bd_dB};
    for (double *t : vtabs) if (t) cudaFree(t);
    for (int k = 0; k < 4; ++k) if (s->E[k]) cudaFreeAsync(s->E[k], s->st);
    if (s->st) cudaStreamSynchronize(s->st);
@@ -534,12 +555,17 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
    {
       s->rho_cell.assign(N, p->rho);
       s->T_cell.assign(N, p->T);
-      s->kappa_cell.resize((size_t)G * N);
+      s->tab_g0 = std::max(0, p->group_begin - 1);
+      s->tab_n = std::min(G, p->group_begin + p->group_count + 1) - s->tab_g0;
+      s->kappa_cell.resize((size_t)s->tab_n * N);
+      s->bd_kappa.resize((size_t)G * 2);
       if (p->rho_cell) std::copy(p->rho_cell, p->rho_cell + N, s->rho_cell.begin());
       if (p->T_cell) std::copy(p->T_cell, p->T_cell + N, s->T_cell.begin());
+      auto kap = [&](int g, int c) { return p->kappa_cell ? p->kappa_cell[(size_t)g + (size_t)G * c] : p->kappa[g]; };
       for (int c = 0; c < N; ++c)
-         for (int g = 0; g < G; ++g)
-            s->kappa_cell[(size_t)g * N + c] = p->kappa_cell ? p->kappa_cell[(size_t)g + (size_t)G * c] : p->kappa[g]; // group-major on the device
+         for (int t = 0; t < s->tab_n; ++t)
+            s->kappa_cell[(size_t)t * N + c] = kap(s->tab_g0 + t, c); // group-major on the device
+      for (int g = 0; g < G; ++g) { s->bd_kappa[2 * (size_t)g] = kap(g, 0); s->bd_kappa[2 * (size_t)g + 1] = kap(g, N - 1); }
       s->p.rho_cell = s->rho_cell.data(); s->p.T_cell = s->T_cell.data(); s->p.kappa_cell = nullptr; // (the copy is transposed)
    }
    s->num_sms = prop.multiProcessorCount;
@@ -631,8 +657,10 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
    }
    if (s->var)
    {
-      CKD(dalloc(&s->d_rho_c, N)); CKD(dalloc(&s->d_T_c, N)); CKD(dalloc(&s->d_kappa_c, (size_t)G * N));
-      CKD(dalloc(&s->d_B_c, (size_t)G * N)); CKD(dalloc(&s->d_dBdT_c, (size_t)G * N));
+      CKD(dalloc(&s->d_rho_c, N)); CKD(dalloc(&s->d_T_c, N)); CKD(dalloc(&s->d_kappa_c, (size_t)s->tab_n * N));
+      CKD(dalloc(&s->d_B_c, (size_t)s->Gl * N)); CKD(dalloc(&s->d_dBdT_c, (size_t)s->Gl * N));
+      CKD(dalloc(&s->d_bd_T, 2)); CKD(dalloc(&s->d_bd_rho, 2)); CKD(dalloc(&s->d_bd_kappa, (size_t)G * 2));
+      CKD(dalloc(&s->d_bd_B, (size_t)G * 2)); CKD(dalloc(&s->d_bd_dB, (size_t)G * 2));
       s->vt_pitch = (N + 15) & ~15;
       for (int k = 0; k < 5; ++k)
       {
@@ -663,10 +691,14 @@ extern "C" int rt_create(const rt_params *p, rt_solver **out)
          CKC(cudaMemsetAsync(s->d_T_bad, 0, sizeof(int), s->st));
          for (int m = 0; m < M; ++m) s->wsum += s->wt[m];
       }
-      CKC(cudaMemsetAsync(s->d_B_c, 0, (size_t)G * N * sizeof(double), s->st));
-      CKC(cudaMemsetAsync(s->d_dBdT_c, 0, (size_t)G * N * sizeof(double), s->st));
+      CKC(cudaMemsetAsync(s->d_B_c, 0, (size_t)s->Gl * N * sizeof(double), s->st));
+      CKC(cudaMemsetAsync(s->d_dBdT_c, 0, (size_t)s->Gl * N * sizeof(double), s->st));
       CKD(upload(s, s->d_rho_c, s->rho_cell.data(), N)); CKD(upload(s, s->d_T_c, s->T_cell.data(), N));
-      CKD(upload(s, s->d_kappa_c, s->kappa_cell.data(), (size_t)G * N));
+      CKD(upload(s, s->d_kappa_c, s->kappa_cell.data(), (size_t)s->tab_n * N));
+      std::vector<double>().swap(s->kappa_cell); // the device copy is the only one a run needs
+      const double bT[2] = {s->T_cell[0], s->T_cell[N - 1]}, brho[2] = {s->rho_cell[0], s->rho_cell[N - 1]};
+      CKD(upload(s, s->d_bd_T, bT, 2)); CKD(upload(s, s->d_bd_rho, brho, 2));
+      CKD(upload(s, s->d_bd_kappa, s->bd_kappa.data(), (size_t)G * 2));
    }
 
    // ---- memory plan: time-level buffers of (u,v) per unknown + look-back state + result / per-step output arrays.

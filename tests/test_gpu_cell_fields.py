@@ -103,6 +103,29 @@ def test_only_temperature_given_and_group_shards(rt, oracle):
         assert np.array_equal(s.ends(0), whole[:, 2:5])
 
 
+def test_per_cell_tables_are_sharded_with_the_groups(rt):
+    """a handle that owns groups [g0, g0+n) keeps kappa_g(c) of those groups and ONE neighbour on either side (edge opacities
+    interpolate between group centres, correction.cpp:125-139) plus all groups at the two boundary cells (equilibrium
+    boundary sources) -- nothing else of the G x N input is read: poison it and the shard's result does not change;
+    the owner of the last group still gets the grey remainder over ALL groups (integrated on the fly, not tabulated)"""
+    p = synthetic_parameters(rt, M=4, G=12, N=700, dt=1e-3, V=1.0, steps=2, bc_left=2, bc_right=1)
+    _fields(p)
+    with rt.Solver(p) as s:
+        s.solve()
+        whole = s.ends(0)
+    clean = p.kappa_cell.copy()
+    for g0, n in ((4, 3), (0, 2), (9, 3)):
+        p.kappa_cell = clean.copy()
+        outside = [g for g in range(p.G) if g < g0 - 1 or g > g0 + n]
+        p.kappa_cell[outside, 1:-1] = np.nan
+        with rt.Solver(p, group_begin=g0, group_count=n) as s:
+            s.solve()
+            got = s.ends(0)
+            assert np.isfinite(got).all()
+            assert np.array_equal(got, whole[:, g0:g0 + n]), (g0, n)
+    p.kappa_cell = clean
+
+
 def test_validation_is_refused_with_cell_fields(rt):
     p = synthetic_parameters(rt, M=4, G=3, N=100, dt=1e-3, V=1.0, steps=1)
     p.include_validation = True
