@@ -84,7 +84,33 @@ SYNTH = [
     ("c5like_longrange_source",     32, 4,  6151,  1e-3, 1.0, 2,    1,   1),
     ("very_long_range_vacuum",      4,  3,  20000, 5e-2, 0.5, 1,    0,   0),
     ("v0_reflect_multitile",        8,  5,  2049,  1e-4, 0.0, 2,    2,   1),
+    ("mixed_local_and_long_range",  16, 24, 5000,  1e-4, 1.0, 2,    2,   1),
 ]
+
+
+def _local_rows(rt, p):
+    """rows the fused step kernel treats as LOCAL (step_warp_kernel.cu SC_LOCAL: alpha^16 < 2^-70 for all three stage kinds,
+    so its warp scan runs one step instead of five) -- the stepper constants of SURVEY 8(a) S1-S3 / S*"""
+    from parity_util import host_setup
+    c = 299.792458
+    mu, _, _, kap = host_setup(rt, p)
+    sig, amu, tau, dx = p.rho * np.asarray(kap)[None, :], np.abs(np.asarray(mu))[:, None], p.dt / 2, p.dx
+    worst = 0.0
+    for k, d in ((c * tau * amu, 0.5 * ((1 + c * tau * sig) * dx + c * tau * amu)),
+                 (0.5 * c * amu * tau, 0.5 * ((1 + 0.5 * c * tau * sig) * dx + 0.5 * c * amu * tau)),
+                 (c * amu * p.dt / 6, 0.5 * ((1 + c * sig * tau / 6) * dx + c * amu * p.dt / 6))):
+        worst = np.maximum(worst, 0.5 * k * k / (d * d + 0.25 * k * k))
+    return worst ** 16 < 2.0 ** -70
+
+
+def test_the_mixed_case_has_rows_of_both_kinds(rt):
+    """mixed_local_and_long_range above puts local and long-range rows into the SAME launch (and the same CTA: tickets run
+    over the rows of a tile position), c4like_local_reflect is all local, very_long_range_vacuum has none"""
+    frac = {}
+    for name, M, G, N, dt, V, steps, bcl, bcr in SYNTH:
+        frac[name] = float(np.mean(_local_rows(rt, synthetic_parameters(rt, M=M, G=G, N=N, dt=dt, V=V, steps=steps, bc_left=bcl, bc_right=bcr))))
+    assert 0.05 < frac["mixed_local_and_long_range"] < 0.95, frac
+    assert frac["c4like_local_reflect"] == 1.0 and frac["very_long_range_vacuum"] == 0.0, frac
 
 
 @pytest.mark.parametrize("name,M,G,N,dt,V,steps,bcl,bcr", SYNTH)
