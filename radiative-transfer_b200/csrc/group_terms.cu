@@ -374,20 +374,27 @@ __global__ void planck_range_finalize_kernel(int G, int ncell, int g0, int ng, c
    {
       double bsum = rad_a_long() * C_LIGHT * (t * t) * (t * t);
       double dsum = 4.0 * rad_a_long() * C_LIGHT * (t * t) * t;
-      for (int g = 0; g < G - 1; ++g)
+      for (int g = 0; g < g0; ++g) // groups this handle does not own: integrated, not stored
       {
          double b, d;
-         if (g >= g0) { b = B[(size_t)g * ncell + c]; d = dBdT[(size_t)g * ncell + c]; }
-         else planck_group_pair<true>(t, e_edge[g], e_edge[g + 1], b, d);
+         planck_group_pair<true>(t, e_edge[g], e_edge[g + 1], b, d);
          bsum -= b;
          dsum -= d;
+      }
+      for (int g = g0; g < G - 1; ++g) // owned groups: one pass, like planck_finalize_kernel
+      {
+         const size_t o = (size_t)g * ncell + c;
+         bsum -= B[o];
+         dsum -= dBdT[o];
+         B[o] *= K_JPK;
+         dBdT[o] *= K_JPK;
       }
       const size_t o = (size_t)(G - 1) * ncell + c;
       B[o] = K_JPK * (bsum > 0.0 ? bsum : B[o]);
       dBdT[o] = K_JPK * (dsum > 0.0 ? dsum : dBdT[o]);
+      return;
    }
-   const int hi = owns_last ? G - 1 : g0 + ng;
-   for (int g = g0; g < hi; ++g)
+   for (int g = g0; g < g0 + ng; ++g)
    {
       B[(size_t)g * ncell + c] *= K_JPK;
       dBdT[(size_t)g * ncell + c] *= K_JPK;
