@@ -526,8 +526,12 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
             }
             if (valid != WT) publish_ragged(std::integral_constant<int, 1>{}, vv);
          }
-         // ================= stage 2: BE predictor, x1 = stage-1 result; only u+v survives (the BDF stage's source)
+         // ================= stage 2: BE predictor, x1 = stage-1 result; only u+v survives (the BDF stage's source).
+         // Without the correction source (V = 0 or use_correction off: the reference's defaults) nothing reads it: the BDF
+         // stage takes half_ends and prev_ends, and `ends` between the stages of a step is not observable from a fused
+         // step -- the whole stage, its scan and its look-back chain are left out (3 scans per sub-tile instead of 4).
          double xs[CPT];
+         if (CORR)
          {
             const double *c = cf + SC_BE, *pw = cf + SC_BE_POW;
             const double alpha = pw[0], gamma = c[0];
