@@ -299,7 +299,9 @@ var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
             v = vn;
          }
       }
-      // ================= stage 2: BE predictor, x1 = S1 -> S2 (only u+v survives: the BDF stage's correction source)
+      // ================= stage 2: BE predictor, x1 = S1 -> S2 (only u+v survives: the BDF stage's correction source; without
+      // that source nothing reads the stage -- it is left out, its scan and look-back chain included, cf. step_warp_kernel.cu)
+      if (CORR)
       {
 #pragma unroll
          for (int jj = 0; jj < CPT; ++jj) xsum[jj] = r[jj].x + r[jj].y;
@@ -313,6 +315,7 @@ var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
             v = vn;
          }
       }
+      else __syncthreads(); // stage 3 reads the neighbouring thread's cell of S1, written in stage 1: the order stage 2's barriers gave
       // ================= stage 3: BDF corrector, x1 = half (S1 for mu<0 rows, S0 for mu>0 rows), x2 = X -> ends^(n+1)
       {
          const unsigned char *const sh = ti.sgn ? t0 : t1;

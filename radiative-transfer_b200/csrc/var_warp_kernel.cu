@@ -462,7 +462,9 @@ var_warp_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
                for (int jj = 0; jj < CPT; ++jj) *reinterpret_cast<double2 *>(th + ox[jj]) = r[jj];
             }
          }
-         // ================= stage 2: BE predictor, x1 = stage-1 result; only u+v survives (the BDF stage's source)
+         // ================= stage 2: BE predictor, x1 = stage-1 result; only u+v survives (the BDF stage's source): left out
+         // when there is no correction source to read it
+         if (CORR)
          {
 #pragma unroll
             for (int jj = 0; jj < CPT; ++jj) xsum[jj] = r[jj].x + r[jj].y;
