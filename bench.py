@@ -620,7 +620,9 @@ def main():
             r = device_timed(rt, sharding, pr, (M, G, N), local_rank, world, rank, dist, max(W, 3), K)
             regimes.append({"dt": dt_r, "V": V_r, "value": r["value"], "ms_per_step": r["ms"] / K, "steps": K, "warmup": max(W, 3),
                             "vs_value": r["value"] / value, "clocks": r["clocks"],
-                            "hbm_frac_per_gpu": (r["value"] / world / 4.0 * 32.0) / (peak * 1e9)})
+                            "hbm_frac_per_gpu": (r["value"] / world / 4.0 * 32.0) / (peak * 1e9),
+                            "note": ("V = 0: the step's third stage (a predictor only the correction source reads) is not computed; the metric "
+                                     "counts the reference's four stage sweeps per step, whose result the step reproduces") if V_r == 0.0 else None})
     local = regimes[0] if regimes else None
 
     cpu = None
