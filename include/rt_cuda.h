@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 4
+#define RT_ABI_VERSION 5
 
 typedef struct rt_params
 {
@@ -109,6 +109,8 @@ typedef struct rt_plan
    int time_levels;      /* time-level buffers allocated: 2 for the fused step, 4 once a step has run stage by stage (ABI 4) */
    int step_kernel;      /* fused step kernel a whole step would use now: 1 = four scalar scans (plain steps), 4 = one 4-vector
                           * scan that also sums phi (per-step output on); RT_CUDA_STEP_KERNEL=1|4 forces one                */
+   int var_scan_steps;   /* cell-dependent fused step: warp-scan steps that are run, 5 = all; 2 when no row of the solver can
+                          * feel more (small time steps; RT_CUDA_VAR_SCAN_STEPS=5 forces all) (ABI 5)                       */
 } rt_plan;
 
 const char *rt_last_error(void);

@@ -66,7 +66,7 @@ class RtPlan(C.Structure):
         ("bytes_per_group", C.c_size_t), ("state_bytes", C.c_size_t), ("free_bytes", C.c_size_t),
         ("total_bytes", C.c_size_t),
         ("fused", C.c_int), ("step_tile_cells", C.c_int), ("step_block", C.c_int), ("step_chain", C.c_int),
-        ("time_levels", C.c_int), ("step_kernel", C.c_int),
+        ("time_levels", C.c_int), ("step_kernel", C.c_int), ("var_scan_steps", C.c_int),
     ]
 
 

@@ -74,6 +74,7 @@ struct rt_solver
    int tab_g0 = 0, tab_n = 0;
    std::vector<double> bd_kappa;                                   // [G][2]: kappa_g at cell 0 / cell N-1
    double *d_bd_T = nullptr, *d_bd_rho = nullptr, *d_bd_kappa = nullptr, *d_bd_B = nullptr, *d_bd_dB = nullptr;
+   int var_scan_steps = 5; // warp-scan steps the fused cell-dependent step has to run (launch_var_scan_steps; RT_CUDA_VAR_SCAN_STEPS=5 forces all)
    double *kap_base() const { return d_kappa_c - (ptrdiff_t)tab_g0 * p.N; }
    double *B_base() const { return d_B_c - (ptrdiff_t)p.group_begin * p.N; }
    double *dB_base() const { return d_dBdT_c - (ptrdiff_t)p.group_begin * p.N; }
@@ -355,6 +356,24 @@ static int compute_var_tables(rt_solver *s, bool with_boundary, bool sharded = f
    ca.B_left = s->d_edge_state[0]; ca.dEB_left = s->d_edge_state[1]; ca.B_right = s->d_edge_state[2]; ca.dEB_right = s->d_edge_state[3];
    launch_cell_terms(ca, s->st);
    s->tm.kernel_launches += 1;
+   if (with_boundary && s->fused_var && p.ts_method == 3)
+   {
+      // once per solver (sigma does not change during a solve): can the later steps of the warp scans matter for any row?
+      const char *se = getenv("RT_CUDA_VAR_SCAN_STEPS");
+      s->var_scan_steps = 5;
+      if (!(se && atoi(se) == 5))
+      {
+         int *d_n = nullptr, n = 5;
+         CK(cudaMalloc(&d_n, sizeof(int)));
+         launch_var_scan_steps(s->vt_fwd(0), s->vt_pitch, p.N, s->Gl, s->d_mu, p.M, p.dx, p.dt / 2., p.dt, p.V / C_LIGHT, 4, d_n, s->st);
+         s->tm.kernel_launches += 1;
+         const cudaError_t e = cudaMemcpyAsync(&n, d_n, sizeof(int), cudaMemcpyDeviceToHost, s->st);
+         if (e == cudaSuccess) cudaStreamSynchronize(s->st);
+         cudaFree(d_n);
+         if (e != cudaSuccess) return fail("rt: scan-step evaluation failed: %s", cudaGetErrorString(e));
+         s->var_scan_steps = n;
+      }
+   }
    if (with_boundary)
    {
       // all G groups at the two boundary cells: Planck integrals at their two temperatures, then the same per-cell pipeline
@@ -781,6 +800,7 @@ extern "C" int rt_get_plan(const rt_solver *s, rt_plan *plan)
    plan->bytes_per_group = (size_t)s->plan_levels * s->p.M * s->Np * sizeof(double2);
    plan->state_bytes = (size_t)s->levels * s->buf_elems * sizeof(double2);
    plan->time_levels = s->levels;
+   plan->var_scan_steps = s->var ? s->var_scan_steps : 5;
    plan->step_kernel = (s->step_kernel == 4 || (s->step_kernel == 0 && ((s->step_phi_host && s->step_group_major) || s->hist_E_host) && s->d_phi_part)) ? 4 : 1;
    cudaSetDevice(s->p.device);
    cudaMemGetInfo(&plan->free_bytes, &plan->total_bytes);
@@ -1044,7 +1064,7 @@ static int run_fused_step_var(rt_solver *s)
    if (event_begin(s, 4, &ep)) return 1;
    int grid = 0;
    if (s->var_warp) CK(launch_var_warp(corr, s->var_chain, s->maps_vwarp, s->mat_maps_vwarp, va, s->num_sms, s->st, &grid));
-   else CK(launch_var_step(corr, s->var_threads, s->var_cpt, s->var_threads == 64 ? s->var_step_mat_slots : 2, s->maps_var, s->mat_maps, va, s->num_sms, s->st, &grid));
+   else CK(launch_var_step(corr, s->var_threads, s->var_cpt, s->var_threads == 64 ? s->var_step_mat_slots : 2, s->var_scan_steps, s->maps_var, s->mat_maps, va, s->num_sms, s->st, &grid));
    if (event_end(s, ep)) return 1;
    const unsigned long long total_tiles = (unsigned long long)a.n_chains * a.tiles_per_chain;
    s->ticket_base += (total_tiles + s->ticket_batch - 1) / s->ticket_batch + (unsigned long long)grid;

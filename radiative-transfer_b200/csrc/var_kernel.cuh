@@ -50,9 +50,12 @@ int var_warp_subtile_cells();
 cudaError_t launch_var_warp(bool corr, int chain_warps, const SweepMaps &maps, const MatMaps &mats, const VarStepArgs &va, int num_sms,
                             cudaStream_t st, int *grid_out);
 bool var_step_shape_supported(int threads, int cpt); // 64 x 4, 128 x 4
-// mat_slots: shared-memory slots of material tables, 2 or (64 x 4 only) 1
-cudaError_t launch_var_step(bool corr, int threads, int cpt, int mat_slots, const SweepMaps &maps, const MatMaps &mats,
+// mat_slots: shared-memory slots of material tables, 2 or (64 x 4 only) 1 ; scan_steps: what launch_var_scan_steps found (5 = all)
+cudaError_t launch_var_step(bool corr, int threads, int cpt, int mat_slots, int scan_steps, const SweepMaps &maps, const MatMaps &mats,
                             const VarStepArgs &va, int num_sms, cudaStream_t st, int *grid_out);
+// *max_steps (device) = the largest number of warp-scan steps any row needs (0..5), from the smallest sigma of every group
+void launch_var_scan_steps(const double *sigma_fwd, int pitch, int N, int groups, const double *mu, int M, double dx, double tau, double dt,
+                           double beta, int cpt, int *max_steps, cudaStream_t st);
 
 bool var_tile_shape_supported(int threads, int cpt); // 64 x 4, 64 x 8, 128 x 4
 // persistent CTAs of `threads` x `cpt` cells; the caller advances its ticket base like after launch_sweep

@@ -43,7 +43,9 @@ constexpr int var_step_min_blocks()
    return by_smem < by_regs ? by_smem : by_regs;
 }
 
-template <bool CORR, int THREADS, int CPT, int MB>
+// NSTEPS: warp-scan steps that are run (5 = all; fewer when launch_var_scan_steps says that the later ones cannot matter for
+// ANY row of the solver: a compile-time constant, so the full kernel carries nothing for it)
+template <bool CORR, int THREADS, int CPT, int MB, int NSTEPS>
 __global__ void __launch_bounds__(THREADS, var_step_min_blocks<CORR, THREADS, CPT, MB>())
 var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ MatMaps mats, const VarStepArgs va)
 {
@@ -148,6 +150,8 @@ var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
       const int j0 = tid * CPT;
       const bool row_first = (ti.tile_start == 0) && (tid == 0);
       const bool full = ti.valid == TILE;
+      // last lane of this warp that holds a real cell (31 when the warp is full, or empty: all identity)
+      const int wl_ = (ti.valid - 1) / CPT - 32 * warp, wlast = (wl_ < 0 || wl_ > 31) ? 31 : wl_;
       const double mu = va.mu[ti.dir];
       double2 xr[CPT];
 #pragma unroll
@@ -214,7 +218,7 @@ var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
          constexpr int k = decltype(kc)::value;
          double Ai = A, Wi = W;
 #pragma unroll
-         for (int d = 1; d < 32; d <<= 1)
+         for (int d = 1; d < (1 << NSTEPS); d <<= 1)
          {
             const double Au = __shfl_up_sync(0xffffffffu, Ai, d), Wu = __shfl_up_sync(0xffffffffu, Wi, d);
             if (lane >= d)
@@ -223,9 +227,13 @@ var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
                Ai *= Au;
             }
          }
+
          double Ae = __shfl_up_sync(0xffffffffu, Ai, 1), We = __shfl_up_sync(0xffffffffu, Wi, 1);
          if (lane == 0) { Ae = 1.0; We = 0.0; }
-         if (lane == 31) { s_wA[warp] = Ai; s_wW[warp] = Wi; }
+         // The warp's aggregate.  A row's last tile is padded with identity elements (alpha = 1), whose products do not die
+         // out: with the short scan the aggregate would not travel from the last real cell to lane 31 (a reflective left
+         // boundary reads the tile's aggregate), so it is taken where it is complete -- at the warp's last real lane.
+         if (lane == (NSTEPS < 5 ? wlast : 31)) { s_wA[warp] = Ai; s_wW[warp] = Wi; }
          __syncthreads(); // (C)
          if (MB == 1 && k == 0 && tid == PROD && nxt < total_tiles) issue_mat(s_desc[slot_next], buf ^ 1); // the tables were read at the tile's start
          double Ap = 1.0, Wp = 0.0;
@@ -354,7 +362,52 @@ var_step_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
 }
 
 // ------------------------------------------------------------------------------------------ host side
-template <bool CORR, int THREADS, int CPT, int MB>
+// The largest number of warp-scan steps any row of the solver needs.  Step s folds in the lane 2^s below with the product
+// of the alphas of cpt 2^s cells; alpha falls with sigma, so over a group it is at most alpha(sigma_min); once that bound
+// is below 2^-70 the step cannot change a result by more than 2^-70 of a neighbouring value.  sigma never changes during
+// a solve (the temperature update moves T, not rho kappa), so this is evaluated once.
+__global__ void var_scan_steps_kernel(const double *__restrict__ sigma_fwd, int pitch, int N, const double *__restrict__ mu, int M,
+                                      double dx, double tau, double dt, double beta, int cpt, int *__restrict__ max_steps)
+{
+   __shared__ double s_min[32];
+   const int gl = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+   double m = 1e300;
+   for (int c = tid; c < N; c += blockDim.x) m = fmin(m, sigma_fwd[(size_t)gl * pitch + c]);
+   for (int d = 16; d > 0; d >>= 1) m = fmin(m, __shfl_xor_sync(0xffffffffu, m, d));
+   if (lane == 0) s_min[warp] = m;
+   __syncthreads();
+   if (tid == 0)
+   {
+      for (int w = 1; w < (int)(blockDim.x >> 5); ++w) m = fmin(m, s_min[w]);
+      s_min[0] = m;
+   }
+   __syncthreads();
+   const double smin = s_min[0];
+   for (int i = tid; i < M; i += blockDim.x)
+   {
+      const double a = fmax(fmax(RowConst<KIND_BE, false>(mu[i], dx, tau, dt, beta).cell_q(smin, 0.0, 0.0).alpha,
+                                 RowConst<KIND_CN, false>(mu[i], dx, tau, dt, beta).cell_q(smin, 0.0, 0.0).alpha),
+                            RowConst<KIND_BDF, false>(mu[i], dx, tau, dt, beta).cell_q(smin, 0.0, 0.0).alpha);
+      double f = a; // alpha_max^(cpt 2^s), s = 0, 1, ...
+      for (int j = 1; j < cpt; ++j) f *= a;
+      int n = 0;
+      for (int sidx = 0; sidx < 5; ++sidx)
+      {
+         if (!(f < 0x1p-70)) n = sidx + 1;
+         f = f * f;
+      }
+      atomicMax(max_steps, n);
+   }
+}
+
+void launch_var_scan_steps(const double *sigma_fwd, int pitch, int N, int groups, const double *mu, int M, double dx, double tau, double dt,
+                           double beta, int cpt, int *max_steps, cudaStream_t st)
+{
+   cudaMemsetAsync(max_steps, 0, sizeof(int), st);
+   var_scan_steps_kernel<<<groups, 256, 0, st>>>(sigma_fwd, pitch, N, mu, M, dx, tau, dt, beta, cpt, max_steps);
+}
+
+template <bool CORR, int THREADS, int CPT, int MB, int NSTEPS>
 static cudaError_t var_step_launch_one(const SweepMaps &maps, const MatMaps &mats, const VarStepArgs &va, int num_sms, cudaStream_t st,
                                        int *grid_out)
 {
@@ -362,7 +415,7 @@ static cudaError_t var_step_launch_one(const SweepMaps &maps, const MatMaps &mat
    std::atomic<int> *plan_slot = nullptr;
    if (cudaError_t e0 = device_plan_slot(plans, &plan_slot)) return e0;
    int ctas_per_sm = plan_slot->load(std::memory_order_acquire);
-   auto kern = var_step_kernel<CORR, THREADS, CPT, MB>;
+   auto kern = var_step_kernel<CORR, THREADS, CPT, MB, NSTEPS>;
    const size_t smem = (size_t)var_step_smem_bytes<CORR, THREADS, CPT, MB>();
    if (ctas_per_sm <= 0)
    {
@@ -385,16 +438,20 @@ static cudaError_t var_step_launch_one(const SweepMaps &maps, const MatMaps &mat
 
 bool var_step_shape_supported(int threads, int cpt) { return (threads == 64 || threads == 128) && cpt == 4; }
 
-cudaError_t launch_var_step(bool corr, int threads, int cpt, int mat_slots, const SweepMaps &maps, const MatMaps &mats, const VarStepArgs &va,
-                            int num_sms, cudaStream_t st, int *grid_out)
+cudaError_t launch_var_step(bool corr, int threads, int cpt, int mat_slots, int scan_steps, const SweepMaps &maps, const MatMaps &mats,
+                            const VarStepArgs &va, int num_sms, cudaStream_t st, int *grid_out)
 {
    if (cpt != 4) return cudaErrorInvalidValue;
-   if (threads == 64 && mat_slots == 1) return corr ? var_step_launch_one<true, 64, 4, 1>(maps, mats, va, num_sms, st, grid_out)
-                                                    : var_step_launch_one<false, 64, 4, 1>(maps, mats, va, num_sms, st, grid_out);
-   if (threads == 64) return corr ? var_step_launch_one<true, 64, 4, 2>(maps, mats, va, num_sms, st, grid_out)
-                                  : var_step_launch_one<false, 64, 4, 2>(maps, mats, va, num_sms, st, grid_out);
-   if (threads == 128) return corr ? var_step_launch_one<true, 128, 4, 2>(maps, mats, va, num_sms, st, grid_out)
-                                   : var_step_launch_one<false, 128, 4, 2>(maps, mats, va, num_sms, st, grid_out);
+   // the short-scan instantiation exists for the default shape only
+   if (threads == 64 && mat_slots == 1 && scan_steps <= 2)
+      return corr ? var_step_launch_one<true, 64, 4, 1, 2>(maps, mats, va, num_sms, st, grid_out)
+                  : var_step_launch_one<false, 64, 4, 1, 2>(maps, mats, va, num_sms, st, grid_out);
+   if (threads == 64 && mat_slots == 1) return corr ? var_step_launch_one<true, 64, 4, 1, 5>(maps, mats, va, num_sms, st, grid_out)
+                                                    : var_step_launch_one<false, 64, 4, 1, 5>(maps, mats, va, num_sms, st, grid_out);
+   if (threads == 64) return corr ? var_step_launch_one<true, 64, 4, 2, 5>(maps, mats, va, num_sms, st, grid_out)
+                                  : var_step_launch_one<false, 64, 4, 2, 5>(maps, mats, va, num_sms, st, grid_out);
+   if (threads == 128) return corr ? var_step_launch_one<true, 128, 4, 2, 5>(maps, mats, va, num_sms, st, grid_out)
+                                   : var_step_launch_one<false, 128, 4, 2, 5>(maps, mats, va, num_sms, st, grid_out);
    return cudaErrorInvalidValue;
 }
 } // namespace rtk

@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol(rt):
     lib = rt.capi.lib()
     for name in declared_functions():
         assert hasattr(lib, name), f"{name} declared in include/rt_cuda.h but not exported"
-    assert lib.rt_abi_version() == 4
+    assert lib.rt_abi_version() == 5
     out = subprocess.check_output(["nm", "-D", "--defined-only", rt.capi.LIB_PATH], text=True)
     exported = {ln.split()[-1] for ln in out.splitlines() if " T " in ln}
     assert set(declared_functions()) <= exported

@@ -126,6 +126,34 @@ def test_per_cell_tables_are_sharded_with_the_groups(rt):
     p.kappa_cell = clean
 
 
+def test_short_scan_kernel_for_small_time_steps(rt, oracle, monkeypatch):
+    """at small time steps no row can feel more than the first two steps of the warp scan (alpha(sigma_min)^16 < 2^-70 for
+    every group and direction): the solver picks the instantiation that runs two (rt_plan::var_scan_steps) -- checked
+    against the oracle like every other case and against the full scan; at dt = 1e-3 it must NOT be picked"""
+    # N = 3000: the rows end inside a tile, whose identity padding must still carry the aggregate to the reflective junction
+    p = synthetic_parameters(rt, M=8, G=6, N=3000, dt=1e-5, V=1.0, steps=2, bc_left=2, bc_right=1)
+    _fields(p)
+    with rt.Solver(p) as s:
+        assert s.plan().var_scan_steps == 2
+        s.solve()
+        short = s.ends(0)
+    _compare(rt, oracle, p, 8)
+    for N, bcl in ((2048, 2), (4097, 1), (300, 2)):
+        q = synthetic_parameters(rt, M=4, G=3, N=N, dt=1e-5, V=1.0, steps=2, bc_left=bcl, bc_right=1)
+        _fields(q)
+        _compare(rt, oracle, q, 8, threads=2)
+    monkeypatch.setenv("RT_CUDA_VAR_SCAN_STEPS", "5")
+    with rt.Solver(p) as s:
+        assert s.plan().var_scan_steps == 5
+        s.solve()
+        assert state_err(short, s.ends(0)) <= 1e-13
+    monkeypatch.delenv("RT_CUDA_VAR_SCAN_STEPS")
+    p = synthetic_parameters(rt, M=8, G=6, N=3000, dt=1e-3, V=1.0, steps=1, bc_left=2, bc_right=1)
+    _fields(p)
+    with rt.Solver(p) as s:
+        assert s.plan().var_scan_steps == 5
+
+
 def test_validation_is_refused_with_cell_fields(rt):
     p = synthetic_parameters(rt, M=4, G=3, N=100, dt=1e-3, V=1.0, steps=1)
     p.include_validation = True
