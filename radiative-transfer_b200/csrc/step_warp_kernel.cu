@@ -28,7 +28,10 @@
 #include "sweep_device.cuh"
 
 #ifndef STEP_SPIN_SLEEP
-#define STEP_SPIN_SLEEP 0 // nanoseconds a warp sleeps between two polls of the previous warp's carry word (A/B knob)
+// nanoseconds a warp sleeps between two polls of the previous warp's carry word.  Measured on C4 at 20 steps, where the
+// board runs into its power cap: 0 -> 100 ns leaves the rate where it is (+0.1 ... +0.4 %) and takes 5-10 % off the peak
+// board power (870 -> 800-830 W; 250 ns: 725 W) -- the polls were instructions and watts, not progress.
+#define STEP_SPIN_SLEEP 100
 #endif
 
 // Polling loops and warp convergence.  This kernel has no CTA barrier in its tile loop, and ptxas is told that the warp
@@ -394,7 +397,12 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
             // then read the word -- still checked against its own sequence number below
             const int *seq_word = reinterpret_cast<const int *>(src) + 2;
             while (poll_again<4>(ld_flag(seq_word) != seq + 1))
+            {
+#if STEP_SPIN_SLEEP > 0
+               __nanosleep(STEP_SPIN_SLEEP); // a polling warp burns issue slots and power the working warps could use
+#endif
                if (++spins > SPIN_LIMIT_S) __trap();
+            }
             double2 w = lds_word(src);
             while (poll_again<4>((int)__double_as_longlong(w.y) != seq + 1))
             {
