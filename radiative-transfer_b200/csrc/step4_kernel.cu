@@ -35,6 +35,7 @@
 #include "rt_common.cuh"
 #include "step_kernel.cuh"
 #include "sweep_device.cuh"
+#include "warp_tile.cuh"
 
 #ifndef RT_SPIN_SHIFT
 #define RT_SPIN_SHIFT 22
@@ -202,27 +203,6 @@ struct Tile
    int pad[3];
 };
 
-__device__ __forceinline__ double2 lds_word(const double2 *p)
-{
-   double2 v;
-   asm volatile("ld.volatile.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(smem_u32(p)) : "memory");
-   return v;
-}
-__device__ __forceinline__ void sts_word(double2 *p, double value, int seq1)
-{
-   const double f = __longlong_as_double((long long)seq1);
-   asm volatile("st.volatile.shared.v2.f64 [%0], {%1, %2};" ::"r"(smem_u32(p)), "d"(value), "d"(f) : "memory");
-}
-__device__ __forceinline__ int ld_flag(const int *p)
-{
-   int v;
-   asm volatile("ld.volatile.shared.s32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)) : "memory");
-   return v;
-}
-__device__ __forceinline__ void st_flag(int *p, int v)
-{
-   asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory");
-}
 __device__ __forceinline__ double2 lds2(const double *p) { return *reinterpret_cast<const double2 *>(p); }
 // every polling loop leaves through a warp vote: all lanes leave in the same iteration (see step_warp_kernel.cu on why a
 // 16-byte poll is not warp-uniform on the hardware although ptxas takes it for one)

@@ -26,6 +26,7 @@
 #include "rt_common.cuh"
 #include "step_kernel.cuh"
 #include "sweep_device.cuh"
+#include "warp_tile.cuh"
 
 #ifndef STEP_SPIN_SLEEP
 // nanoseconds a warp sleeps between two polls of the previous warp's carry word.  Measured on C4 at 20 steps, where the
@@ -162,28 +163,6 @@ struct WarpTile
    int tf;    // tile in row * 4 + sgn * 2 + junction
 };
 
-// {value, sequence} carry words between the warps of a CTA: one 128-bit shared-memory access each way
-__device__ __forceinline__ double2 lds_word(const double2 *p)
-{
-   double2 v;
-   asm volatile("ld.volatile.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(smem_u32(p)) : "memory");
-   return v;
-}
-__device__ __forceinline__ void sts_word(double2 *p, double value, int seq1)
-{
-   const double f = __longlong_as_double((long long)seq1);
-   asm volatile("st.volatile.shared.v2.f64 [%0], {%1, %2};" ::"r"(smem_u32(p)), "d"(value), "d"(f) : "memory");
-}
-__device__ __forceinline__ int ld_flag(const int *p)
-{
-   int v;
-   asm volatile("ld.volatile.shared.s32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)) : "memory");
-   return v;
-}
-__device__ __forceinline__ void st_flag(int *p, int v)
-{
-   asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory");
-}
 
 template <bool CORR, int CPT, int NW>
 __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __grid_constant__ SweepMaps maps, const StepArgs a)

@@ -29,6 +29,7 @@
 #include "rt_common.cuh"
 #include "step_kernel.cuh"
 #include "sweep_device.cuh"
+#include "warp_tile.cuh"
 #include "sweep_kernel.cuh"
 #include "var_device.cuh"
 #include "var_kernel.cuh"
@@ -61,27 +62,6 @@ struct WarpTile // one tile descriptor of the ring: 16 bytes
    int p;     // tile position in the chain
    int tf;    // tile in row * 4 + sgn * 2 + junction
 };
-__device__ __forceinline__ double2 lds_word(const double2 *p)
-{
-   double2 v;
-   asm volatile("ld.volatile.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(smem_u32(p)) : "memory");
-   return v;
-}
-__device__ __forceinline__ void sts_word(double2 *p, double value, int seq1)
-{
-   const double f = __longlong_as_double((long long)seq1);
-   asm volatile("st.volatile.shared.v2.f64 [%0], {%1, %2};" ::"r"(smem_u32(p)), "d"(value), "d"(f) : "memory");
-}
-__device__ __forceinline__ int ld_flag(const int *p)
-{
-   int v;
-   asm volatile("ld.volatile.shared.s32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)) : "memory");
-   return v;
-}
-__device__ __forceinline__ void st_flag(int *p, int v)
-{
-   asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory");
-}
 constexpr int CPT = 4, WT = 32 * CPT, WT_BYTES = WT * 16, MAT_BYTES = WT * 8;
 template <bool CORR>
 constexpr int warp_smem_bytes()
