@@ -154,15 +154,6 @@ void launch_pack_step_coef(const double *be, const double *cn, const double *bdf
                                                             reinterpret_cast<const RowCoef *>(bdf), out, rows, corr ? 1 : 0);
 }
 
-// one tile descriptor of the ring: 16 bytes
-struct WarpTile
-{
-   int row;   // row of the batch, -1 = ticket past the end
-   int chain; // look-back chain (row, or pair of mirrored rows with a reflective left boundary)
-   int p;     // tile position in the chain
-   int tf;    // tile in row * 4 + sgn * 2 + junction
-};
-
 
 template <bool CORR, int CPT, int NW>
 __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __grid_constant__ SweepMaps maps, const StepArgs a)
@@ -204,39 +195,7 @@ __global__ void __launch_bounds__(32 * NW, 16 / NW) step_warp_kernel(const __gri
       q_start = (long long)(t0 - a.ticket_base) * batch;
       if (lane < batch)
       {
-         const long long t = q_start + lane;
-         WarpTile d;
-         d.row = -1; d.chain = 0; d.p = 0; d.tf = 0;
-         if (t < total_tiles)
-         {
-            int p, chain;
-            if (total_tiles < 0x7fffffffll)
-            {
-               p = (int)((unsigned)t / (unsigned)a.n_chains);
-               chain = (int)((unsigned)t - (unsigned)p * (unsigned)a.n_chains);
-            }
-            else
-            {
-               p = (int)(t / a.n_chains);
-               chain = (int)(t - (long long)p * a.n_chains);
-            }
-            const int gl = chain / dm, pp = chain - gl * dm;
-            int sgn, row, tr;
-            if (a.reflective_left)
-            {
-               sgn = (p >= a.tiles_per_row) ? 1 : 0;
-               row = gl * a.M + (sgn ? half_m + pp : half_m - 1 - pp);
-               tr = sgn ? p - a.tiles_per_row : p;
-            }
-            else
-            {
-               sgn = (pp >= half_m) ? 1 : 0;
-               row = chain;
-               tr = p;
-            }
-            d.row = row; d.chain = chain; d.p = p;
-            d.tf = tr * 4 + sgn * 2 + ((tr == 0 && p > 0) ? 1 : 0);
-         }
+         const WarpTile d = decode_warp_tile(a, q_start + lane, total_tiles, half_m, dm);
          s_desc[(dec + lane) & 15] = d;
       }
       if (q_start + batch > total_tiles) ended = true;

@@ -55,13 +55,6 @@ __device__ __forceinline__ void mbar_wait_vote(unsigned long long *bar, unsigned
    while (__any_sync(0xffffffffu, !mbar_try_wait(bar, parity)))
       if (++spins > SPIN_W) __trap();
 }
-struct WarpTile // one tile descriptor of the ring: 16 bytes
-{
-   int row;   // row of the batch, -1 = ticket past the end
-   int chain; // look-back chain
-   int p;     // tile position in the chain
-   int tf;    // tile in row * 4 + sgn * 2 + junction
-};
 constexpr int CPT = 4, WT = 32 * CPT, WT_BYTES = WT * 16, MAT_BYTES = WT * 8;
 template <bool CORR>
 constexpr int warp_smem_bytes()
@@ -116,29 +109,7 @@ var_warp_kernel(const __grid_constant__ SweepMaps maps, const __grid_constant__ 
       q_start = (long long)(t0 - a.ticket_base) * batch;
       if (lane < batch)
       {
-         const long long t = q_start + lane;
-         WarpTile d;
-         d.row = -1; d.chain = 0; d.p = 0; d.tf = 0;
-         if (t < total_tiles)
-         {
-            const int p = (int)(t / a.n_chains), chain = (int)(t - (long long)p * a.n_chains);
-            const int gl = chain / dm, pp = chain - gl * dm;
-            int sgn, row, tr;
-            if (a.reflective_left)
-            {
-               sgn = (p >= a.tiles_per_row) ? 1 : 0;
-               row = gl * a.M + (sgn ? half_m + pp : half_m - 1 - pp);
-               tr = sgn ? p - a.tiles_per_row : p;
-            }
-            else
-            {
-               sgn = (pp >= half_m) ? 1 : 0;
-               row = chain;
-               tr = p;
-            }
-            d.row = row; d.chain = chain; d.p = p;
-            d.tf = tr * 4 + sgn * 2 + ((tr == 0 && p > 0) ? 1 : 0);
-         }
+         const WarpTile d = decode_warp_tile(a, q_start + lane, total_tiles, half_m, dm);
          s_desc[(dec + lane) & 15] = d;
       }
       if (q_start + batch > total_tiles) ended = true;
